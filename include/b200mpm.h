@@ -1,0 +1,373 @@
+/*
+ * include/b200mpm.h -- C ABI of libb200mpm.so: the B200-native replacement for Taichi's
+ * sparse-SNode struct-for / MLS-MPM hot path (arch = cuda, sm_100a only).
+ *
+ * Part 1 (ti_*) keeps the names, argument meaning, struct layouts and error convention of
+ * the reference C-API subset this path uses, so a client compiled against
+ *   /root/reference/c_api/include/taichi/taichi_core.h   and   taichi_cuda.h
+ * links against this library unchanged (reference line numbers given per entry).
+ * Part 2 (b2_*) exports what the reference only offers through pybind
+ * (taichi/python/export_lang.cpp:498-529 SNode builders; Program::compile_kernel /
+ * launch_kernel): SNode-tree building, activation, listgen, struct-for built-ins, GC, and
+ * the prebuilt MLS-MPM kernels.
+ *
+ * Conventions (same as the reference, taichi_core_impl.h:80-92, taichi_core_impl.cpp:63-70):
+ * no exception or error code crosses the ABI; failing calls record (TiError, message) in a
+ * thread-local slot read with ti_get_last_error and return TI_NULL_HANDLE / void / -1.
+ * All launches are asynchronous and in-order on ONE CUDA stream (ti_set_cuda_stream
+ * replaces it); ti_wait / b2_sync synchronise.  Pointers named *_any may be host or device
+ * pointers (detected like runtime/cuda/kernel_launcher.cpp:7-13 does); host data is staged.
+ * There is no CPU fallback: without a CUDA device ti_create_runtime fails.
+ */
+#ifndef B200MPM_H
+#define B200MPM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(_WIN32)
+#define TI_DLL_EXPORT __declspec(dllexport)
+#define TI_API_CALL __stdcall
+#else
+#define TI_DLL_EXPORT __attribute__((visibility("default")))
+#define TI_API_CALL
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ===================================================================================== */
+/* Part 1: Taichi C-API subset (taichi_core.h / taichi_cuda.h)                            */
+/* ===================================================================================== */
+#ifndef TI_C_API_VERSION
+#define TI_C_API_VERSION 1007000 /* taichi_core.h:229 */
+#endif
+
+typedef uint32_t TiBool;  /* taichi_core.h:246 */
+typedef uint32_t TiFlags; /* :266 */
+#define TI_FALSE 0
+#define TI_TRUE 1
+#define TI_NULL_HANDLE 0
+
+typedef struct TiRuntime_t *TiRuntime;           /* :280 */
+typedef struct TiAotModule_t *TiAotModule;       /* :286 */
+typedef struct TiMemory_t *TiMemory;             /* :291 */
+typedef struct TiImage_t *TiImage;               /* :296 (graphics: not supported) */
+typedef struct TiSampler_t *TiSampler;           /* :303 (graphics: not supported) */
+typedef struct TiKernel_t *TiKernel;             /* :308 */
+typedef struct TiComputeGraph_t *TiComputeGraph; /* :314 */
+
+typedef enum TiError { /* :319-353 */
+  TI_ERROR_SUCCESS = 0,
+  TI_ERROR_NOT_SUPPORTED = -1,
+  TI_ERROR_CORRUPTED_DATA = -2,
+  TI_ERROR_NAME_NOT_FOUND = -3,
+  TI_ERROR_INVALID_ARGUMENT = -4,
+  TI_ERROR_ARGUMENT_NULL = -5,
+  TI_ERROR_ARGUMENT_OUT_OF_RANGE = -6,
+  TI_ERROR_ARGUMENT_NOT_FOUND = -7,
+  TI_ERROR_INVALID_INTEROP = -8,
+  TI_ERROR_INVALID_STATE = -9,
+  TI_ERROR_INCOMPATIBLE_MODULE = -10,
+  TI_ERROR_OUT_OF_MEMORY = -11,
+  TI_ERROR_MAX_ENUM = 0xffffffff,
+} TiError;
+
+typedef enum TiArch { /* :358-375 */
+  TI_ARCH_RESERVED = 0,
+  TI_ARCH_VULKAN = 1,
+  TI_ARCH_METAL = 2,
+  TI_ARCH_CUDA = 3,
+  TI_ARCH_X64 = 4,
+  TI_ARCH_ARM64 = 5,
+  TI_ARCH_OPENGL = 6,
+  TI_ARCH_GLES = 7,
+  TI_ARCH_MAX_ENUM = 0xffffffff,
+} TiArch;
+
+typedef enum TiDataType { /* :423-450 */
+  TI_DATA_TYPE_F16 = 0,
+  TI_DATA_TYPE_F32 = 1,
+  TI_DATA_TYPE_F64 = 2,
+  TI_DATA_TYPE_I8 = 3,
+  TI_DATA_TYPE_I16 = 4,
+  TI_DATA_TYPE_I32 = 5,
+  TI_DATA_TYPE_I64 = 6,
+  TI_DATA_TYPE_U1 = 7,
+  TI_DATA_TYPE_U8 = 8,
+  TI_DATA_TYPE_U16 = 9,
+  TI_DATA_TYPE_U32 = 10,
+  TI_DATA_TYPE_U64 = 11,
+  TI_DATA_TYPE_GEN = 12,
+  TI_DATA_TYPE_UNKNOWN = 13,
+  TI_DATA_TYPE_MAX_ENUM = 0xffffffff,
+} TiDataType;
+
+typedef enum TiArgumentType { /* :455-469 */
+  TI_ARGUMENT_TYPE_I32 = 0,
+  TI_ARGUMENT_TYPE_F32 = 1,
+  TI_ARGUMENT_TYPE_NDARRAY = 2,
+  TI_ARGUMENT_TYPE_TEXTURE = 3,
+  TI_ARGUMENT_TYPE_SCALAR = 4,
+  TI_ARGUMENT_TYPE_TENSOR = 5,
+  TI_ARGUMENT_TYPE_MAX_ENUM = 0xffffffff,
+} TiArgumentType;
+
+typedef enum TiMemoryUsageFlagBits { /* :475-484 */
+  TI_MEMORY_USAGE_STORAGE_BIT = 1 << 0,
+  TI_MEMORY_USAGE_UNIFORM_BIT = 1 << 1,
+  TI_MEMORY_USAGE_VERTEX_BIT = 1 << 2,
+  TI_MEMORY_USAGE_INDEX_BIT = 1 << 3,
+} TiMemoryUsageFlagBits;
+typedef TiFlags TiMemoryUsageFlags;
+
+typedef struct TiMemoryAllocateInfo { /* :490-503 */
+  uint64_t size;
+  TiBool host_write;
+  TiBool host_read;
+  TiBool export_sharing;
+  TiMemoryUsageFlags usage;
+} TiMemoryAllocateInfo;
+
+typedef struct TiMemorySlice { /* :509-516 */
+  TiMemory memory;
+  uint64_t offset;
+  uint64_t size;
+} TiMemorySlice;
+
+typedef struct TiNdShape { /* :522-527 */
+  uint32_t dim_count;
+  uint32_t dims[16];
+} TiNdShape;
+
+typedef struct TiNdArray { /* :532-542 */
+  TiMemory memory;
+  TiNdShape shape;
+  TiNdShape elem_shape;
+  TiDataType elem_type;
+} TiNdArray;
+
+/* Texture plumbing exists only so that sizeof(TiArgument) matches the reference. */
+typedef struct TiImageExtent {
+  uint32_t width, height, depth, array_layer_count;
+} TiImageExtent;
+typedef struct TiTexture { /* :765-777 */
+  TiImage image;
+  TiSampler sampler;
+  uint32_t dimension; /* TiImageDimension */
+  TiImageExtent extent;
+  uint32_t format; /* TiFormat */
+} TiTexture;
+
+typedef union TiScalarValue { /* :788-797 */
+  uint8_t x8;
+  uint16_t x16;
+  uint32_t x32;
+  uint64_t x64;
+} TiScalarValue;
+typedef struct TiScalar {
+  TiDataType type;
+  TiScalarValue value;
+} TiScalar;
+typedef union TiTensorValue { /* :810-819 */
+  uint8_t x8[128];
+  uint16_t x16[64];
+  uint32_t x32[32];
+  uint64_t x64[16];
+} TiTensorValue;
+typedef struct TiTensorValueWithLength {
+  uint32_t length;
+  TiTensorValue data;
+} TiTensorValueWithLength;
+typedef struct TiTensor {
+  TiDataType type;
+  TiTensorValueWithLength contents;
+} TiTensor;
+
+typedef union TiArgumentValue { /* :840-855 */
+  int32_t i32;
+  float f32;
+  TiNdArray ndarray;
+  TiTexture texture;
+  TiScalar scalar;
+  TiTensor tensor;
+} TiArgumentValue;
+typedef struct TiArgument { /* :860-865 */
+  TiArgumentType type;
+  TiArgumentValue value;
+} TiArgument;
+typedef struct TiNamedArgument { /* :870-875 */
+  const char *name;
+  TiArgument argument;
+} TiNamedArgument;
+
+TI_DLL_EXPORT uint32_t TI_API_CALL ti_get_version(void);                                     /* :881 */
+TI_DLL_EXPORT void TI_API_CALL ti_get_available_archs(uint32_t *arch_count, TiArch *archs);  /* :898 */
+TI_DLL_EXPORT TiError TI_API_CALL ti_get_last_error(uint64_t *message_size, char *message);  /* :905 */
+TI_DLL_EXPORT void TI_API_CALL ti_set_last_error(TiError error, const char *message);        /* :917 */
+/* arch must be TI_ARCH_CUDA; device_index selects the CUDA device of THIS process (the
+   reference rejects != 0, taichi_core_impl.cpp:270-297; the multi-GPU layer runs one process
+   per GPU and passes LOCAL_RANK). */
+TI_DLL_EXPORT TiRuntime TI_API_CALL ti_create_runtime(TiArch arch, uint32_t device_index);   /* :927 */
+TI_DLL_EXPORT void TI_API_CALL ti_destroy_runtime(TiRuntime runtime);                        /* :937 */
+TI_DLL_EXPORT TiMemory TI_API_CALL ti_allocate_memory(TiRuntime runtime,
+                                                      const TiMemoryAllocateInfo *allocate_info); /* :960 */
+TI_DLL_EXPORT void TI_API_CALL ti_free_memory(TiRuntime runtime, TiMemory memory);           /* :967 */
+/* Returns a host pointer: the allocation itself for host_read/host_write memory (pinned,
+   device-visible), else a staging copy written back by ti_unmap_memory. */
+TI_DLL_EXPORT void *TI_API_CALL ti_map_memory(TiRuntime runtime, TiMemory memory);           /* :974 */
+TI_DLL_EXPORT void TI_API_CALL ti_unmap_memory(TiRuntime runtime, TiMemory memory);          /* :982 */
+TI_DLL_EXPORT void TI_API_CALL ti_copy_memory_device_to_device(TiRuntime runtime,
+                                                               const TiMemorySlice *dst_memory,
+                                                               const TiMemorySlice *src_memory); /* :1008 */
+TI_DLL_EXPORT void TI_API_CALL ti_launch_kernel(TiRuntime runtime, TiKernel kernel,
+                                                uint32_t arg_count, const TiArgument *args);  /* :1044 */
+TI_DLL_EXPORT void TI_API_CALL ti_launch_compute_graph(TiRuntime runtime, TiComputeGraph graph,
+                                                       uint32_t arg_count,
+                                                       const TiNamedArgument *args);         /* :1053 */
+TI_DLL_EXPORT void TI_API_CALL ti_flush(TiRuntime runtime);                                  /* :1063 */
+TI_DLL_EXPORT void TI_API_CALL ti_wait(TiRuntime runtime);                                   /* :1069 */
+/* module_path: "builtin:mpm88" | "builtin:mpm3d" | "builtin:mpm128" (prebuilt kernel tables
+   named as tests/cpp/aot/python_scripts/mpm88_graph_aot.py:29-108), or a directory whose
+   name ends in one of those (so TAICHI_AOT_FOLDER_PATH-style callers keep working). */
+TI_DLL_EXPORT TiAotModule TI_API_CALL ti_load_aot_module(TiRuntime runtime, const char *module_path); /* :1076 */
+TI_DLL_EXPORT void TI_API_CALL ti_destroy_aot_module(TiAotModule aot_module);                /* :1091 */
+TI_DLL_EXPORT TiKernel TI_API_CALL ti_get_aot_module_kernel(TiAotModule aot_module, const char *name); /* :1098 */
+TI_DLL_EXPORT TiComputeGraph TI_API_CALL ti_get_aot_module_compute_graph(TiAotModule aot_module,
+                                                                         const char *name);  /* :1106 */
+
+/* taichi_cuda.h:12-32 */
+typedef struct TiCudaMemoryInteropInfo {
+  void *ptr;
+  uint64_t size;
+} TiCudaMemoryInteropInfo;
+TI_DLL_EXPORT void TI_API_CALL ti_export_cuda_memory(TiRuntime runtime, TiMemory memory,
+                                                     TiCudaMemoryInteropInfo *interop_info);
+/* Borrowed: never freed by the runtime (rhi/cuda/cuda_device.cpp:106,189-201). */
+TI_DLL_EXPORT TiMemory TI_API_CALL ti_import_cuda_memory(TiRuntime runtime, void *ptr, size_t memory_size);
+TI_DLL_EXPORT void TI_API_CALL ti_set_cuda_stream(void *stream);
+TI_DLL_EXPORT void TI_API_CALL ti_get_cuda_stream(void **stream);
+
+/* ===================================================================================== */
+/* Part 2: SNode trees, struct-for built-ins, MLS-MPM                                      */
+/* ===================================================================================== */
+#define B2_MAX_AXES 12 /* taichi/inc/constants.h:5 */
+
+enum { B2_ROOT = 0, B2_DENSE = 1, B2_POINTER = 2, B2_BITMASKED = 3, B2_DYNAMIC = 4, B2_PLACE = 5 };
+
+/* One SNode of a tree, in creation order (index 0 = root).  Mirrors the arguments of
+   SNode::dense/pointer/bitmasked/dynamic/place (export_lang.cpp:498-529) and the geometry
+   rules of SNode::create_node (taichi/ir/snode.cpp:37-125). */
+typedef struct B2SNodeDesc {
+  int32_t type;
+  int32_t parent; /* index into the array; -1 for the root */
+  int32_t num_axes;
+  int32_t axes[B2_MAX_AXES];  /* physical axis ids, 0 = i, 1 = j ... */
+  int32_t sizes[B2_MAX_AXES]; /* extent along each listed axis */
+  int32_t dtype_bytes;        /* place: 4 (f32/i32) or 8 */
+  int32_t chunk_size;         /* dynamic */
+} B2SNodeDesc;
+
+typedef struct B2Tree_t *B2Tree;
+typedef struct B2Mpm_t *B2Mpm;
+
+/* Program::add_snode_tree + materialize_snode_tree (program.cpp:238-255,
+   llvm_runtime_executor.cpp:391-469): layout, zeroed root buffer, one element list per SNode,
+   one NodeManager per pointer/dynamic SNode. */
+TI_DLL_EXPORT B2Tree b2_create_tree(TiRuntime runtime, const B2SNodeDesc *desc, int32_t n);
+TI_DLL_EXPORT void b2_destroy_tree(B2Tree tree);
+TI_DLL_EXPORT int64_t b2_snode_num_cells(B2Tree tree, int32_t snode); /* num_cells_per_container */
+TI_DLL_EXPORT int64_t b2_snode_cell_size(B2Tree tree, int32_t snode); /* SNode._cell_size_bytes  */
+TI_DLL_EXPORT int64_t b2_snode_node_size(B2Tree tree, int32_t snode); /* bytes of one container  */
+
+/* coords: n x 12 int32 (global indices by physical axis), host or device. */
+TI_DLL_EXPORT int32_t b2_activate(B2Tree tree, int32_t snode, const int32_t *coords_any, int64_t n);   /* ti.activate, Pointer/Bitmasked/Dynamic_activate */
+TI_DLL_EXPORT int32_t b2_deactivate(B2Tree tree, int32_t snode, const int32_t *coords_any, int64_t n); /* ti.deactivate (+gc task, offload.cpp:671-695) */
+TI_DLL_EXPORT int32_t b2_is_active(B2Tree tree, int32_t snode, const int32_t *coords_any, int64_t n, uint8_t *out_any); /* ti.is_active */
+/* clear_list + element_listgen_root/nonroot for every level root..snode (offload.cpp:204-222);
+   returns the number of Elements of `snode`'s list (synchronises). */
+TI_DLL_EXPORT int64_t b2_listgen(B2Tree tree, int32_t snode);
+/* Same, asynchronous (no read-back). */
+TI_DLL_EXPORT int32_t b2_listgen_async(B2Tree tree, int32_t snode);
+/* Copies up to cap Elements as 14 x int32 {pcoord[12], loop_lo, loop_hi}; returns the count. */
+TI_DLL_EXPORT int64_t b2_get_list(B2Tree tree, int32_t snode, int32_t *out_any, int64_t cap);
+/* struct-for over `snode` (listgen + active-cell filter): writes the visited coordinates
+   (12 x int32 each) and returns how many cells were visited.  out may be NULL (count only). */
+TI_DLL_EXPORT int64_t b2_struct_for_coords(B2Tree tree, int32_t snode, int32_t *out_any, int64_t cap);
+TI_DLL_EXPORT int32_t b2_deactivate_all(B2Tree tree, int32_t snode); /* SNode.deactivate_all, snode.py:286-304 */
+TI_DLL_EXPORT int32_t b2_gc(B2Tree tree, int32_t snode);             /* gc_parallel_0/1/2 fused */
+/* out[4] = {data_list size, free_list size, recycled_list size, free_list_used} */
+TI_DLL_EXPORT int32_t b2_alloc_stats(B2Tree tree, int32_t snode, int32_t *out_host);
+TI_DLL_EXPORT int64_t b2_num_dynamically_allocated(B2Tree tree, int32_t snode); /* snode.py _num_dynamically_allocated */
+/* Field element access through the full access path (lower_access.cpp:227-281): writes
+   activate, reads of inactive cells return the ambient zero. */
+TI_DLL_EXPORT int32_t b2_write(B2Tree tree, int32_t place, const int32_t *coords_any, int64_t n, const void *vals_any, int32_t atomic_add_f32);
+TI_DLL_EXPORT int32_t b2_read(B2Tree tree, int32_t place, const int32_t *coords_any, int64_t n, void *vals_any);
+TI_DLL_EXPORT int32_t b2_dynamic_append_i32(B2Tree tree, int32_t dyn, const int32_t *coords_any, int64_t n, const int32_t *vals_any); /* ti.append */
+TI_DLL_EXPORT int32_t b2_dynamic_length(B2Tree tree, int32_t dyn, const int32_t *coords_any, int64_t n, int32_t *out_any);          /* ti.length */
+/* Whole-field operations = struct-fors with built-in bodies. */
+TI_DLL_EXPORT int32_t b2_field_fill(B2Tree tree, int32_t place, uint32_t value_bits);      /* field.fill over ACTIVE cells */
+/* dense row-major image of the field over `shape` (ndim = number of active axes of the place's
+   path, ascending axis order); inactive cells read 0 (field.to_numpy, _kernels.py:40-60) */
+TI_DLL_EXPORT int32_t b2_field_to_dense(B2Tree tree, int32_t place, void *out_any);
+TI_DLL_EXPORT int32_t b2_field_from_dense(B2Tree tree, int32_t place, const void *in_any); /* activates everything (from_numpy) */
+/* op: 0 add, 1 min, 2 max; dtype 0 f32, 1 i32.  reduce_* of runtime.cpp:1235-1266 behind a
+   thread-local accumulator (make_thread_local.cpp:100-213). Result written to out_host (4 B). */
+TI_DLL_EXPORT int32_t b2_field_reduce(B2Tree tree, int32_t place, int32_t op, int32_t dtype, void *out_host);
+/* Dense-array reductions (range-for with TLS). */
+TI_DLL_EXPORT int32_t b2_reduce(TiRuntime runtime, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_host);
+
+/* runtime-level */
+TI_DLL_EXPORT void b2_sync(TiRuntime runtime);
+TI_DLL_EXPORT int32_t b2_device_index(TiRuntime runtime);
+TI_DLL_EXPORT int64_t b2_pool_bytes_used(TiRuntime runtime); /* memory-profiler query */
+TI_DLL_EXPORT void b2_set_pool_size(uint64_t bytes);         /* ti.init(device_memory_GB=), before ti_create_runtime */
+/* Kernel launch counter (all kernels this library launched since creation). */
+TI_DLL_EXPORT uint64_t b2_launch_count(TiRuntime runtime);
+/* device-side error channel (taichi_assert_format / check_runtime_error): returns 0 if none,
+   else copies the message. */
+TI_DLL_EXPORT int32_t b2_check_runtime_error(TiRuntime runtime, char *msg, uint64_t cap);
+
+/* ---------------------------- MLS-MPM (3-D, mpm3d.py:36-81 model) ---------------------- */
+typedef struct B2MpmParams {
+  int32_t n_grid;     /* cells per axis (multiple of 4)                                   */
+  int32_t layout;     /* 0: dense(n/4).dense(4)   1: pointer(n/32).bitmasked(8).dense(4)
+                         2: pointer(n/32).pointer(8).dense(4)                              */
+  float dt, E, p_rho, gravity; /* mpm3d.py:13-23                                           */
+  int32_t bound;      /* mpm3d.py:23                                                       */
+  int32_t block_local;/* 1: shared-memory pad P2G/G2P (ti.block_local), 0: plain atomics   */
+  int32_t bls_activate_halo; /* 1: reproduce the CUDA-BLS epilogue's wider active set      */
+  int32_t slab_lo, slab_hi;  /* owned range of 4^3-block indices along i ([0,n/4) = all)    */
+  int64_t max_particles;
+} B2MpmParams;
+
+TI_DLL_EXPORT B2Mpm b2_mpm_create(TiRuntime runtime, const B2MpmParams *params);
+TI_DLL_EXPORT void b2_mpm_destroy(B2Mpm mpm);
+TI_DLL_EXPORT B2Tree b2_mpm_tree(B2Mpm mpm);          /* the grid's SNode tree (leaf: dense 4^3 of {vx,vy,vz,m}) */
+TI_DLL_EXPORT int32_t b2_mpm_leaf_snode(B2Mpm mpm);   /* id of the dense(4^3) SNode   */
+/* x[N][3], v[N][3], C[N][3][3], J[N] in the reference's field layout; host or device. */
+TI_DLL_EXPORT int32_t b2_mpm_set_particles(B2Mpm mpm, int64_t n, const float *x_any, const float *v_any, const float *C_any, const float *J_any);
+TI_DLL_EXPORT int32_t b2_mpm_add_particles(B2Mpm mpm, int64_t n, const float *x_any, const float *v_any, const float *C_any, const float *J_any, const int32_t *ids_any);
+TI_DLL_EXPORT int64_t b2_mpm_num_particles(B2Mpm mpm);
+/* Any pointer may be NULL. Output is in original particle-id order. */
+TI_DLL_EXPORT int32_t b2_mpm_get_particles(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *J_any);
+TI_DLL_EXPORT int32_t b2_mpm_substep(B2Mpm mpm, int32_t nsteps);
+/* individual phases (mpm88_graph_aot.py kernel split) */
+TI_DLL_EXPORT int32_t b2_mpm_clear_grid(B2Mpm mpm);
+TI_DLL_EXPORT int32_t b2_mpm_p2g(B2Mpm mpm);
+TI_DLL_EXPORT int32_t b2_mpm_grid_op(B2Mpm mpm);
+TI_DLL_EXPORT int32_t b2_mpm_g2p(B2Mpm mpm);
+/* dense image of the grid, [n][n][n][4] floats {vx,vy,vz,m}; inactive cells 0 */
+TI_DLL_EXPORT int32_t b2_mpm_grid_to_dense(B2Mpm mpm, float *out_any);
+/* out_host[8]: {n_particles, n_active_blocks, n_bins, n_work_items, sum_m, sum_px, sum_py, sum_pz} (doubles) */
+TI_DLL_EXPORT int32_t b2_mpm_stats(B2Mpm mpm, double *out_host);
+/* per-phase device time of the last b2_mpm_substep call with profiling on, ms:
+   {clear, p2g, listgen, grid_op, g2p, rebin} */
+TI_DLL_EXPORT int32_t b2_mpm_set_profiling(B2Mpm mpm, int32_t on);
+TI_DLL_EXPORT int32_t b2_mpm_phase_ms(B2Mpm mpm, float *out_host6);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200MPM_H */

@@ -1,0 +1,1012 @@
+// b2_mpm.cu -- block-binned 3-D MLS-MPM (mpm3d.py:36-81 physics) over a sparse SNode grid, sm_100a.
+//
+// What this replaces in the reference: the JIT-generated struct-for bodies of a BLS MPM program
+// (bls_test_template.py:185-238 idiom): make_block_local's shared-memory pad prologue/epilogue
+// (transforms/make_block_local.cpp:97-365), the per-block dynamic particle-id lists
+// (node_dynamic.h), the per-access SNode walk with activation (lower_access.cpp:227-281) and the
+// 27x4 float atomics per particle (codegen_llvm.cpp:1495-1569).
+//
+// B200-first design:
+//  * Particles live in per-4^3-block bins: chains of 256-particle AoSoA chunks (four float4 planes
+//    {x,J} {v,C00} {C01..C11} {C12..C22} + a u32 id plane). G2P writes every particle straight
+//    into the bin of the block it now belongs to (next generation), so the particles stay
+//    block-sorted with no sort pass and no extra HBM traffic.
+//  * P2G: one CTA per occupied block.  The CTA counting-sorts each chunk by cell in shared memory,
+//    then thread (cell, i-plane) accumulates its 9 stencil nodes x {mv, m} in REGISTERS over the
+//    cell's particles -- no shared or global float atomics in the inner loop -- a gather pass sums
+//    the per-cell partials into the (4+2)^3 pad, and the pad is flushed with one 128-bit
+//    red.global.add.v4.f32 per node into the <=8 destination blocks, which are activated
+//    (lock-free CAS / atomicOr) only if a particle really touches them (x64 semantics;
+//    activate_halo=1 reproduces the CUDA-BLS epilogue).
+//  * G2P: one CTA per occupied block: pad of post-grid-op velocities staged once, particles
+//    cell-sorted so that same-cell lanes broadcast their shared-memory reads.
+//  * grid clear / grid op: struct-for over the leaf Element list, one float4 per cell, 1 KiB per
+//    block fully coalesced.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "b2_host.h"
+#include "b2_mpm.h"
+
+// ------------------------------------------------------------------------------------------
+// device helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void red_add_v4(float4 *addr, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ int ld_volatile_i32(const int *p) { return *(const volatile int *)p; }
+__device__ __forceinline__ u32 ld_volatile_u32(const u32 *p) { return *(const volatile u32 *)p; }
+
+// Container of the 4^3 block (bx,by,bz); ACT activates every level above it.  nullptr if the
+// block is outside the grid / the owned slab (+ghost layer), or (non-activating) inactive.
+template <bool ACT>
+__device__ __forceinline__ float4 *mpm_block_ptr(const MpmDev &M, int bx, int by, int bz) {
+  if ((unsigned)bx >= (unsigned)M.nb || (unsigned)by >= (unsigned)M.nb || (unsigned)bz >= (unsigned)M.nb) return nullptr;
+  int I[B2_MAX_AXES];
+#pragma unroll
+  for (int a = 0; a < B2_MAX_AXES; a++) I[a] = 0;
+  I[0] = bx * 4, I[1] = by * 4, I[2] = bz * 4;
+  int cell;
+  bool dead;
+  u8 *node = b2_walk<ACT>(M.T, M.leaf, I, &cell, &dead);
+  if (dead) return nullptr;
+  return (float4 *)node;
+}
+
+struct MpmStencil {
+  int base[3];
+  float fx[3];
+  float w[3][3];  // w[offset][axis]
+};
+__device__ __forceinline__ void mpm_stencil(const MpmDev &M, float x, float y, float z, MpmStencil &s) {
+  const float xp[3] = {x, y, z};
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    const float X = M.pot ? xp[d] * M.inv_dx : xp[d] / M.dx;  // Xp = x / dx (mpm3d.py:41)
+    s.base[d] = (int)(X - 0.5f);
+    s.fx[d] = X - (float)s.base[d];
+    s.w[0][d] = 0.5f * (1.5f - s.fx[d]) * (1.5f - s.fx[d]);
+    s.w[1][d] = 0.75f - (s.fx[d] - 1.0f) * (s.fx[d] - 1.0f);
+    s.w[2][d] = 0.5f * (s.fx[d] - 0.5f) * (s.fx[d] - 0.5f);
+  }
+}
+__device__ __forceinline__ int mpm_key(const MpmDev &M, int bx, int by, int bz) { return (bx * M.nb + by) * M.nb + bz; }
+
+__device__ __forceinline__ u8 *mpm_chunk_ptr(const MpmDev &M, int gen, u32 id1) { return M.arena[gen] + (u64)(id1 - 1) * MPM_CHUNK_BYTES; }
+
+// Appends one particle to the bin of block `key` in generation `gen`.  Must be called by all 32
+// lanes of the warp (valid = false for idle lanes): lanes that go to the same bin share one
+// atomicAdd (match_any), the lane that opens a new chunk allocates it, the others wait for it.
+__device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, bool valid, float4 p0, float4 p1, float4 p2, float4 p3, u32 id) {
+  const int lane = threadIdx.x & 31;
+  int slot = -1;
+  if (valid) {
+    slot = ld_volatile_i32(&M.slot_of[key]);
+    if (slot == -1) {
+      if (atomicCAS(&M.slot_of[key], -1, -2) == -1) {  // this lane creates the slot
+        u32 s = atomicAdd(M.nslots, 1u);
+        if (s >= (u32)M.max_slots) {
+          b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, key);
+          s = (u32)M.max_slots - 1;
+        }
+        M.slot_key[s] = key;
+        __threadfence();
+        *(volatile int *)&M.slot_of[key] = (int)s;
+        slot = (int)s;
+      }
+    }
+  }
+  __syncwarp();
+  if (valid && slot < 0) {
+    unsigned ns = 8;
+    while ((slot = ld_volatile_i32(&M.slot_of[key])) < 0) {
+      __nanosleep(ns);
+      if (ns < 256) ns *= 2;
+    }
+    __threadfence();
+  }
+  const unsigned peers = __match_any_sync(0xffffffffu, valid ? slot : -1 - lane);
+  const int leader = __ffs(peers) - 1;
+  u32 basepos = 0;
+  if (valid && lane == leader) basepos = atomicAdd(&M.count[gen][slot], (u32)__popc(peers));
+  basepos = __shfl_sync(0xffffffffu, basepos, leader);
+  u32 *cslot = nullptr;
+  u32 i = 0;
+  if (valid) {
+    const u32 pos = basepos + __popc(peers & ((1u << lane) - 1u));
+    const u32 c = pos / MPM_CHUNK;
+    i = pos % MPM_CHUNK;
+    if (c >= (u32)M.maxc) {
+      b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, key);
+      valid = false;
+    } else {
+      cslot = &M.chunk_of[gen][(u64)slot * M.maxc + c];
+      if (i == 0) {
+        u32 cid = atomicAdd(M.arena_next[gen], 1u);
+        if (cid >= M.arena_cap) {
+          b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, -1);
+          cid = M.arena_cap - 1;
+        }
+        __threadfence();
+        *(volatile u32 *)cslot = cid + 1;
+      }
+    }
+  }
+  __syncwarp();
+  if (valid) {
+    u32 id1;
+    unsigned ns = 8;
+    while ((id1 = ld_volatile_u32(cslot)) == 0) {
+      __nanosleep(ns);
+      if (ns < 256) ns *= 2;
+    }
+    u8 *ch = mpm_chunk_ptr(M, gen, id1);
+    ((float4 *)ch)[i] = p0;
+    ((float4 *)(ch + MPM_PLANE_BYTES))[i] = p1;
+    ((float4 *)(ch + 2 * MPM_PLANE_BYTES))[i] = p2;
+    ((float4 *)(ch + 3 * MPM_PLANE_BYTES))[i] = p3;
+    ((u32 *)(ch + 4 * MPM_PLANE_BYTES))[i] = id;
+  }
+}
+
+__device__ __forceinline__ int mpm_key_of_position(const MpmDev &M, float x, float y, float z, bool *ok) {
+  const float xp[3] = {x, y, z};
+  int b[3];
+  bool good = true;
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    const float X = M.pot ? xp[d] * M.inv_dx : xp[d] / M.dx;
+    int base = (int)(X - 0.5f);
+    if (!(X == X) || base < 0 || base + 2 >= M.n_grid) {  // NaN or outside the grid
+      good = false;
+      base = (X == X && base >= 0) ? M.n_grid - 3 : 0;
+    }
+    b[d] = base >> 2;
+  }
+  *ok = good;
+  return mpm_key(M, b[0], b[1], b[2]);
+}
+
+// ------------------------------------------------------------------------------------------
+// particle I/O
+// ------------------------------------------------------------------------------------------
+// x[N][3] v[N][3] C[N][3][3] J[N] (reference field layouts) -> bins of generation gen
+__global__ void __launch_bounds__(256) k_mpm_insert(MpmDev M, int gen, const float *__restrict__ x, const float *__restrict__ v,
+                                                     const float *__restrict__ C, const float *__restrict__ J, const int *__restrict__ ids,
+                                                     long long n, long long id0) {
+  const long long nround = (n + 31) / 32 * 32;
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < nround; p += (long long)gridDim.x * blockDim.x) {
+    const bool valid = p < n;
+    float4 p0 = make_float4(0, 0, 0, 1), p1 = make_float4(0, 0, 0, 0), p2 = p1, p3 = p1;
+    int key = 0;
+    u32 id = 0;
+    if (valid) {
+      p0 = make_float4(x[p * 3], x[p * 3 + 1], x[p * 3 + 2], J ? J[p] : 1.f);
+      if (v) p1.x = v[p * 3], p1.y = v[p * 3 + 1], p1.z = v[p * 3 + 2];
+      if (C) {
+        const float *c = C + p * 9;
+        p1.w = c[0];
+        p2 = make_float4(c[1], c[2], c[3], c[4]);
+        p3 = make_float4(c[5], c[6], c[7], c[8]);
+      }
+      id = ids ? (u32)ids[p] : (u32)(id0 + p);
+      bool ok;
+      key = mpm_key_of_position(M, p0.x, p0.y, p0.z, &ok);
+      if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)p);
+    }
+    mpm_insert(M, gen, key, valid, p0, p1, p2, p3, id);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_mpm_extract(MpmDev M, int gen, float *x, float *v, float *C, float *J, long long nmax) {
+  const u32 ns = *M.nslots;
+  for (u32 slot = blockIdx.x; slot < ns; slot += gridDim.x) {
+    const u32 cnt = M.count[gen][slot];
+    for (u32 q = threadIdx.x; q < cnt; q += blockDim.x) {
+      const u32 id1 = M.chunk_of[gen][(u64)slot * M.maxc + q / MPM_CHUNK];
+      const u8 *ch = mpm_chunk_ptr(M, gen, id1);
+      const u32 i = q % MPM_CHUNK;
+      const u32 id = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[i];
+      if ((long long)id >= nmax) continue;
+      const float4 p0 = ((const float4 *)ch)[i];
+      const float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[i];
+      const float4 p2 = ((const float4 *)(ch + 2 * MPM_PLANE_BYTES))[i];
+      const float4 p3 = ((const float4 *)(ch + 3 * MPM_PLANE_BYTES))[i];
+      if (x) x[(u64)id * 3] = p0.x, x[(u64)id * 3 + 1] = p0.y, x[(u64)id * 3 + 2] = p0.z;
+      if (J) J[id] = p0.w;
+      if (v) v[(u64)id * 3] = p1.x, v[(u64)id * 3 + 1] = p1.y, v[(u64)id * 3 + 2] = p1.z;
+      if (C) {
+        float *c = C + (u64)id * 9;
+        c[0] = p1.w, c[1] = p2.x, c[2] = p2.y, c[3] = p2.z, c[4] = p2.w, c[5] = p3.x, c[6] = p3.y, c[7] = p3.z, c[8] = p3.w;
+      }
+    }
+  }
+}
+
+// stats[0] particles, [1] slots, [2] occupied slots, [3] chunks in use
+__global__ void k_mpm_stats(MpmDev M, int gen) {
+  const u32 ns = *M.nslots;
+  unsigned long long np = 0, occ = 0;
+  for (u32 s = blockIdx.x * blockDim.x + threadIdx.x; s < ns; s += gridDim.x * blockDim.x) {
+    u32 c = M.count[gen][s];
+    np += c;
+    occ += c > 0;
+  }
+  for (int d = 16; d > 0; d >>= 1) {
+    np += __shfl_down_sync(0xffffffffu, np, d);
+    occ += __shfl_down_sync(0xffffffffu, occ, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(&M.stats[0], (double)np);
+    atomicAdd(&M.stats[2], (double)occ);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    M.stats[1] = (double)ns;
+    M.stats[3] = (double)*M.arena_next[gen];
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// grid kernels: struct-for over the leaf Element list (one Element = one 4^3 block = 1 KiB)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_mpm_clear(B2TreeDev *T, int leaf) {
+  B2CList *L = T->lists[leaf];
+  const u32 ne = L->count;
+  const int sub = threadIdx.x >> 6, t = threadIdx.x & 63;
+  for (u32 e = blockIdx.x * 4 + sub; e < ne; e += gridDim.x * 4) {
+    const B2Element *E = (const B2Element *)b2_list_get(L, e);
+    float4 *blk = (float4 *)E->node;
+    blk[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+// mpm3d.py:56-61: v /= m (m > 0); v.y -= dt*g; walls
+__global__ void __launch_bounds__(256) k_mpm_gridop(MpmDev M) {
+  B2CList *L = M.T->lists[M.leaf_sid];
+  const u32 ne = L->count;
+  const int sub = threadIdx.x >> 6, t = threadIdx.x & 63;
+  for (u32 e = blockIdx.x * 4 + sub; e < ne; e += gridDim.x * 4) {
+    const B2Element *E = (const B2Element *)b2_list_get(L, e);
+    float4 *blk = (float4 *)E->node;
+    const int I[3] = {E->pcoord[0] * 4 + (t >> 4), E->pcoord[1] * 4 + ((t >> 2) & 3), E->pcoord[2] * 4 + (t & 3)};
+    float4 g = blk[t];
+    float vv[3] = {g.x, g.y, g.z};
+    if (g.w > 0.f) {
+      vv[0] /= g.w;
+      vv[1] /= g.w;
+      vv[2] /= g.w;
+    }
+    vv[1] -= M.dt * M.gravity;
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+      const bool cond = (I[d] < M.bound && vv[d] < 0.f) || (I[d] > M.n_grid - M.bound && vv[d] > 0.f);
+      if (cond) vv[d] = 0.f;
+    }
+    blk[t] = make_float4(vv[0], vv[1], vv[2], g.w);
+  }
+}
+
+// grid -> dense [n][n][n][4] image
+__global__ void __launch_bounds__(256) k_mpm_grid_to_dense(MpmDev M, float4 *out) {
+  B2CList *L = M.T->lists[M.leaf_sid];
+  const u32 ne = L->count;
+  const int sub = threadIdx.x >> 6, t = threadIdx.x & 63;
+  for (u32 e = blockIdx.x * 4 + sub; e < ne; e += gridDim.x * 4) {
+    const B2Element *E = (const B2Element *)b2_list_get(L, e);
+    const float4 *blk = (const float4 *)E->node;
+    const long long i = E->pcoord[0] * 4 + (t >> 4), j = E->pcoord[1] * 4 + ((t >> 2) & 3), k = E->pcoord[2] * 4 + (t & 3);
+    out[(i * M.n_grid + j) * M.n_grid + k] = blk[t];
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// P2G, block-local: registers -> per-cell partials -> pad -> one vector red per node
+// ------------------------------------------------------------------------------------------
+#define P2G_THREADS 192
+__global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
+  // staging of one chunk (sorted by cell): 3 shared float4 planes + 3 plane-specific float4 per
+  // particle = 24 KiB; aliased by the per-cell partial sums R[64][27] (27 KiB) afterwards
+  __shared__ float4 sBuf[64 * 27];
+  __shared__ float4 sPad[216];
+  __shared__ int sHist[64];
+  __shared__ int sStart[65];
+  __shared__ unsigned short sCell[MPM_CHUNK];
+  __shared__ unsigned short sRank[MPM_CHUNK];
+  __shared__ u32 sTouched;
+  __shared__ int sSlot;
+  __shared__ float4 *sNb[8];
+  float4 *sSh = sBuf;            // [3][256]
+  float4 *sSp = sBuf + 3 * 256;  // [256][3]
+
+  const int tid = threadIdx.x;
+  const int cell = tid / 3, plane = tid - cell * 3;
+  const u32 nslots = *M.nslots;
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[0], 1u);
+    __syncthreads();
+    const u32 slot = (u32)sSlot;
+    if (slot >= nslots) break;
+    const u32 total = M.count[gen][slot];
+    if (total == 0) continue;
+    const int key = M.slot_key[slot];
+    const int bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
+    if (tid == 0) sTouched = M.activate_halo ? 0xffu : 1u;
+
+    float4 acc[9];
+#pragma unroll
+    for (int q = 0; q < 9; q++) acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+    const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
+    for (u32 c = 0; c < nchunks; c++) {
+      const u8 *ch = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + c]);
+      const int n = (int)min((u32)MPM_CHUNK, total - c * MPM_CHUNK);
+      if (tid < 64) sHist[tid] = 0;
+      __syncthreads();
+      // pass 1: cell of every particle + its rank inside the cell
+      u32 tmask = 0;
+      for (int t = tid; t < n; t += P2G_THREADS) {
+        const float4 p0 = ((const float4 *)ch)[t];
+        const float xp[3] = {p0.x, p0.y, p0.z};
+        int l[3];
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+          const float X = M.pot ? xp[d] * M.inv_dx : xp[d] / M.dx;
+          l[d] = ((int)(X - 0.5f)) & 3;
+        }
+        const int cidx = (l[0] << 4) | (l[1] << 2) | l[2];
+        sCell[t] = (unsigned short)cidx;
+        sRank[t] = (unsigned short)atomicAdd(&sHist[cidx], 1);
+        const int h = ((l[0] >> 1) << 2) | ((l[1] >> 1) << 1) | (l[2] >> 1);
+#pragma unroll
+        for (int nbh = 0; nbh < 8; nbh++)
+          if ((nbh & ~h) == 0) tmask |= 1u << nbh;
+      }
+      tmask = __reduce_or_sync(0xffffffffu, tmask);
+      if ((tid & 31) == 0 && tmask) atomicOr(&sTouched, tmask);
+      __syncthreads();
+      // exclusive scan of the 64 cell counts (warps 0 and 1)
+      if (tid < 64) {
+        const int lane = tid & 31;
+        const int vcnt = sHist[tid];
+        int inc = vcnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int tv = __shfl_up_sync(0xffffffffu, inc, d);
+          if (lane >= d) inc += tv;
+        }
+        sStart[tid + 1] = inc;  // per-warp inclusive; fixed up below
+      }
+      __syncthreads();
+      if (tid >= 32 && tid < 64) sStart[tid + 1] += sStart[32];
+      if (tid == 0) sStart[0] = 0;
+      __syncthreads();
+      // pass 2: per-particle constants, written at the cell-sorted position
+      for (int t = tid; t < n; t += P2G_THREADS) {
+        const float4 p0 = ((const float4 *)ch)[t];
+        const float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[t];
+        const float4 p2 = ((const float4 *)(ch + 2 * MPM_PLANE_BYTES))[t];
+        const float4 p3 = ((const float4 *)(ch + 3 * MPM_PLANE_BYTES))[t];
+        MpmStencil s;
+        mpm_stencil(M, p0.x, p0.y, p0.z, s);
+        const float stress = M.stress_k * (p0.w - 1.0f);
+        // A' = (stress I + m C) dx ; b = m v - A' fx ; V_i = b + i A'[:,0]
+        const float m = M.p_mass;
+        const float A00 = (stress + m * p1.w) * M.dx, A01 = m * p2.x * M.dx, A02 = m * p2.y * M.dx;
+        const float A10 = m * p2.z * M.dx, A11 = (stress + m * p2.w) * M.dx, A12 = m * p3.x * M.dx;
+        const float A20 = m * p3.y * M.dx, A21 = m * p3.z * M.dx, A22 = (stress + m * p3.w) * M.dx;
+        const float b0 = m * p1.x - (A00 * s.fx[0] + A01 * s.fx[1] + A02 * s.fx[2]);
+        const float b1 = m * p1.y - (A10 * s.fx[0] + A11 * s.fx[1] + A12 * s.fx[2]);
+        const float b2 = m * p1.z - (A20 * s.fx[0] + A21 * s.fx[1] + A22 * s.fx[2]);
+        const int q = sStart[sCell[t]] + sRank[t];
+        sSh[q] = make_float4(s.w[0][1], s.w[1][1], s.w[2][1], s.w[0][2]);
+        sSh[256 + q] = make_float4(s.w[1][2], s.w[2][2], A01, A11);
+        sSh[512 + q] = make_float4(A21, A02, A12, A22);
+        sSp[q * 3 + 0] = make_float4(s.w[0][0], b0, b1, b2);
+        sSp[q * 3 + 1] = make_float4(s.w[1][0], b0 + A00, b1 + A10, b2 + A20);
+        sSp[q * 3 + 2] = make_float4(s.w[2][0], b0 + 2.f * A00, b1 + 2.f * A10, b2 + 2.f * A20);
+      }
+      __syncthreads();
+      // stage 1: thread (cell, plane i) accumulates its 9 nodes over the cell's particles
+      {
+        const int q1 = sStart[cell + 1];
+        for (int q = sStart[cell]; q < q1; q++) {
+          const float4 h0 = sSh[q], h1 = sSh[256 + q], h2 = sSh[512 + q];
+          const float4 pl = sSp[q * 3 + plane];
+          const float wy[3] = {h0.x, h0.y, h0.z};
+          const float wz[3] = {h0.w, h1.x, h1.y};
+          float r0 = pl.y, r1 = pl.z, r2 = pl.w;  // value at (i, j, k=0), walks along j
+#pragma unroll
+          for (int j = 0; j < 3; j++) {
+            const float wxy = pl.x * wy[j];
+            float c0 = r0, c1 = r1, c2 = r2;  // walks along k
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+              const float w = wxy * wz[k];
+              float4 &a = acc[j * 3 + k];
+              a.x = fmaf(w, c0, a.x);
+              a.y = fmaf(w, c1, a.y);
+              a.z = fmaf(w, c2, a.z);
+              a.w += w;
+              c0 += h2.y, c1 += h2.z, c2 += h2.w;  // + A'[:,2]
+            }
+            r0 += h1.z, r1 += h1.w, r2 += h2.x;  // + A'[:,1]
+          }
+        }
+      }
+      __syncthreads();  // staging is overwritten by the next chunk / by R
+    }
+    // per-cell partials -> shared
+#pragma unroll
+    for (int q = 0; q < 9; q++) {
+      float4 a = acc[q];
+      a.w *= M.p_mass;
+      sBuf[cell * 27 + plane * 9 + q] = a;
+    }
+    // destination blocks (activated only if touched)
+    if (tid < 8) {
+      float4 *p = nullptr;
+      if ((sTouched >> tid) & 1u) p = mpm_block_ptr<true>(M, bx + (tid >> 2), by + ((tid >> 1) & 1), bz + (tid & 1));
+      sNb[tid] = p;
+    }
+    __syncthreads();
+    // stage 2: pad node = sum of the partials of the <=27 cells whose stencil covers it; flush
+    for (int nidx = tid; nidx < 216; nidx += P2G_THREADS) {
+      const int px = nidx / 36, py = (nidx / 6) % 6, pz = nidx % 6;
+      float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        const int cx = px - i;
+        if ((unsigned)cx > 3u) continue;
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+          const int cy = py - j;
+          if ((unsigned)cy > 3u) continue;
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+            const int cz = pz - k;
+            if ((unsigned)cz > 3u) continue;
+            const float4 r = sBuf[((cx << 4) | (cy << 2) | cz) * 27 + i * 9 + j * 3 + k];
+            s4.x += r.x, s4.y += r.y, s4.z += r.z, s4.w += r.w;
+          }
+        }
+      }
+      float4 *dst = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
+      if (dst && (s4.x != 0.f || s4.y != 0.f || s4.z != 0.f || s4.w != 0.f)) red_add_v4(dst + (((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)), s4);
+    }
+  }
+}
+
+// Plain path (ti.block_local off): every particle walks the SNode tree with activation and issues
+// one vector red per node -- the reference's non-BLS access pattern (K15) on the binned particles.
+__global__ void __launch_bounds__(256) k_mpm_p2g_plain(MpmDev M, int gen) {
+  const u32 nslots = *M.nslots;
+  for (u32 slot = blockIdx.x; slot < nslots; slot += gridDim.x) {
+    const u32 total = M.count[gen][slot];
+    for (u32 q = threadIdx.x; q < total; q += blockDim.x) {
+      const u8 *ch = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + q / MPM_CHUNK]);
+      const u32 t = q % MPM_CHUNK;
+      const float4 p0 = ((const float4 *)ch)[t];
+      const float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[t];
+      const float4 p2 = ((const float4 *)(ch + 2 * MPM_PLANE_BYTES))[t];
+      const float4 p3 = ((const float4 *)(ch + 3 * MPM_PLANE_BYTES))[t];
+      MpmStencil s;
+      mpm_stencil(M, p0.x, p0.y, p0.z, s);
+      const float stress = M.stress_k * (p0.w - 1.0f);
+      const float m = M.p_mass;
+      const float A[3][3] = {{stress + m * p1.w, m * p2.x, m * p2.y}, {m * p2.z, stress + m * p2.w, m * p3.x}, {m * p3.y, m * p3.z, stress + m * p3.w}};
+      const float vp[3] = {p1.x, p1.y, p1.z};
+      for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++)
+          for (int k = 0; k < 3; k++) {
+            const float dpos[3] = {((float)i - s.fx[0]) * M.dx, ((float)j - s.fx[1]) * M.dx, ((float)k - s.fx[2]) * M.dx};
+            const float w = s.w[i][0] * s.w[j][1] * s.w[k][2];
+            const int gx = s.base[0] + i, gy = s.base[1] + j, gz = s.base[2] + k;
+            float4 *blk = mpm_block_ptr<true>(M, gx >> 2, gy >> 2, gz >> 2);
+            if (!blk) continue;
+            float4 val;
+            val.x = w * (m * vp[0] + (A[0][0] * dpos[0] + A[0][1] * dpos[1] + A[0][2] * dpos[2]));
+            val.y = w * (m * vp[1] + (A[1][0] * dpos[0] + A[1][1] * dpos[1] + A[1][2] * dpos[2]));
+            val.z = w * (m * vp[2] + (A[2][0] * dpos[0] + A[2][1] * dpos[1] + A[2][2] * dpos[2]));
+            val.w = w * m;
+            red_add_v4(blk + (((gx & 3) << 4) | ((gy & 3) << 2) | (gz & 3)), val);
+          }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// G2P + re-binning
+// ------------------------------------------------------------------------------------------
+#define G2P_THREADS 256
+template <bool BLS>
+__global__ void __launch_bounds__(G2P_THREADS, 3) k_mpm_g2p(MpmDev M, int gen) {
+  __shared__ float4 sPad[216];
+  __shared__ float4 sP0[MPM_CHUNK];
+  __shared__ u32 sId[MPM_CHUNK];
+  __shared__ int sHist[64];
+  __shared__ int sStart[65];
+  __shared__ int sSlot;
+  __shared__ float4 *sNb[8];
+  const int tid = threadIdx.x;
+  const u32 nslots = *M.nslots;
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[1], 1u);
+    __syncthreads();
+    const u32 slot = (u32)sSlot;
+    if (slot >= nslots) break;
+    const u32 total = M.count[gen][slot];
+    if (total == 0) continue;
+    const int key = M.slot_key[slot];
+    const int bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
+    if (BLS) {
+      if (tid < 8) sNb[tid] = mpm_block_ptr<false>(M, bx + (tid >> 2), by + ((tid >> 1) & 1), bz + (tid & 1));
+      __syncthreads();
+      if (tid < 216) {
+        const int px = tid / 36, py = (tid / 6) % 6, pz = tid % 6;
+        const float4 *src = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
+        sPad[tid] = src ? src[((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)] : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
+    for (u32 c = 0; c < nchunks; c++) {
+      const u8 *ch = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + c]);
+      const int n = (int)min((u32)MPM_CHUNK, total - c * MPM_CHUNK);
+      if (tid < 64) sHist[tid] = 0;
+      __syncthreads();
+      float4 p0 = make_float4(0.f, 0.f, 0.f, 1.f);
+      u32 id = 0;
+      int cidx = 0, rank = 0;
+      if (tid < n) {
+        p0 = ((const float4 *)ch)[tid];
+        id = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[tid];
+        const float xp[3] = {p0.x, p0.y, p0.z};
+        int l[3];
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+          const float X = M.pot ? xp[d] * M.inv_dx : xp[d] / M.dx;
+          l[d] = ((int)(X - 0.5f)) & 3;
+        }
+        cidx = (l[0] << 4) | (l[1] << 2) | l[2];
+        rank = atomicAdd(&sHist[cidx], 1);
+      }
+      __syncthreads();
+      if (tid < 64) {
+        const int lane = tid & 31;
+        int inc = sHist[tid];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int tv = __shfl_up_sync(0xffffffffu, inc, d);
+          if (lane >= d) inc += tv;
+        }
+        sStart[tid + 1] = inc;
+      }
+      __syncthreads();
+      if (tid >= 32 && tid < 64) sStart[tid + 1] += sStart[32];
+      if (tid == 0) sStart[0] = 0;
+      __syncthreads();
+      if (tid < n) {
+        const int q = sStart[cidx] + rank;
+        sP0[q] = p0;
+        sId[q] = id;
+      }
+      __syncthreads();
+      const bool valid = tid < n;
+      float4 o0 = make_float4(0.f, 0.f, 0.f, 1.f), o1 = make_float4(0.f, 0.f, 0.f, 0.f), o2 = o1, o3 = o1;
+      int nkey = 0;
+      if (valid) {
+        p0 = sP0[tid];
+        id = sId[tid];
+        MpmStencil s;
+        mpm_stencil(M, p0.x, p0.y, p0.z, s);
+        float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+        float Sx0 = 0.f, Sx1 = 0.f, Sx2 = 0.f, Sy0 = 0.f, Sy1 = 0.f, Sy2 = 0.f, Sz0 = 0.f, Sz1 = 0.f, Sz2 = 0.f;
+        const int l0 = s.base[0] & 3, l1 = s.base[1] & 3, l2 = s.base[2] & 3;
+        const float wz0 = s.w[0][2], wz1 = s.w[1][2], wz2 = s.w[2][2];
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+#pragma unroll
+          for (int j = 0; j < 3; j++) {
+            const float wxy = s.w[i][0] * s.w[j][1];
+            float4 g0, g1, g2;
+            if (BLS) {
+              const int pidx = ((l0 + i) * 6 + (l1 + j)) * 6 + l2;
+              g0 = sPad[pidx], g1 = sPad[pidx + 1], g2 = sPad[pidx + 2];
+            } else {
+              float4 g[3];
+#pragma unroll
+              for (int k = 0; k < 3; k++) {
+                const int gx = s.base[0] + i, gy = s.base[1] + j, gz = s.base[2] + k;
+                const float4 *blk = mpm_block_ptr<false>(M, gx >> 2, gy >> 2, gz >> 2);
+                g[k] = blk ? blk[((gx & 3) << 4) | ((gy & 3) << 2) | (gz & 3)] : make_float4(0.f, 0.f, 0.f, 0.f);
+              }
+              g0 = g[0], g1 = g[1], g2 = g[2];
+            }
+            // row = sum_k wz_k g_k ; rz = sum_k k wz_k g_k
+            const float t1x = wz1 * g1.x, t1y = wz1 * g1.y, t1z = wz1 * g1.z;
+            const float t2x = wz2 * g2.x, t2y = wz2 * g2.y, t2z = wz2 * g2.z;
+            const float rx = fmaf(wz0, g0.x, t1x + t2x), ry = fmaf(wz0, g0.y, t1y + t2y), rzv = fmaf(wz0, g0.z, t1z + t2z);
+            const float zx = fmaf(2.f, t2x, t1x), zy = fmaf(2.f, t2y, t1y), zz = fmaf(2.f, t2z, t1z);
+            v0 = fmaf(wxy, rx, v0), v1 = fmaf(wxy, ry, v1), v2 = fmaf(wxy, rzv, v2);
+            Sz0 = fmaf(wxy, zx, Sz0), Sz1 = fmaf(wxy, zy, Sz1), Sz2 = fmaf(wxy, zz, Sz2);
+            if (j > 0) {
+              const float wj = (float)j * wxy;
+              Sy0 = fmaf(wj, rx, Sy0), Sy1 = fmaf(wj, ry, Sy1), Sy2 = fmaf(wj, rzv, Sy2);
+            }
+            if (i > 0) {
+              const float wi = (float)i * wxy;
+              Sx0 = fmaf(wi, rx, Sx0), Sx1 = fmaf(wi, ry, Sx1), Sx2 = fmaf(wi, rzv, Sx2);
+            }
+          }
+        }
+        // C[a][b] = 4/dx * (sum w g_a o_b - fx_b v_a)   (mpm3d.py:75 with dpos = (o - fx) dx)
+        const float k4 = 4.0f * M.inv_dx;
+        const float C00 = k4 * (Sx0 - s.fx[0] * v0), C01 = k4 * (Sy0 - s.fx[1] * v0), C02 = k4 * (Sz0 - s.fx[2] * v0);
+        const float C10 = k4 * (Sx1 - s.fx[0] * v1), C11 = k4 * (Sy1 - s.fx[1] * v1), C12 = k4 * (Sz1 - s.fx[2] * v1);
+        const float C20 = k4 * (Sx2 - s.fx[0] * v2), C21 = k4 * (Sy2 - s.fx[1] * v2), C22 = k4 * (Sz2 - s.fx[2] * v2);
+        const float nx = p0.x + M.dt * v0, ny = p0.y + M.dt * v1, nz = p0.z + M.dt * v2;
+        const float nJ = p0.w * (1.0f + M.dt * (C00 + C11 + C22));
+        o0 = make_float4(nx, ny, nz, nJ);
+        o1 = make_float4(v0, v1, v2, C00);
+        o2 = make_float4(C01, C02, C10, C11);
+        o3 = make_float4(C12, C20, C21, C22);
+        bool ok;
+        nkey = mpm_key_of_position(M, nx, ny, nz, &ok);
+        if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)id);
+      }
+      mpm_insert(M, gen ^ 1, nkey, valid, o0, o1, o2, o3, id);
+      __syncthreads();
+    }
+    // this generation's bin is consumed: leave it empty for the generation after next
+    if (tid < (int)nchunks) M.chunk_of[gen][(u64)slot * M.maxc + tid] = 0;
+    for (int t = tid + G2P_THREADS; t < (int)nchunks; t += G2P_THREADS) M.chunk_of[gen][(u64)slot * M.maxc + t] = 0;
+    if (tid == 0) M.count[gen][slot] = 0;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+struct B2Mpm_t {
+  TiRuntime_t *rt;
+  B2MpmParams prm;
+  B2Tree_t *tree = nullptr;
+  MpmDev M;
+  int gen = 0;
+  int64_t n_particles = 0;
+  bool lists_valid = false;
+  bool sparse = false;
+  bool profiling = false;
+  cudaEvent_t ev[8];
+  float phase_ms[6] = {0, 0, 0, 0, 0, 0};
+  std::vector<void *> allocs;
+
+  template <typename T>
+  T *dalloc(size_t count, int fill = 0) {
+    void *p = nullptr;
+    B2_CUDA(cudaMalloc(&p, std::max<size_t>(count * sizeof(T), 16)));
+    B2_CUDA(cudaMemsetAsync(p, fill, std::max<size_t>(count * sizeof(T), 16), rt->stream()));
+    allocs.push_back(p);
+    return (T *)p;
+  }
+  B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p);
+  ~B2Mpm_t();
+  void reset_bins();
+  void ensure_lists();
+  void clear_grid();
+  void p2g();
+  void grid_op();
+  void g2p();
+  void substep(int n);
+};
+
+static void add_axes3(B2SNodeDesc &d, int size) {
+  d.num_axes = 3;
+  for (int a = 0; a < 3; a++) d.axes[a] = a, d.sizes[a] = size;
+}
+
+B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
+  if (p.n_grid < 8 || p.n_grid % 4) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "n_grid must be a multiple of 4, >= 8");
+  if (p.layout < 0 || p.layout > 2) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "layout");
+  if (p.layout > 0 && p.n_grid % 32) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "sparse layouts need n_grid % 32 == 0");
+  if (p.max_particles <= 0) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "max_particles");
+  const int nb = p.n_grid / 4;
+  // grid SNode tree; leaf cell = {vx, vy, vz, m}
+  std::vector<B2SNodeDesc> d;
+  auto node = [&](int type, int parent) {
+    B2SNodeDesc x;
+    memset(&x, 0, sizeof(x));
+    x.type = type;
+    x.parent = parent;
+    d.push_back(x);
+    return (int)d.size() - 1;
+  };
+  node(B2_ROOT, -1);
+  int leaf;
+  if (p.layout == 0) {
+    int a = node(B2_DENSE, 0);
+    add_axes3(d[a], nb);
+    leaf = node(B2_DENSE, a);
+  } else {
+    int a = node(B2_POINTER, 0);
+    add_axes3(d[a], nb / 8);
+    int b = node(p.layout == 1 ? B2_BITMASKED : B2_POINTER, a);
+    add_axes3(d[b], 8);
+    leaf = node(B2_DENSE, b);
+  }
+  add_axes3(d[leaf], 4);
+  for (int k = 0; k < 4; k++) {
+    int pl = node(B2_PLACE, leaf);
+    d[pl].dtype_bytes = 4;
+  }
+  sparse = p.layout != 0;
+  tree = new B2Tree_t(rt, d.data(), (int)d.size());
+  if (tree->s[leaf].cell_size != 16 || tree->s[leaf].node_size != 1024)
+    throw B2Error(TI_ERROR_INVALID_STATE, "leaf block must be 64 x float4");
+
+  memset(&M, 0, sizeof(M));
+  M.n_grid = p.n_grid;
+  M.nb = nb;
+  M.pot = (p.n_grid & (p.n_grid - 1)) == 0;
+  M.dx = 1.0f / (float)p.n_grid;
+  M.inv_dx = (float)p.n_grid;
+  M.dt = p.dt;
+  M.p_vol = (M.dx * 0.5f) * (M.dx * 0.5f);
+  M.p_mass = M.p_vol * p.p_rho;
+  M.E = p.E;
+  M.gravity = p.gravity;
+  M.stress_k = -p.dt * 4.0f * p.E * M.p_vol / (M.dx * M.dx);
+  M.bound = p.bound;
+  M.activate_halo = p.bls_activate_halo;
+  M.slab_lo = p.slab_lo;
+  M.slab_hi = p.slab_hi > 0 ? p.slab_hi : nb;
+  M.T = tree->dev;
+  M.leaf = tree->path_to(leaf);
+  M.leaf_sid = leaf;
+  const int64_t nblocks = (int64_t)nb * nb * nb;
+  M.max_slots = (int)std::min<int64_t>(nblocks, std::max<int64_t>(4096, p.max_particles / 16));
+  M.maxc = 32;
+  M.arena_cap = (u32)((p.max_particles + MPM_CHUNK - 1) / MPM_CHUNK + M.max_slots + 64);
+  M.slot_of = dalloc<int>(nblocks, 0xFF);
+  M.slot_key = dalloc<int>(M.max_slots);
+  M.nslots = dalloc<u32>(4);
+  for (int g = 0; g < 2; g++) {
+    M.count[g] = dalloc<u32>(M.max_slots);
+    M.chunk_of[g] = dalloc<u32>((size_t)M.max_slots * M.maxc);
+    void *a = nullptr;
+    B2_CUDA(cudaMalloc(&a, (size_t)M.arena_cap * MPM_CHUNK_BYTES));
+    allocs.push_back(a);
+    M.arena[g] = (u8 *)a;
+    M.arena_next[g] = dalloc<u32>(4);
+  }
+  M.work_counter = dalloc<u32>(8);
+  M.stats = dalloc<double>(8);
+  for (auto &e : ev) B2_CUDA(cudaEventCreate(&e));
+  rt->sync();
+}
+B2Mpm_t::~B2Mpm_t() {
+  cudaStreamSynchronize(rt->stream());
+  for (void *p : allocs) cudaFree(p);
+  for (auto &e : ev) cudaEventDestroy(e);
+  delete tree;
+}
+void B2Mpm_t::reset_bins() {
+  cudaStream_t st = rt->stream();
+  const int64_t nblocks = (int64_t)M.nb * M.nb * M.nb;
+  B2_CUDA(cudaMemsetAsync(M.slot_of, 0xFF, nblocks * 4, st));
+  B2_CUDA(cudaMemsetAsync(M.nslots, 0, 16, st));
+  for (int g = 0; g < 2; g++) {
+    B2_CUDA(cudaMemsetAsync(M.count[g], 0, (size_t)M.max_slots * 4, st));
+    B2_CUDA(cudaMemsetAsync(M.chunk_of[g], 0, (size_t)M.max_slots * M.maxc * 4, st));
+    B2_CUDA(cudaMemsetAsync(M.arena_next[g], 0, 16, st));
+  }
+  gen = 0;
+  n_particles = 0;
+}
+void B2Mpm_t::ensure_lists() {
+  if (!lists_valid) {
+    tree->listgen_async(M.leaf_sid);
+    lists_valid = true;
+  }
+}
+void B2Mpm_t::clear_grid() {
+  ensure_lists();
+  k_mpm_clear<<<rt->num_sms * 8, 256, 0, rt->stream()>>>(tree->dev, M.leaf_sid);
+  rt->count_launch();
+}
+void B2Mpm_t::p2g() {
+  cudaStream_t st = rt->stream();
+  B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
+  if (prm.block_local)
+    k_mpm_p2g<<<rt->num_sms * 4, P2G_THREADS, 0, st>>>(M, gen);
+  else
+    k_mpm_p2g_plain<<<rt->num_sms * 8, 256, 0, st>>>(M, gen);
+  rt->count_launch();
+  if (sparse) lists_valid = false;  // P2G may have activated blocks
+}
+void B2Mpm_t::grid_op() {
+  ensure_lists();
+  k_mpm_gridop<<<rt->num_sms * 8, 256, 0, rt->stream()>>>(M);
+  rt->count_launch();
+}
+void B2Mpm_t::g2p() {
+  cudaStream_t st = rt->stream();
+  // the generation being written starts with an empty chunk arena
+  B2_CUDA(cudaMemsetAsync(M.arena_next[gen ^ 1], 0, 16, st));
+  B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
+  if (prm.block_local)
+    k_mpm_g2p<true><<<rt->num_sms * 3, G2P_THREADS, 0, st>>>(M, gen);
+  else
+    k_mpm_g2p<false><<<rt->num_sms * 3, G2P_THREADS, 0, st>>>(M, gen);
+  rt->count_launch();
+  gen ^= 1;
+}
+void B2Mpm_t::substep(int n) {
+  cudaStream_t st = rt->stream();
+  for (int s = 0; s < n; s++) {
+    const bool prof = profiling && s == n - 1;
+    if (prof) B2_CUDA(cudaEventRecord(ev[0], st));
+    clear_grid();
+    if (prof) B2_CUDA(cudaEventRecord(ev[1], st));
+    p2g();
+    if (prof) B2_CUDA(cudaEventRecord(ev[2], st));
+    ensure_lists();
+    if (prof) B2_CUDA(cudaEventRecord(ev[3], st));
+    grid_op();
+    if (prof) B2_CUDA(cudaEventRecord(ev[4], st));
+    g2p();
+    if (prof) {
+      B2_CUDA(cudaEventRecord(ev[5], st));
+      B2_CUDA(cudaEventSynchronize(ev[5]));
+      float ms[5];
+      for (int k = 0; k < 5; k++) B2_CUDA(cudaEventElapsedTime(&ms[k], ev[k], ev[k + 1]));
+      phase_ms[0] = ms[0], phase_ms[1] = ms[1], phase_ms[2] = ms[2], phase_ms[3] = ms[3], phase_ms[4] = ms[4], phase_ms[5] = 0.f;
+    }
+  }
+  B2_CUDA(cudaGetLastError());
+}
+
+static void require(bool ok, TiError code, const char *msg) {
+  if (!ok) throw B2Error(code, msg);
+}
+
+extern "C" {
+B2Mpm b2_mpm_create(TiRuntime runtime, const B2MpmParams *params) {
+  B2_API_BEGIN
+  require(runtime != nullptr, TI_ERROR_ARGUMENT_NULL, "runtime");
+  require(params != nullptr, TI_ERROR_ARGUMENT_NULL, "params");
+  B2_CUDA(cudaSetDevice(runtime->device));
+  return new B2Mpm_t(runtime, *params);
+  B2_API_END(nullptr)
+}
+void b2_mpm_destroy(B2Mpm mpm) { delete mpm; }
+B2Tree b2_mpm_tree(B2Mpm mpm) { return mpm ? mpm->tree : nullptr; }
+int32_t b2_mpm_leaf_snode(B2Mpm mpm) { return mpm ? mpm->M.leaf_sid : -1; }
+
+int32_t b2_mpm_add_particles(B2Mpm m, int64_t n, const float *x, const float *v, const float *C, const float *J, const int32_t *ids) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  if (n <= 0) return 0;
+  require(x != nullptr, TI_ERROR_ARGUMENT_NULL, "x");
+  require(m->n_particles + n <= m->prm.max_particles, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "more particles than max_particles");
+  cudaStream_t st = m->rt->stream();
+  B2Staged sx, sv, sc, sj, si;
+  sx.init(x, (size_t)n * 12, true, false, st);
+  if (v) sv.init(v, (size_t)n * 12, true, false, st);
+  if (C) sc.init(C, (size_t)n * 36, true, false, st);
+  if (J) sj.init(J, (size_t)n * 4, true, false, st);
+  if (ids) si.init(ids, (size_t)n * 4, true, false, st);
+  k_mpm_insert<<<m->rt->grid_for(n, 256, 8), 256, 0, st>>>(m->M, m->gen, sx.as<float>(), sv.as<float>(), sc.as<float>(), sj.as<float>(), si.as<int>(), n, m->n_particles);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  m->n_particles += n;
+  sx.finish(), sv.finish(), sc.finish(), sj.finish(), si.finish();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_set_particles(B2Mpm m, int64_t n, const float *x, const float *v, const float *C, const float *J) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  m->reset_bins();
+  B2_API_END(-1)
+  return b2_mpm_add_particles(m, n, x, v, C, J, nullptr);
+}
+int64_t b2_mpm_num_particles(B2Mpm m) { return m ? m->n_particles : -1; }
+int32_t b2_mpm_get_particles(B2Mpm m, float *x, float *v, float *C, float *J) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  const int64_t n = m->n_particles;
+  if (n == 0) return 0;
+  cudaStream_t st = m->rt->stream();
+  B2Staged sx, sv, sc, sj;
+  if (x) sx.init(x, (size_t)n * 12, false, true, st);
+  if (v) sv.init(v, (size_t)n * 12, false, true, st);
+  if (C) sc.init(C, (size_t)n * 36, false, true, st);
+  if (J) sj.init(J, (size_t)n * 4, false, true, st);
+  k_mpm_extract<<<m->rt->num_sms * 8, 256, 0, st>>>(m->M, m->gen, sx.as<float>(), sv.as<float>(), sc.as<float>(), sj.as<float>(), n);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  sx.finish(), sv.finish(), sc.finish(), sj.finish();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_substep(B2Mpm m, int32_t nsteps) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  m->substep(nsteps);
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_clear_grid(B2Mpm m) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  m->clear_grid();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_p2g(B2Mpm m) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  m->p2g();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_grid_op(B2Mpm m) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  m->grid_op();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_g2p(B2Mpm m) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  m->g2p();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_grid_to_dense(B2Mpm m, float *out) {
+  B2_API_BEGIN
+  require(m != nullptr && out != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm/out");
+  cudaStream_t st = m->rt->stream();
+  const size_t bytes = (size_t)m->M.n_grid * m->M.n_grid * m->M.n_grid * 16;
+  B2Staged o;
+  o.init(out, bytes, false, true, st);
+  if (!o.owned) B2_CUDA(cudaMemsetAsync(o.dev, 0, bytes, st));
+  m->ensure_lists();
+  k_mpm_grid_to_dense<<<m->rt->num_sms * 8, 256, 0, st>>>(m->M, o.as<float4>());
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  o.finish();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_stats(B2Mpm m, double *out) {
+  B2_API_BEGIN
+  require(m != nullptr && out != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm/out");
+  cudaStream_t st = m->rt->stream();
+  B2_CUDA(cudaMemsetAsync(m->M.stats, 0, 64, st));
+  k_mpm_stats<<<m->rt->num_sms, 256, 0, st>>>(m->M, m->gen);
+  m->rt->count_launch();
+  B2_CUDA(cudaMemcpyAsync(out, m->M.stats, 64, cudaMemcpyDeviceToHost, st));
+  m->rt->sync();
+  m->ensure_lists();
+  out[4] = (double)m->tree->list_count(m->M.leaf_sid);
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_set_profiling(B2Mpm m, int32_t on) {
+  if (!m) return -1;
+  m->profiling = on != 0;
+  return 0;
+}
+int32_t b2_mpm_phase_ms(B2Mpm m, float *out) {
+  if (!m || !out) return -1;
+  memcpy(out, m->phase_ms, sizeof(m->phase_ms));
+  return 0;
+}
+}  // extern "C"

@@ -1,0 +1,35 @@
+// b2_mpm.h -- device-visible state of the block-binned 3-D MLS-MPM solver (b2_mpm.cu)
+#pragma once
+#include "b2_internal.cuh"
+
+#define MPM_CHUNK 256            /* particles per bin chunk                      */
+#define MPM_PLANE_BYTES 4096     /* 256 x float4                                 */
+#define MPM_CHUNK_BYTES 17408    /* 4 float4 planes + 256 x u32 particle ids      */
+
+// Everything kernels need, passed by value.
+struct MpmDev {
+  // physics (mpm3d.py:13-23)
+  int n_grid, nb;  // cells / 4^3-blocks per axis
+  int pot;         // n_grid is a power of two (x*inv_dx is then exact = x/dx)
+  float dx, inv_dx, dt, p_vol, p_mass, E, gravity, stress_k;  // stress_k = -dt*4*E*p_vol/dx^2
+  int bound;
+  int activate_halo;  // reproduce the CUDA-BLS epilogue's wider active set
+  int slab_lo, slab_hi;
+  // grid
+  B2TreeDev *T;
+  B2Path leaf;  // path to the dense(4^3) SNode holding {vx,vy,vz,m}
+  int leaf_sid;
+  // block slots (a block gets a slot the first time a particle lands in it)
+  int *slot_of;    // [nb^3] -> slot, -1 none, -2 being created
+  int *slot_key;   // [max_slots]
+  u32 *nslots;
+  int max_slots, maxc;
+  // two particle generations (read g, write g^1)
+  u32 *count[2];     // [max_slots]
+  u32 *chunk_of[2];  // [max_slots * maxc] chunk id + 1
+  u8 *arena[2];
+  u32 *arena_next[2];
+  u32 arena_cap;
+  u32 *work_counter;  // dynamic slot fetch for the persistent kernels [8]
+  double *stats;      // [8]
+};

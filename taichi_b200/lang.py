@@ -1,0 +1,336 @@
+"""Taichi-like Python surface for the sparse-SNode path (names + argument meaning of
+python/taichi/lang/snode.py:26-304, lang/misc.py:323, lang/impl.py:592-625, lang/field.py:121-351).
+
+    import taichi_b200 as ti
+    ti.init(arch=ti.cuda, device_memory_GB=2)
+    x = ti.field(ti.f32)
+    block = ti.root.pointer(ti.ijk, 16).bitmasked(ti.ijk, 8).dense(ti.ijk, 4)
+    block.place(x)
+    x[3, 4, 5] = 1.0                  # activates, like the reference's python-scope write
+    for I in ti.active_indices(block):  # struct-for over active cells (host view of the kernel's loop)
+        ...
+    block.parent().deactivate_all()
+
+There is no kernel compiler here: struct-fors run as the library's built-in bodies
+(fill / reduce / to_numpy / deactivate / coordinate dump) and as the prebuilt MPM kernels.
+"""
+import ctypes as C
+import numpy as np
+
+from . import _lib as L
+
+lib = L.lib
+
+cuda = gpu = "cuda"
+cpu = x64 = "x64"
+f32, i32, f64, i64 = "f32", "i32", "f64", "i64"
+_DT = {"f32": (np.float32, 4), "i32": (np.int32, 4), "f64": (np.float64, 8), "i64": (np.int64, 8),
+       float: (np.float32, 4), int: (np.int32, 4)}
+
+
+class _Axes(tuple):
+    pass
+
+
+i, j, k, l = _Axes((0,)), _Axes((1,)), _Axes((2,)), _Axes((3,))
+ij, ijk, ijkl = _Axes((0, 1)), _Axes((0, 1, 2)), _Axes((0, 1, 2, 3))
+jk, ik = _Axes((1, 2)), _Axes((0, 2))
+
+
+class _Program:
+    def __init__(self):
+        self.rt = None
+        self.nodes = None
+        self.tree = None
+        self.fields = []
+
+
+_prog = _Program()
+root = None
+
+
+def init(arch=cuda, device_memory_GB=None, device_memory_fraction=None, device_index=0, **_ignored):
+    """ti.init: only arch=ti.cuda exists in this library (no CPU fallback)."""
+    global root
+    if arch not in (cuda,):
+        raise RuntimeError("taichi_b200 implements arch=ti.cuda only (no ti.cpu fallback)")
+    reset()
+    if device_memory_GB is not None:
+        lib.b2_set_pool_size(C.c_uint64(int(device_memory_GB * (1 << 30))))
+    _prog.rt = lib.ti_create_runtime(L.TI_ARCH_CUDA, device_index)
+    L.check()
+    _prog.nodes = [dict(type=L.ROOT, parent=-1, axes=[], sizes=[], dtype_bytes=0, chunk_size=0)]
+    root = SNode(0)
+    return _prog.rt
+
+
+def reset():
+    global root
+    if _prog.tree:
+        lib.b2_destroy_tree(_prog.tree)
+    if _prog.rt:
+        lib.ti_destroy_runtime(_prog.rt)
+    _prog.rt = _prog.tree = _prog.nodes = None
+    _prog.fields = []
+    root = None
+
+
+def sync():
+    lib.b2_sync(_prog.rt)
+    L.check()
+
+
+def _materialize():
+    """Program::add_snode_tree: first use of any field freezes the tree (program.cpp:238-255)."""
+    if _prog.tree is None:
+        n = len(_prog.nodes)
+        arr = (L.B2SNodeDesc * n)()
+        for q, nd in enumerate(_prog.nodes):
+            arr[q].type, arr[q].parent, arr[q].num_axes = nd["type"], nd["parent"], len(nd["axes"])
+            for t, (a, s) in enumerate(zip(nd["axes"], nd["sizes"])):
+                arr[q].axes[t], arr[q].sizes[t] = a, s
+            arr[q].dtype_bytes, arr[q].chunk_size = nd["dtype_bytes"], nd["chunk_size"]
+        _prog.tree = lib.b2_create_tree(_prog.rt, arr, n)
+        L.check()
+    return _prog.tree
+
+
+def _coords(idx, ndim=None):
+    c = np.atleast_2d(np.asarray(idx, dtype=np.int32))
+    out = np.zeros((c.shape[0], 12), np.int32)
+    out[:, :c.shape[1]] = c
+    return out
+
+
+class SNode:
+    def __init__(self, idx):
+        self.id = idx
+
+    def _child(self, type_, axes, sizes, chunk_size=0):
+        if _prog.tree is not None:
+            raise RuntimeError("the SNode tree is already materialized")
+        axes = list(axes)
+        sizes = [sizes] * len(axes) if isinstance(sizes, int) else list(sizes)
+        _prog.nodes.append(dict(type=type_, parent=self.id, axes=axes, sizes=sizes, dtype_bytes=0, chunk_size=chunk_size))
+        return SNode(len(_prog.nodes) - 1)
+
+    def dense(self, axes, dimensions):
+        return self._child(L.DENSE, axes, dimensions)
+
+    def pointer(self, axes, dimensions):
+        return self._child(L.POINTER, axes, dimensions)
+
+    def bitmasked(self, axes, dimensions):
+        return self._child(L.BITMASKED, axes, dimensions)
+
+    def dynamic(self, axis, dimension, chunk_size=None):
+        return self._child(L.DYNAMIC, axis, [dimension], chunk_size or dimension)
+
+    def place(self, *fields):
+        for f in fields:
+            for comp in f._components():
+                _prog.nodes.append(dict(type=L.PLACE, parent=self.id, axes=[], sizes=[], dtype_bytes=comp.itemsize, chunk_size=0))
+                comp.place_id = len(_prog.nodes) - 1
+                comp.parent_snode = self
+        return self
+
+    def parent(self, n=1):
+        p = self
+        for _ in range(n):
+            p = SNode(_prog.nodes[p.id]["parent"])
+        return p
+
+    @property
+    def shape(self):
+        ext = {}
+        q = self.id
+        while q > 0:
+            nd = _prog.nodes[q]
+            for a, s in zip(nd["axes"], nd["sizes"]):
+                ext[a] = ext.get(a, 1) * s
+            q = nd["parent"]
+        return tuple(ext[a] for a in sorted(ext))
+
+    def _axes(self):
+        ax = set()
+        q = self.id
+        while q > 0:
+            ax.update(_prog.nodes[q]["axes"])
+            q = _prog.nodes[q]["parent"]
+        return sorted(ax)
+
+    def deactivate_all(self):
+        lib.b2_deactivate_all(_materialize(), self.id)
+        L.check()
+
+    @property
+    def _num_dynamically_allocated(self):
+        n = lib.b2_num_dynamically_allocated(_materialize(), self.id)
+        L.check()
+        return int(n)
+
+    @property
+    def _cell_size_bytes(self):
+        return int(lib.b2_snode_cell_size(_materialize(), self.id))
+
+    def _to_full(self, idx):
+        c = np.atleast_2d(np.asarray(idx, dtype=np.int32))
+        out = np.zeros((c.shape[0], 12), np.int32)
+        for t, a in enumerate(self._axes()):
+            out[:, a] = c[:, t]
+        return out
+
+
+def activate(snode, idx):
+    c = snode._to_full(idx)
+    lib.b2_activate(_materialize(), snode.id, c.ctypes.data_as(C.c_void_p), len(c))
+    L.check()
+
+
+def deactivate(snode, idx):
+    c = snode._to_full(idx)
+    lib.b2_deactivate(_materialize(), snode.id, c.ctypes.data_as(C.c_void_p), len(c))
+    L.check()
+
+
+def is_active(snode, idx):
+    c = snode._to_full(idx)
+    out = np.zeros(len(c), np.uint8)
+    lib.b2_is_active(_materialize(), snode.id, c.ctypes.data_as(C.c_void_p), len(c), out.ctypes.data_as(C.c_void_p))
+    L.check()
+    return out.astype(bool) if np.ndim(idx) > 1 else bool(out[0])
+
+
+def append(snode, idx, val):
+    c = snode.parent()._to_full(idx) if np.ndim(idx) else snode.parent()._to_full([idx])
+    v = np.ascontiguousarray(np.broadcast_to(val, (len(c),)), dtype=np.int32)
+    lib.b2_dynamic_append_i32(_materialize(), snode.id, c.ctypes.data_as(C.c_void_p), len(c), v.ctypes.data_as(C.c_void_p))
+    L.check()
+
+
+def length(snode, idx):
+    c = snode.parent()._to_full(idx) if np.ndim(idx) else snode.parent()._to_full([idx])
+    out = np.zeros(len(c), np.int32)
+    lib.b2_dynamic_length(_materialize(), snode.id, c.ctypes.data_as(C.c_void_p), len(c), out.ctypes.data_as(C.c_void_p))
+    L.check()
+    return out if np.ndim(idx) > 1 else int(out[0])
+
+
+def active_indices(snode):
+    """Coordinates a struct-for over `snode` visits (n, ndim), sorted."""
+    t = _materialize()
+    n = lib.b2_struct_for_coords(t, snode.id, None, 0)
+    L.check()
+    out = np.zeros((max(n, 1), 12), np.int32)
+    lib.b2_struct_for_coords(t, snode.id, out.ctypes.data_as(C.c_void_p), n)
+    L.check()
+    out = out[:n][:, snode._axes()]
+    return out[np.lexsort(out.T[::-1])] if n else out
+
+
+def deactivate_all_snodes():
+    for q, nd in enumerate(_prog.nodes):
+        if nd["parent"] == 0 and nd["type"] != L.PLACE:
+            SNode(q).deactivate_all()
+
+
+class ScalarField:
+    def __init__(self, dtype):
+        self.np_dtype, self.itemsize = _DT[dtype]
+        self.np_dtype = np.dtype(self.np_dtype)
+        self.place_id = None
+        self.parent_snode = None
+
+    def _components(self):
+        return [self]
+
+    @property
+    def shape(self):
+        return self.parent_snode.shape
+
+    def __setitem__(self, idx, val):
+        c = self.parent_snode._to_full([idx] if np.ndim(idx) <= 1 else idx)
+        v = np.ascontiguousarray(np.broadcast_to(val, (len(c),)), dtype=self.np_dtype)
+        lib.b2_write(_materialize(), self.place_id, c.ctypes.data_as(C.c_void_p), len(c), v.ctypes.data_as(C.c_void_p), 0)
+        L.check()
+
+    def __getitem__(self, idx):
+        c = self.parent_snode._to_full([idx] if np.ndim(idx) <= 1 else idx)
+        v = np.zeros(len(c), self.np_dtype)
+        lib.b2_read(_materialize(), self.place_id, c.ctypes.data_as(C.c_void_p), len(c), v.ctypes.data_as(C.c_void_p))
+        L.check()
+        return v if np.ndim(idx) > 1 else v[0]
+
+    def atomic_add(self, idx, val):
+        """ti.atomic_add(x[I], v) for a batch of indices (f32)."""
+        c = self.parent_snode._to_full(idx)
+        v = np.ascontiguousarray(np.broadcast_to(val, (len(c),)), dtype=np.float32)
+        lib.b2_write(_materialize(), self.place_id, c.ctypes.data_as(C.c_void_p), len(c), v.ctypes.data_as(C.c_void_p), 1)
+        L.check()
+
+    def fill(self, val):
+        bits = int(np.array([val], self.np_dtype).view(np.uint32)[0])
+        lib.b2_field_fill(_materialize(), self.place_id, C.c_uint32(bits))
+        L.check()
+
+    def to_numpy(self):
+        out = np.zeros(self.shape, self.np_dtype)
+        lib.b2_field_to_dense(_materialize(), self.place_id, out.ctypes.data_as(C.c_void_p))
+        L.check()
+        return out
+
+    def from_numpy(self, arr):
+        arr = np.ascontiguousarray(arr, dtype=self.np_dtype)
+        assert arr.shape == self.shape
+        lib.b2_field_from_dense(_materialize(), self.place_id, arr.ctypes.data_as(C.c_void_p))
+        L.check()
+
+    def to_torch(self, device="cuda"):
+        import torch
+        out = torch.zeros(self.shape, dtype=getattr(torch, self.np_dtype.name), device=device)
+        lib.b2_field_to_dense(_materialize(), self.place_id, C.c_void_p(out.data_ptr()))
+        L.check()
+        sync()
+        return out
+
+    def from_torch(self, t):
+        assert t.is_contiguous() and tuple(t.shape) == self.shape
+        lib.b2_field_from_dense(_materialize(), self.place_id, C.c_void_p(t.data_ptr()))
+        L.check()
+        sync()
+
+    def _reduce(self, op):
+        out = np.zeros(1, self.np_dtype)
+        lib.b2_field_reduce(_materialize(), self.place_id, op, 0 if self.np_dtype == np.float32 else 1, out.ctypes.data_as(C.c_void_p))
+        L.check()
+        return out[0]
+
+    def sum(self):
+        return self._reduce(0)
+
+    def min(self):
+        return self._reduce(1)
+
+    def max(self):
+        return self._reduce(2)
+
+
+def field(dtype, shape=None):
+    f = ScalarField(dtype)
+    if shape is not None:
+        shape = (shape,) if isinstance(shape, int) else tuple(shape)
+        root.dense(_Axes(range(len(shape))), list(shape)).place(f)
+    _prog.fields.append(f)
+    return f
+
+
+def block_local(*_fields):
+    """ti.block_local is a property of the prebuilt MPM kernels here (Mpm3D(block_local=True))."""
+
+
+def no_activate(*_snodes):
+    pass
+
+
+def loop_config(**_kw):
+    pass

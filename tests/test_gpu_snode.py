@@ -1,0 +1,331 @@
+"""Parity of the CUDA sparse-SNode runtime (through the C ABI) against the oracle
+(oracle/snode_oracle.c, itself pinned to the reference's runtime.cpp by
+test_oracle_vs_reference.py) on identical inputs: element lists and struct-for coordinate sets
+bit-exact as sorted sets, allocator counts equal, zero-fill on reuse.
+Reference tests restated: tests/python/test_bitmasked.py:5-137, test_sparse_deactivate.py:5-107,
+test_listgen.py:8-58, test_gc.py:17-90, test_dynamic*.py (append/length), internal_functions.h."""
+import numpy as np
+import pytest
+
+from _desc import TreeBuilder
+from _b2 import B2Impl, have_gpu
+from test_oracle_vs_reference import Impl, ORC, _random_tree
+
+pytestmark = pytest.mark.gpu
+
+
+class OrcImpl(Impl):
+    def append(self, dyn, coords, vals):
+        from _desc import coords12, i32p
+        c = coords12(coords)
+        v = np.ascontiguousarray(vals, dtype=np.int32)
+        self.lib.orc_dynamic_append_i32(dyn, i32p(c), len(c), i32p(v))
+
+    def length(self, dyn, coords):
+        from _desc import coords12, i32p
+        c = coords12(coords)
+        out = np.zeros(len(c), dtype=np.int32)
+        self.lib.orc_dynamic_length(dyn, i32p(c), len(c), i32p(out))
+        return out
+
+
+@pytest.fixture()
+def impls():
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    g = B2Impl()
+    yield g, OrcImpl(ORC, "orc_")
+    g.close()
+    code, msg = g.runtime_error()
+    assert code == 0, msg
+
+
+def both(impls, fn):
+    return [fn(i) for i in impls]
+
+
+def test_bitmasked_basic(impls):  # test_bitmasked.py:5-31 -> c == 3, s == 42
+    tb = TreeBuilder()
+    b0 = tb.bitmasked(0, "ij", (3, 6))
+    bm = tb.bitmasked(b0, "i", 8)
+    x = tb.place(bm)
+    res = []
+    for impl in impls:
+        impl.create(tb)
+        impl.write_i32(x, [[5, 1], [9, 4], [0, 3]], [2, 20, 20])
+        v = impl.visited(bm)
+        assert len(v) == 3
+        assert impl.read_i32(x, v[:, :2]).sum() == 42
+        assert impl.is_active(bm, v[:, :2]).sum() == 3
+        assert impl.is_active(bm, [[1, 1], [2, 5]]).sum() == 0
+        res.append(v)
+    assert np.array_equal(res[0], res[1])
+
+
+def test_bitmasked_then_dense_and_bitmasked(impls):  # test_bitmasked.py:34-79 -> 256 and 4
+    for inner, expect in (("dense", 256), ("bitmasked", 4)):
+        tb = TreeBuilder()
+        b = tb.bitmasked(0, "i", 128)
+        d = getattr(tb, inner)(b, "i", 128)
+        x = tb.place(d)
+        out = []
+        for impl in impls:
+            impl.create(tb)
+            impl.write_i32(x, [[0], [127], [256], [257]], [1, 1, 1, 1])
+            v = impl.visited(d)
+            assert len(v) == expect
+            out.append(v)
+        assert np.array_equal(out[0], out[1])
+
+
+def test_huge_bitmasked(impls):  # test_bitmasked.py:82-106 at the reference's full n = 1024 on the GPU
+    g, o = impls
+    for impl, n in ((g, 1024), (o, 256)):
+        tb = TreeBuilder()
+        b = tb.bitmasked(0, "i", n)
+        b2 = tb.bitmasked(b, "i", 2 * n)
+        tb.place(b2)
+        impl.create(tb)
+        idx = np.arange(0, n * n * 2, 32)
+        impl.activate(b2, idx[:, None])
+        v = impl.visited(b2)
+        assert len(v) == (n * n * 2) // 32
+        assert np.array_equal(v[:, 0], idx)
+
+
+def test_bitmasked_listgen_prime(impls):  # test_bitmasked.py:109-137, n = 80173 (prime)
+    n = 80173
+    tb = TreeBuilder()
+    d = tb.dense(0, "i", n)
+    b = tb.bitmasked(d, "i", 1)
+    tb.place(b)
+    lists = []
+    for impl in impls:
+        impl.create(tb)
+        impl.activate(b, np.arange(n)[:, None])
+        assert len(impl.visited(b)) == n
+        lst = impl.list(d)
+        assert len(lst) == (n + 1023) // 1024 and lst[:, 13].max() == n  # runtime.cpp:1313-1328
+        lists.append(lst)
+    assert np.array_equal(lists[0], lists[1])
+
+
+def test_sparse_deactivate_pointer(impls):  # test_sparse_deactivate.py:5-70
+    tb = TreeBuilder()
+    ptr = tb.pointer(0, "i", 16)
+    d = tb.dense(ptr, "i", 16)
+    x = tb.place(d)
+    for impl in impls:
+        impl.create(tb)
+        impl.write_i32(x, [[0], [19]], [1, 1])
+        assert len(impl.visited(d)) == 32
+        impl.deactivate(ptr, [[0]])
+        impl.gc(ptr)
+        assert len(impl.visited(d)) == 16
+        impl.write_i32(x, [[20], [45]], [1, 1])
+        assert len(impl.visited(d)) == 32
+        impl.activate(d, [[3]])
+        assert impl.read_i32(x, [[0]])[0] == 0  # recycled memory is zero-filled at GC
+        assert impl.stats(ptr)[0] == 3
+
+
+def test_gc_reuses_nodes(impls):  # test_gc.py:75-90: _num_dynamically_allocated stays 1
+    tb = TreeBuilder()
+    ptr = tb.pointer(0, "i", 16)
+    d = tb.dense(ptr, "i", 16)
+    x = tb.place(d)
+    for impl in impls:
+        impl.create(tb)
+        for it in range(20):
+            impl.deactivate_all(ptr)
+            impl.write_i32(x, [[(it * 7) % 256]], [1])
+            assert impl.stats(ptr)[0] == 1
+        assert len(impl.visited(d)) == 16
+    g = impls[0]
+    assert g.lib.b2_num_dynamically_allocated(g.tree, ptr) == 1
+
+
+def test_listgen_coverage_3d(impls):  # test_listgen.py:35-58 shape
+    tb = TreeBuilder()
+    p = 0
+    for _ in range(3):
+        p = tb.dense(p, "ijk", 4)
+    tb.place(p)
+    g = impls[0]
+    g.create(tb)
+    v = g.visited(p)
+    assert len(v) == 64**3
+    lin = (v[:, 0].astype(np.int64) * 64 + v[:, 1]) * 64 + v[:, 2]
+    assert np.array_equal(np.sort(lin), np.arange(64**3))
+
+
+def test_refine_coordinates_known_answer(impls):  # refine_coordinates_test.cpp:149-165
+    tb = TreeBuilder()
+    d = tb.dense(0, "ij", (4, 8))
+    tb.place(d)
+    g = impls[0]
+    g.create(tb)
+    v = g.visited(d)
+    assert np.array_equal(v[:, 0] * 8 + v[:, 1], np.arange(32))
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_random_trees_match_oracle(impls, seed):
+    g, o = impls
+    rng = np.random.default_rng(seed)
+    ndim = int(rng.integers(1, 4))
+    tb, leaf, places, extent = _random_tree(rng, ndim)
+    g.create(tb)
+    o.create(tb)
+    n = int(rng.integers(1, 200))
+    coords = np.stack([rng.integers(0, e, n) for e in extent], axis=1)
+    vals = rng.integers(1, 1000, n).astype(np.int32)
+    for impl in (g, o):
+        impl.activate(leaf, coords)
+    # writes to a place activate as well; last writer wins is racy -> use distinct coords
+    uc, ui = np.unique(coords, axis=0, return_index=True)
+    for impl in (g, o):
+        impl.write_i32(places[0], uc, vals[ui])
+    assert np.array_equal(g.read_i32(places[0], uc), o.read_i32(places[0], uc))
+    path = []
+    q = leaf
+    while q > 0:
+        path.append(q)
+        q = tb.nodes[q]["parent"]
+    for lvl in path:
+        assert np.array_equal(g.list(lvl), o.list(lvl))
+        assert np.array_equal(g.visited(lvl), o.visited(lvl))
+    probe = np.stack([rng.integers(0, e, 64) for e in extent], axis=1)
+    for lvl in path:
+        assert np.array_equal(g.is_active(lvl, probe), o.is_active(lvl, probe))
+    sparse = [q for q in path if tb.nodes[q]["type"] in (2, 3)]
+    lvl = int(rng.choice(sparse))
+    vis = o.visited(lvl)
+    if len(vis):
+        sub = vis[rng.random(len(vis)) < 0.5][:, :ndim]
+        if len(sub):
+            for impl in (g, o):
+                impl.deactivate(lvl, sub)
+                if tb.nodes[lvl]["type"] == 2:
+                    impl.gc(lvl)
+    coords2 = np.stack([rng.integers(0, e, n // 2 + 1) for e in extent], axis=1)
+    for impl in (g, o):
+        impl.activate(leaf, coords2)
+    for q in path:
+        assert np.array_equal(g.list(q), o.list(q))
+        assert np.array_equal(g.visited(q), o.visited(q))
+        if tb.nodes[q]["type"] == 2:
+            assert np.array_equal(g.stats(q), o.stats(q))
+    top = path[-1]
+    for impl in (g, o):
+        impl.deactivate_all(top)
+    for q in path:
+        assert len(g.visited(q)) == len(o.visited(q))
+        if tb.nodes[q]["type"] == 2:
+            assert np.array_equal(g.stats(q), o.stats(q))
+
+
+def test_massive_concurrent_activation(impls):
+    """10^6 writers hammer few pointer cells: exactly one node per cell may be allocated
+    (Pointer_activate under contention, node_pointer.h:41-65)."""
+    g, _ = impls
+    tb = TreeBuilder()
+    p = tb.pointer(0, "ijk", 8)
+    b = tb.bitmasked(p, "ijk", 4)
+    d = tb.dense(b, "ijk", 4)
+    x = tb.place(d, 4)
+    g.create(tb)
+    rng = np.random.default_rng(7)
+    n = 1 << 20
+    coords = rng.integers(0, 32, (n, 3)).astype(np.int32)  # corner 32^3 region -> 2^3 pointer cells, 8^3 blocks
+    g.add_f32(x, coords, np.ones(n, np.float32))
+    assert g.stats(p)[0] == 8
+    v = g.visited(d)
+    uc, cnt = np.unique(coords, axis=0, return_counts=True)
+    blocks = np.unique(uc // 4, axis=0)
+    assert len(v) == len(blocks) * 64
+    got = g.read_f32(x, uc)
+    assert np.array_equal(got, cnt.astype(np.float32))  # small integers: exact in fp32 whatever the order
+
+
+def test_dynamic_append_length_gc(impls):  # ti.append / ti.length / deactivate_all on dynamic (test_gc.py:55-72 shape)
+    tb = TreeBuilder()
+    p = tb.pointer(0, "i", 8)
+    dyn = tb.dynamic(p, "j", 1024, 32)
+    x = tb.place(dyn)
+    rng = np.random.default_rng(3)
+    rows = rng.integers(0, 8, 3000)
+    vals = np.arange(3000, dtype=np.int32)
+    res = []
+    for impl in impls:
+        impl.create(tb)
+        impl.append(dyn, np.stack([rows, np.zeros_like(rows)], 1), vals)
+        ln = impl.length(dyn, np.stack([np.arange(8), np.zeros(8, int)], 1))
+        assert np.array_equal(ln, np.bincount(rows, minlength=8))
+        v = impl.visited(dyn)
+        assert len(v) == 3000
+        got = impl.read_i32(x, v[:, :2])
+        # every appended value present exactly once in its row (order within a row is racy on the GPU)
+        for r in range(8):
+            assert np.array_equal(np.sort(got[v[:, 0] == r]), np.sort(vals[rows == r]))
+        st = impl.stats(dyn)
+        res.append(st.copy())
+        impl.deactivate_all(p)
+        assert impl.length(dyn, [[3, 0]])[0] == 0
+        assert len(impl.visited(dyn)) == 0
+        st2 = impl.stats(dyn)
+        assert st2[1] == st[0] and st2[2] == 0  # every chunk back on the free list
+        impl.append(dyn, [[2, 0]], [77])
+        assert impl.stats(dyn)[0] == st[0]  # reused, not newly carved
+        assert impl.read_i32(x, [[2, 0]])[0] == 77
+    assert np.array_equal(res[0], res[1])
+
+
+def test_field_fill_to_dense_reduce(impls):
+    import ctypes as C
+    g, _ = impls
+    tb = TreeBuilder()
+    p = tb.pointer(0, "ij", 4)
+    d = tb.dense(p, "ij", 8)
+    x = tb.place(d, 4)
+    g.create(tb)
+    coords = np.array([[1, 2], [9, 30], [31, 31]])
+    g.add_f32(x, coords, [1.5, 2.5, -3.0])
+    img = np.full((32, 32), 7, np.float32)
+    assert g.lib.b2_field_to_dense(g.tree, x, img.ctypes.data_as(C.c_void_p)) == 0
+    ref = np.zeros((32, 32), np.float32)
+    ref[1, 2], ref[9, 30], ref[31, 31] = 1.5, 2.5, -3.0
+    assert np.array_equal(img, ref)
+    out = np.zeros(1, np.float32)
+    for op, expect in ((0, 1.0), (1, -3.0), (2, 2.5)):
+        assert g.lib.b2_field_reduce(g.tree, x, op, 0, out.ctypes.data_as(C.c_void_p)) == 0
+        assert out[0] == np.float32(expect)
+    one = np.float32(1.0).view(np.uint32)
+    assert g.lib.b2_field_fill(g.tree, x, C.c_uint32(int(one))) == 0
+    assert g.lib.b2_field_reduce(g.tree, x, 0, 0, out.ctypes.data_as(C.c_void_p)) == 0
+    assert out[0] == 3 * 64  # three active 8x8 blocks
+    full = np.arange(32 * 32, dtype=np.float32).reshape(32, 32)
+    assert g.lib.b2_field_from_dense(g.tree, x, full.ctypes.data_as(C.c_void_p)) == 0
+    assert g.lib.b2_field_to_dense(g.tree, x, img.ctypes.data_as(C.c_void_p)) == 0
+    assert np.array_equal(img, full)
+    assert g.stats(p)[0] == 16
+
+
+def test_error_convention(impls):
+    """Errors never cross the ABI as exceptions: NULL / -1 + thread-local (code, message)."""
+    g, _ = impls
+    L = g.L
+    assert L.lib.b2_create_tree(None, None, 0) is None
+    code, msg = L.last_error()
+    assert code == -5 and "runtime" in msg  # TI_ERROR_ARGUMENT_NULL
+    L.lib.ti_set_last_error(0, None)
+    tb = TreeBuilder()
+    d = tb.dense(0, "i", 4)
+    tb.place(d)
+    g.create(tb)
+    assert L.lib.b2_gc(g.tree, d) == -1
+    assert L.last_error()[0] == -4  # INVALID_ARGUMENT: not gc-able
+    L.lib.ti_set_last_error(0, None)
+    assert L.lib.ti_create_runtime(4, 0) is None  # TI_ARCH_X64: no CPU path in this library
+    assert L.last_error()[0] == -1
+    L.lib.ti_set_last_error(0, None)
