@@ -1,0 +1,257 @@
+#!/usr/bin/env python
+"""bench.py -- MPM particle-updates/s of the sparse 3-D MLS-MPM hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c2]
+
+One "step" = one frame = SUBSTEPS substeps (mpm3d.py:11 `steps = 25`) of the full substep
+(grid clear + P2G + listgen + grid-op + G2P with re-binning).  Workload at N=1 = config[2] of
+BASELINE.json, the one north_star quotes the metric/target on: sparse 512^3
+pointer->bitmasked->dense(4^3) grid, 8M particles (SURVEY 8d C3 cloud).  `value` is timed with the
+particles resident in HBM; `e2e` re-uploads the particle state from pinned host memory through
+the C ABI (b2_mpm_set_particles) and reads the positions back (b2_mpm_get_particles) every step.
+N>1 (torchrun): one process per GPU, weak scaling (8M particles per rank).
+--impl reference: the CPU restatement of the reference's kernels (oracle/mpm_oracle.c, multi-threaded
+fp32 CAS atomics as the reference's x64 backend) on the host cores; one step = ONE substep.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+sys.path.insert(0, os.path.join(REPO, "tests"))
+
+SUBSTEPS = 25
+WORKLOADS = {
+    # name: (n_grid, particles, dt, layout, description)
+    "c3": (512, 8 * 1024 * 1024, 2e-5, "pointer_bitmasked",
+           "sparse 3D MLS-MPM pointer->bitmasked->dense(4^3) 512^3, 8M particles, ti.block_local P2G/G2P"),
+    "c2": (128, 1024 * 1024, 8e-5, "dense", "mpm3d dense 128^3, 1M particles, fp32"),
+}
+
+
+def make_cloud(name, n_particles, seed, rank=0):
+    """C3 = three balls r=0.08, ~8 particles/cell, v=(0,-1,0); C2 = mpm3d.py:87 cube."""
+    rng = np.random.default_rng(seed + 1000 * rank)
+    if name == "c2":
+        x = (rng.random((n_particles, 3), dtype=np.float32) * 0.4 + 0.15).astype(np.float32)
+        v = np.zeros((n_particles, 3), np.float32)
+    else:
+        centres = np.array([[0.3, 0.6, 0.5], [0.5, 0.3, 0.5], [0.7, 0.6, 0.5]], np.float32)
+        d = rng.standard_normal((n_particles, 3)).astype(np.float32)
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        r = 0.08 * rng.random(n_particles, dtype=np.float32) ** (1.0 / 3.0)
+        x = (centres[np.arange(n_particles) % 3] + d * r[:, None]).astype(np.float32)
+        v = np.tile(np.array([0.0, -1.0, 0.0], np.float32), (n_particles, 1))
+    return x, v, np.zeros((n_particles, 3, 3), np.float32), np.ones(n_particles, np.float32)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.rows, self.stop_flag, self.index = [], False, index
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop_flag = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k].startswith("Active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": int(self.rows[0][1]) if self.rows[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def cpu_reference(name, steps, warmup, sample_particles=None):
+    """The reference's CPU path restated (oracle/mpm_oracle.c mode 1): one substep per step."""
+    from _desc import load_oracle
+    orc = load_oracle()
+    n_grid, n_p, dt, _, desc = WORKLOADS[name]
+    cores = os.cpu_count() or 1
+    threads = min(cores, 256)
+    x, v, Cm, J = make_cloud(name, n_p, seed=3)
+    gv = np.zeros((n_grid,) * 3 + (3,), np.float32)
+    gm = np.zeros((n_grid,) * 3, np.float32)
+    fp = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))  # noqa: E731
+
+    def one():
+        orc.orc_mpm3d_substeps(n_grid, C.c_int64(n_p), fp(x), fp(v), fp(Cm), fp(J), C.c_float(dt), C.c_float(400.0),
+                               C.c_float(1.0), C.c_float(9.8), 3, 1, 1, threads, fp(gv), fp(gm), None, None)
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt_s = (time.perf_counter() - t0) / max(steps, 1)
+    return n_p / dt_s, dt_s * 1e3, threads, f"1 substep of {desc} per step (dense {n_grid}^3 host grid), {threads} threads, fp32 CAS atomics"
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    val, ms, threads, sample = cpu_reference(args.workload, max(1, args.steps), min(args.warmup, 1))
+    n_grid, n_p, dt, layout, desc = WORKLOADS[args.workload]
+    line = {"impl": "reference", "metric": "MPM particle-updates/s", "value": val, "unit": "particle-updates/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "n_grid": n_grid, "particles": n_p, "substeps_per_step": 1, "dt": dt},
+            "cpu_baseline": {"value": val, "unit": "particle-updates/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "particle-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import taichi_b200 as tb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n_grid, n_p, dt, layout, desc = WORKLOADS[args.workload]
+    rt = tb.Runtime(local, device_memory_GB=4 if args.workload == "c3" else 1)
+    solver = tb.Mpm3D(rt, n_grid, n_p, dt, layout=layout)
+    x, v, Cm, J = make_cloud(args.workload, n_p, seed=3, rank=rank)
+    # pinned host buffers (e2e) and the initial upload
+    hx, hv, hC, hJ = (torch.from_numpy(a).pin_memory() for a in (x, v, Cm, J))
+    hx_out = torch.empty_like(hx).pin_memory()
+    solver.set_particles(hx, hv, hC, hJ)
+    rt.wait()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    def step_resident():
+        solver.substep(SUBSTEPS)
+
+    def step_e2e():
+        solver.set_particles(hx, hv, hC, hJ)
+        solver.substep(SUBSTEPS)
+        solver.get_particles(x=hx_out)
+
+    for _ in range(args.warmup):
+        step_resident()
+    solver.set_profiling(True)
+    l0 = rt.launches()
+    with ClockSampler(local) as clocks:
+        total_ms = timed(step_resident, args.steps)
+    launches = rt.launches() - l0
+    phases = solver.phase_ms()
+    solver.set_profiling(False)
+    st = solver.stats()
+    # e2e through the C ABI with host buffers
+    step_e2e()
+    e2e_ms = timed(step_e2e, max(1, args.steps))
+    rt.wait()
+    buf = C.create_string_buffer(256)
+    err = tb._lib.lib.b2_check_runtime_error(rt.handle, buf, 256)
+    assert err == 0, buf.value
+
+    ms_per_step = total_ms / args.steps
+    value = world * n_p * SUBSTEPS / (ms_per_step * 1e-3)
+    e2e_value = world * n_p * SUBSTEPS / (e2e_ms / max(1, args.steps) * 1e-3)
+    cells = st["active_blocks"] * 64
+    peak, peak_kind = hbm_peak()
+    alg = {"p2g": 64 * n_p + 32 * cells, "g2p": 80 * n_p + 12 * cells, "clear": 16 * cells, "grid_op": 28 * cells}
+    dom = max(("p2g", "g2p"), key=lambda k: phases[k])
+    ach = alg[dom] / (phases[dom] * 1e-3) / 1e9 if phases[dom] > 0 else 0.0
+    sub_ms = sum(phases[k] for k in ("clear", "p2g", "listgen", "grid_op", "g2p"))
+    sub_alg = 144 * n_p + 88 * cells
+    line = {
+        "metric": "MPM particle-updates/s", "value": value, "unit": "particle-updates/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "n_grid": n_grid, "particles_per_gpu": n_p, "substeps_per_step": SUBSTEPS, "dt": dt,
+                   "active_cells": cells, "l2": "particle state (>=512 MiB/substep) exceeds the 126 MB L2: no flush needed",
+                   "parallelism": "1 process/GPU, independent domains" if world > 1 else "single GPU"},
+        "e2e": {"value": e2e_value, "unit": "particle-updates/s", "h2d_bytes_per_step": int(n_p * 64), "d2h_bytes_per_step": int(n_p * 12)},
+        "gpu_launches": int(launches),
+        "clocks": clocks.summary(),
+        "roofline": {"bound": "hbm", "kernel": "k_mpm_" + dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                     "traffic": None, "peak_kind": peak_kind, "alg_bytes_per_launch": alg[dom], "ms_per_launch": phases[dom]},
+        "roofline_substep": {"alg_bytes": sub_alg, "ms": sub_ms, "achieved": sub_alg / (sub_ms * 1e-3) / 1e9 if sub_ms else 0,
+                             "frac": (sub_alg / (sub_ms * 1e-3) / 1e9 / peak) if sub_ms else 0},
+        "phase_ms": phases,
+    }
+    if rank == 0:
+        if world == 1 and not args.no_cpu:
+            cv, cms, threads, sample = cpu_reference(args.workload, 1, 1)
+            line["cpu_baseline"] = {"value": cv, "unit": "particle-updates/s", "cores": threads, "kind": "port", "sample": sample}
+        print(json.dumps(line))
+    solver.destroy()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -681,8 +681,9 @@ struct B2Mpm_t {
   bool lists_valid = false;
   bool sparse = false;
   bool profiling = false;
-  cudaEvent_t ev[8];
-  float phase_ms[6] = {0, 0, 0, 0, 0, 0};
+  std::vector<cudaEvent_t> prof_events;
+  double phase_sum[6] = {0, 0, 0, 0, 0, 0};
+  long long phase_count = 0;
   std::vector<void *> allocs;
 
   template <typename T>
@@ -768,7 +769,7 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   M.leaf = tree->path_to(leaf);
   M.leaf_sid = leaf;
   const int64_t nblocks = (int64_t)nb * nb * nb;
-  M.max_slots = (int)std::min<int64_t>(nblocks, std::max<int64_t>(4096, p.max_particles / 16));
+  M.max_slots = (int)std::min<int64_t>(nblocks, std::max<int64_t>(4096, p.max_particles / 64));
   M.maxc = 32;
   M.arena_cap = (u32)((p.max_particles + MPM_CHUNK - 1) / MPM_CHUNK + M.max_slots + 64);
   M.slot_of = dalloc<int>(nblocks, 0xFF);
@@ -785,13 +786,12 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   }
   M.work_counter = dalloc<u32>(8);
   M.stats = dalloc<double>(8);
-  for (auto &e : ev) B2_CUDA(cudaEventCreate(&e));
   rt->sync();
 }
 B2Mpm_t::~B2Mpm_t() {
   cudaStreamSynchronize(rt->stream());
   for (void *p : allocs) cudaFree(p);
-  for (auto &e : ev) cudaEventDestroy(e);
+  for (auto &e : prof_events) cudaEventDestroy(e);
   delete tree;
 }
 void B2Mpm_t::reset_bins() {
@@ -847,25 +847,36 @@ void B2Mpm_t::g2p() {
 }
 void B2Mpm_t::substep(int n) {
   cudaStream_t st = rt->stream();
-  for (int s = 0; s < n; s++) {
-    const bool prof = profiling && s == n - 1;
-    if (prof) B2_CUDA(cudaEventRecord(ev[0], st));
-    clear_grid();
-    if (prof) B2_CUDA(cudaEventRecord(ev[1], st));
-    p2g();
-    if (prof) B2_CUDA(cudaEventRecord(ev[2], st));
-    ensure_lists();
-    if (prof) B2_CUDA(cudaEventRecord(ev[3], st));
-    grid_op();
-    if (prof) B2_CUDA(cudaEventRecord(ev[4], st));
-    g2p();
-    if (prof) {
-      B2_CUDA(cudaEventRecord(ev[5], st));
-      B2_CUDA(cudaEventSynchronize(ev[5]));
-      float ms[5];
-      for (int k = 0; k < 5; k++) B2_CUDA(cudaEventElapsedTime(&ms[k], ev[k], ev[k + 1]));
-      phase_ms[0] = ms[0], phase_ms[1] = ms[1], phase_ms[2] = ms[2], phase_ms[3] = ms[3], phase_ms[4] = ms[4], phase_ms[5] = 0.f;
+  if (profiling) {
+    while ((int)prof_events.size() < 6 * n) {
+      cudaEvent_t e;
+      B2_CUDA(cudaEventCreate(&e));
+      prof_events.push_back(e);
     }
+  }
+  for (int s = 0; s < n; s++) {
+    cudaEvent_t *e = profiling ? &prof_events[6 * s] : nullptr;
+    if (e) B2_CUDA(cudaEventRecord(e[0], st));
+    clear_grid();
+    if (e) B2_CUDA(cudaEventRecord(e[1], st));
+    p2g();
+    if (e) B2_CUDA(cudaEventRecord(e[2], st));
+    ensure_lists();
+    if (e) B2_CUDA(cudaEventRecord(e[3], st));
+    grid_op();
+    if (e) B2_CUDA(cudaEventRecord(e[4], st));
+    g2p();
+    if (e) B2_CUDA(cudaEventRecord(e[5], st));
+  }
+  if (profiling && n > 0) {  // one synchronisation per call, then accumulate every substep's phases
+    B2_CUDA(cudaEventSynchronize(prof_events[6 * (n - 1) + 5]));
+    for (int s = 0; s < n; s++)
+      for (int k = 0; k < 5; k++) {
+        float ms;
+        B2_CUDA(cudaEventElapsedTime(&ms, prof_events[6 * s + k], prof_events[6 * s + k + 1]));
+        phase_sum[k] += ms;
+      }
+    phase_count += n;
   }
   B2_CUDA(cudaGetLastError());
 }
@@ -1002,11 +1013,13 @@ int32_t b2_mpm_stats(B2Mpm m, double *out) {
 int32_t b2_mpm_set_profiling(B2Mpm m, int32_t on) {
   if (!m) return -1;
   m->profiling = on != 0;
+  for (auto &v : m->phase_sum) v = 0;
+  m->phase_count = 0;
   return 0;
 }
 int32_t b2_mpm_phase_ms(B2Mpm m, float *out) {
   if (!m || !out) return -1;
-  memcpy(out, m->phase_ms, sizeof(m->phase_ms));
+  for (int k = 0; k < 6; k++) out[k] = m->phase_count ? (float)(m->phase_sum[k] / (double)m->phase_count) : 0.f;
   return 0;
 }
 }  // extern "C"

@@ -195,8 +195,14 @@ def test_random_trees_match_oracle(impls, seed):
     for lvl in path:
         assert np.array_equal(g.list(lvl), o.list(lvl))
         assert np.array_equal(g.visited(lvl), o.visited(lvl))
-    probe = np.stack([rng.integers(0, e, 64) for e in extent], axis=1)
-    for lvl in path:
+    for lvl in path:  # coordinates of an SNode op are in that SNode's own resolution
+        ext = [1] * ndim
+        q = lvl
+        while q > 0:
+            for a, sz in zip(tb.nodes[q]["axes"], tb.nodes[q]["sizes"]):
+                ext[a] *= sz
+            q = tb.nodes[q]["parent"]
+        probe = np.stack([rng.integers(0, e, 64) for e in ext], axis=1)
         assert np.array_equal(g.is_active(lvl, probe), o.is_active(lvl, probe))
     sparse = [q for q in path if tb.nodes[q]["type"] in (2, 3)]
     lvl = int(rng.choice(sparse))
