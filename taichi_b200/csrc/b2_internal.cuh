@@ -98,8 +98,10 @@ struct B2TreeDev {
 // Access path root..target with the divisors that extract each level's digits.
 struct B2Path {
   int n;
+  int pot;  // every shape and divisor on the path is a power of two: digits are shift + mask
   int id[B2_MAX_LEVELS];
   int div[B2_MAX_LEVELS][B2_MAX_AXES];
+  int shift[B2_MAX_LEVELS][B2_MAX_AXES];
 };
 
 struct B2DynNode {  // container of a dynamic SNode (16 B)
@@ -352,6 +354,13 @@ __device__ __forceinline__ void b2_refine(const B2SNodeDev &s, const int *in, in
 __device__ __forceinline__ int b2_level_index(const B2TreeDev *T, const B2Path &P, int l, const int *I) {
   const B2SNodeDev &s = T->s[P.id[l]];
   int v = 0;
+  if (P.pot) {
+    for (int k = 0; k < s.nax; k++) {
+      int a = s.ax[k];
+      v = v * s.shape[a] + (int)(((u32)I[a] >> P.shift[l][a]) & (u32)(s.shape[a] - 1));
+    }
+    return v;
+  }
   for (int k = 0; k < s.nax; k++) {
     int a = s.ax[k];
     int e = (int)(((u32)I[a] / (u32)P.div[l][a]) % (u32)s.shape[a]);

@@ -207,9 +207,10 @@ __global__ void __launch_bounds__(256) k_mpm_extract(MpmDev M, int gen, float *x
       const u32 id1 = M.chunk_of[gen][(u64)slot * M.maxc + q / MPM_CHUNK];
       const u8 *ch = mpm_chunk_ptr(M, gen, id1);
       const u32 i = q % MPM_CHUNK;
+      const float4 p0 = ((const float4 *)ch)[i];
+      if (p0.x == MPM_TOMB) continue;
       const u32 id = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[i];
       if ((long long)id >= nmax) continue;
-      const float4 p0 = ((const float4 *)ch)[i];
       const float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[i];
       const float4 p2 = ((const float4 *)(ch + 2 * MPM_PLANE_BYTES))[i];
       const float4 p3 = ((const float4 *)(ch + 3 * MPM_PLANE_BYTES))[i];
@@ -224,22 +225,27 @@ __global__ void __launch_bounds__(256) k_mpm_extract(MpmDev M, int gen, float *x
   }
 }
 
-// stats[0] particles, [1] slots, [2] occupied slots, [3] chunks in use
-__global__ void k_mpm_stats(MpmDev M, int gen) {
+// stats[0] live particles, [1] slots, [2] occupied slots, [3] chunks in use, [5] bin entries incl. tombstones
+__global__ void __launch_bounds__(256) k_mpm_stats(MpmDev M, int gen) {
   const u32 ns = *M.nslots;
-  unsigned long long np = 0, occ = 0;
-  for (u32 s = blockIdx.x * blockDim.x + threadIdx.x; s < ns; s += gridDim.x * blockDim.x) {
-    u32 c = M.count[gen][s];
-    np += c;
-    occ += c > 0;
+  unsigned long long np = 0, occ = 0, ent = 0;
+  for (u32 s = blockIdx.x; s < ns; s += gridDim.x) {
+    const u32 c = M.count[gen][s];
+    if (threadIdx.x == 0) occ += c > 0, ent += c;
+    for (u32 q = threadIdx.x; q < c; q += blockDim.x) {
+      const u8 *ch = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)s * M.maxc + q / MPM_CHUNK]);
+      np += ((const float4 *)ch)[q % MPM_CHUNK].x != MPM_TOMB;
+    }
   }
   for (int d = 16; d > 0; d >>= 1) {
     np += __shfl_down_sync(0xffffffffu, np, d);
     occ += __shfl_down_sync(0xffffffffu, occ, d);
+    ent += __shfl_down_sync(0xffffffffu, ent, d);
   }
   if ((threadIdx.x & 31) == 0) {
     atomicAdd(&M.stats[0], (double)np);
     atomicAdd(&M.stats[2], (double)occ);
+    atomicAdd(&M.stats[5], (double)ent);
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     M.stats[1] = (double)ns;
@@ -300,184 +306,7 @@ __global__ void __launch_bounds__(256) k_mpm_grid_to_dense(MpmDev M, float4 *out
   }
 }
 
-// ------------------------------------------------------------------------------------------
-// P2G, block-local: registers -> per-cell partials -> pad -> one vector red per node
-// ------------------------------------------------------------------------------------------
-#define P2G_THREADS 192
-__global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
-  // staging of one chunk (sorted by cell): 3 shared float4 planes + 3 plane-specific float4 per
-  // particle = 24 KiB; aliased by the per-cell partial sums R[64][27] (27 KiB) afterwards
-  __shared__ float4 sBuf[64 * 27];
-  __shared__ float4 sPad[216];
-  __shared__ int sHist[64];
-  __shared__ int sStart[65];
-  __shared__ unsigned short sCell[MPM_CHUNK];
-  __shared__ unsigned short sRank[MPM_CHUNK];
-  __shared__ u32 sTouched;
-  __shared__ int sSlot;
-  __shared__ float4 *sNb[8];
-  float4 *sSh = sBuf;            // [3][256]
-  float4 *sSp = sBuf + 3 * 256;  // [256][3]
-
-  const int tid = threadIdx.x;
-  const int cell = tid / 3, plane = tid - cell * 3;
-  const u32 nslots = *M.nslots;
-
-  for (;;) {
-    __syncthreads();
-    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[0], 1u);
-    __syncthreads();
-    const u32 slot = (u32)sSlot;
-    if (slot >= nslots) break;
-    const u32 total = M.count[gen][slot];
-    if (total == 0) continue;
-    const int key = M.slot_key[slot];
-    const int bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
-    if (tid == 0) sTouched = M.activate_halo ? 0xffu : 1u;
-
-    float4 acc[9];
-#pragma unroll
-    for (int q = 0; q < 9; q++) acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-
-    const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
-    for (u32 c = 0; c < nchunks; c++) {
-      const u8 *ch = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + c]);
-      const int n = (int)min((u32)MPM_CHUNK, total - c * MPM_CHUNK);
-      if (tid < 64) sHist[tid] = 0;
-      __syncthreads();
-      // pass 1: cell of every particle + its rank inside the cell
-      u32 tmask = 0;
-      for (int t = tid; t < n; t += P2G_THREADS) {
-        const float4 p0 = ((const float4 *)ch)[t];
-        const float xp[3] = {p0.x, p0.y, p0.z};
-        int l[3];
-#pragma unroll
-        for (int d = 0; d < 3; d++) {
-          const float X = M.pot ? xp[d] * M.inv_dx : xp[d] / M.dx;
-          l[d] = ((int)(X - 0.5f)) & 3;
-        }
-        const int cidx = (l[0] << 4) | (l[1] << 2) | l[2];
-        sCell[t] = (unsigned short)cidx;
-        sRank[t] = (unsigned short)atomicAdd(&sHist[cidx], 1);
-        const int h = ((l[0] >> 1) << 2) | ((l[1] >> 1) << 1) | (l[2] >> 1);
-#pragma unroll
-        for (int nbh = 0; nbh < 8; nbh++)
-          if ((nbh & ~h) == 0) tmask |= 1u << nbh;
-      }
-      tmask = __reduce_or_sync(0xffffffffu, tmask);
-      if ((tid & 31) == 0 && tmask) atomicOr(&sTouched, tmask);
-      __syncthreads();
-      // exclusive scan of the 64 cell counts (warps 0 and 1)
-      if (tid < 64) {
-        const int lane = tid & 31;
-        const int vcnt = sHist[tid];
-        int inc = vcnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-          const int tv = __shfl_up_sync(0xffffffffu, inc, d);
-          if (lane >= d) inc += tv;
-        }
-        sStart[tid + 1] = inc;  // per-warp inclusive; fixed up below
-      }
-      __syncthreads();
-      if (tid >= 32 && tid < 64) sStart[tid + 1] += sStart[32];
-      if (tid == 0) sStart[0] = 0;
-      __syncthreads();
-      // pass 2: per-particle constants, written at the cell-sorted position
-      for (int t = tid; t < n; t += P2G_THREADS) {
-        const float4 p0 = ((const float4 *)ch)[t];
-        const float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[t];
-        const float4 p2 = ((const float4 *)(ch + 2 * MPM_PLANE_BYTES))[t];
-        const float4 p3 = ((const float4 *)(ch + 3 * MPM_PLANE_BYTES))[t];
-        MpmStencil s;
-        mpm_stencil(M, p0.x, p0.y, p0.z, s);
-        const float stress = M.stress_k * (p0.w - 1.0f);
-        // A' = (stress I + m C) dx ; b = m v - A' fx ; V_i = b + i A'[:,0]
-        const float m = M.p_mass;
-        const float A00 = (stress + m * p1.w) * M.dx, A01 = m * p2.x * M.dx, A02 = m * p2.y * M.dx;
-        const float A10 = m * p2.z * M.dx, A11 = (stress + m * p2.w) * M.dx, A12 = m * p3.x * M.dx;
-        const float A20 = m * p3.y * M.dx, A21 = m * p3.z * M.dx, A22 = (stress + m * p3.w) * M.dx;
-        const float b0 = m * p1.x - (A00 * s.fx[0] + A01 * s.fx[1] + A02 * s.fx[2]);
-        const float b1 = m * p1.y - (A10 * s.fx[0] + A11 * s.fx[1] + A12 * s.fx[2]);
-        const float b2 = m * p1.z - (A20 * s.fx[0] + A21 * s.fx[1] + A22 * s.fx[2]);
-        const int q = sStart[sCell[t]] + sRank[t];
-        sSh[q] = make_float4(s.w[0][1], s.w[1][1], s.w[2][1], s.w[0][2]);
-        sSh[256 + q] = make_float4(s.w[1][2], s.w[2][2], A01, A11);
-        sSh[512 + q] = make_float4(A21, A02, A12, A22);
-        sSp[q * 3 + 0] = make_float4(s.w[0][0], b0, b1, b2);
-        sSp[q * 3 + 1] = make_float4(s.w[1][0], b0 + A00, b1 + A10, b2 + A20);
-        sSp[q * 3 + 2] = make_float4(s.w[2][0], b0 + 2.f * A00, b1 + 2.f * A10, b2 + 2.f * A20);
-      }
-      __syncthreads();
-      // stage 1: thread (cell, plane i) accumulates its 9 nodes over the cell's particles
-      {
-        const int q1 = sStart[cell + 1];
-        for (int q = sStart[cell]; q < q1; q++) {
-          const float4 h0 = sSh[q], h1 = sSh[256 + q], h2 = sSh[512 + q];
-          const float4 pl = sSp[q * 3 + plane];
-          const float wy[3] = {h0.x, h0.y, h0.z};
-          const float wz[3] = {h0.w, h1.x, h1.y};
-          float r0 = pl.y, r1 = pl.z, r2 = pl.w;  // value at (i, j, k=0), walks along j
-#pragma unroll
-          for (int j = 0; j < 3; j++) {
-            const float wxy = pl.x * wy[j];
-            float c0 = r0, c1 = r1, c2 = r2;  // walks along k
-#pragma unroll
-            for (int k = 0; k < 3; k++) {
-              const float w = wxy * wz[k];
-              float4 &a = acc[j * 3 + k];
-              a.x = fmaf(w, c0, a.x);
-              a.y = fmaf(w, c1, a.y);
-              a.z = fmaf(w, c2, a.z);
-              a.w += w;
-              c0 += h2.y, c1 += h2.z, c2 += h2.w;  // + A'[:,2]
-            }
-            r0 += h1.z, r1 += h1.w, r2 += h2.x;  // + A'[:,1]
-          }
-        }
-      }
-      __syncthreads();  // staging is overwritten by the next chunk / by R
-    }
-    // per-cell partials -> shared
-#pragma unroll
-    for (int q = 0; q < 9; q++) {
-      float4 a = acc[q];
-      a.w *= M.p_mass;
-      sBuf[cell * 27 + plane * 9 + q] = a;
-    }
-    // destination blocks (activated only if touched)
-    if (tid < 8) {
-      float4 *p = nullptr;
-      if ((sTouched >> tid) & 1u) p = mpm_block_ptr<true>(M, bx + (tid >> 2), by + ((tid >> 1) & 1), bz + (tid & 1));
-      sNb[tid] = p;
-    }
-    __syncthreads();
-    // stage 2: pad node = sum of the partials of the <=27 cells whose stencil covers it; flush
-    for (int nidx = tid; nidx < 216; nidx += P2G_THREADS) {
-      const int px = nidx / 36, py = (nidx / 6) % 6, pz = nidx % 6;
-      float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-      for (int i = 0; i < 3; i++) {
-        const int cx = px - i;
-        if ((unsigned)cx > 3u) continue;
-#pragma unroll
-        for (int j = 0; j < 3; j++) {
-          const int cy = py - j;
-          if ((unsigned)cy > 3u) continue;
-#pragma unroll
-          for (int k = 0; k < 3; k++) {
-            const int cz = pz - k;
-            if ((unsigned)cz > 3u) continue;
-            const float4 r = sBuf[((cx << 4) | (cy << 2) | cz) * 27 + i * 9 + j * 3 + k];
-            s4.x += r.x, s4.y += r.y, s4.z += r.z, s4.w += r.w;
-          }
-        }
-      }
-      float4 *dst = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
-      if (dst && (s4.x != 0.f || s4.y != 0.f || s4.z != 0.f || s4.w != 0.f)) red_add_v4(dst + (((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)), s4);
-    }
-  }
-}
+#include "b2_mpm_bls.cuh"
 
 // Plain path (ti.block_local off): every particle walks the SNode tree with activation and issues
 // one vector red per node -- the reference's non-BLS access pattern (K15) on the binned particles.
@@ -489,6 +318,7 @@ __global__ void __launch_bounds__(256) k_mpm_p2g_plain(MpmDev M, int gen) {
       const u8 *ch = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + q / MPM_CHUNK]);
       const u32 t = q % MPM_CHUNK;
       const float4 p0 = ((const float4 *)ch)[t];
+      if (p0.x == MPM_TOMB) continue;
       const float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[t];
       const float4 p2 = ((const float4 *)(ch + 2 * MPM_PLANE_BYTES))[t];
       const float4 p3 = ((const float4 *)(ch + 3 * MPM_PLANE_BYTES))[t];
@@ -520,7 +350,6 @@ __global__ void __launch_bounds__(256) k_mpm_p2g_plain(MpmDev M, int gen) {
 // ------------------------------------------------------------------------------------------
 // G2P + re-binning
 // ------------------------------------------------------------------------------------------
-#define G2P_THREADS 256
 template <bool BLS>
 __global__ void __launch_bounds__(G2P_THREADS, 3) k_mpm_g2p(MpmDev M, int gen) {
   __shared__ float4 sPad[216];
@@ -839,7 +668,7 @@ void B2Mpm_t::g2p() {
   B2_CUDA(cudaMemsetAsync(M.arena_next[gen ^ 1], 0, 16, st));
   B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
   if (prm.block_local)
-    k_mpm_g2p<true><<<rt->num_sms * 3, G2P_THREADS, 0, st>>>(M, gen);
+    k_mpm_g2p_bls<<<rt->num_sms * 3, G2P_THREADS, 0, st>>>(M, gen);
   else
     k_mpm_g2p<false><<<rt->num_sms * 3, G2P_THREADS, 0, st>>>(M, gen);
   rt->count_launch();
@@ -1001,7 +830,7 @@ int32_t b2_mpm_stats(B2Mpm m, double *out) {
   require(m != nullptr && out != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm/out");
   cudaStream_t st = m->rt->stream();
   B2_CUDA(cudaMemsetAsync(m->M.stats, 0, 64, st));
-  k_mpm_stats<<<m->rt->num_sms, 256, 0, st>>>(m->M, m->gen);
+  k_mpm_stats<<<m->rt->num_sms * 4, 256, 0, st>>>(m->M, m->gen);
   m->rt->count_launch();
   B2_CUDA(cudaMemcpyAsync(out, m->M.stats, 64, cudaMemcpyDeviceToHost, st));
   m->rt->sync();

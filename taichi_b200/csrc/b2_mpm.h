@@ -5,6 +5,8 @@
 #define MPM_CHUNK 256            /* particles per bin chunk                      */
 #define MPM_PLANE_BYTES 4096     /* 256 x float4                                 */
 #define MPM_CHUNK_BYTES 17408    /* 4 float4 planes + 256 x u32 particle ids      */
+#define MPM_SB 2048              /* particles cell-sorted per pass (shared-memory keys) */
+#define MPM_TOMB (-1.0e30f)      /* p0.x of a bin entry whose particle moved to another block */
 
 // Everything kernels need, passed by value.
 struct MpmDev {

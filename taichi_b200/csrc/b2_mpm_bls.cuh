@@ -1,0 +1,406 @@
+// b2_mpm_bls.cuh -- the block-local (ti.block_local) P2G and G2P kernels, included by b2_mpm.cu.
+//
+// Both kernels process one occupied 4^3 block per CTA (persistent CTAs fetch block slots from an
+// atomic work counter) and start with the same step: a counting sort of the block's particles by
+// cell in shared memory (64 integer bins; ranks come from the native integer ATOMS.ADD), which
+// gives   sStart[cell], sCnt[cell]   and   sPerm[start + rank] = particle index.
+// Tombstones (p0.x == MPM_TOMB, left behind by particles that moved to another block) sort into
+// bin 64 and are skipped.
+#pragma once
+
+
+struct MpmSortSmem {
+  u32 key[MPM_SB];             // cell << 16 | rank
+  unsigned short perm[MPM_SB]; // cell-sorted -> index inside the pass
+  int cnt[65];
+  int start[66];
+  int maxcnt;
+  u32 touched;
+  const u8 *chunk[64];         // chunk base pointers of the block's bin (maxc <= 64)
+};
+
+__device__ __forceinline__ int mpm_cell_of(const MpmDev &M, const float4 p0) {
+  const float xp[3] = {p0.x, p0.y, p0.z};
+  int l[3];
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    const float X = M.pot ? xp[d] * M.inv_dx : xp[d] / M.dx;
+    l[d] = ((int)(X - 0.5f)) & 3;
+  }
+  return (l[0] << 4) | (l[1] << 2) | l[2];
+}
+
+// Sorts particles [q0, q0+n) of the bin. All threads of the CTA must call it. NT = blockDim.x.
+// On return (after its final barrier): S.cnt / S.start / S.perm / S.maxcnt / S.touched are valid;
+// S.start[64] = number of live particles in the pass.
+template <int NT>
+__device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u32 q0, int n) {
+  const int tid = threadIdx.x;
+  if (tid < 65) S.cnt[tid] = 0;
+  __syncthreads();
+  u32 tmask = 0;
+  for (int t = tid; t < n; t += NT) {
+    const u32 q = q0 + t;
+    const float4 p0 = ((const float4 *)S.chunk[q / MPM_CHUNK])[q % MPM_CHUNK];
+    int c = 64;
+    if (p0.x != MPM_TOMB) {
+      c = mpm_cell_of(M, p0);
+      const int h = (((c >> 4) & 3) >> 1) << 2 | (((c >> 2) & 3) >> 1) << 1 | ((c & 3) >> 1);
+      // neighbour blocks {0,1}^3 whose nodes this particle's stencil reaches
+      tmask |= (h == 0) ? 0x01u : (h == 1) ? 0x03u : (h == 2) ? 0x05u : (h == 3) ? 0x0fu : (h == 4) ? 0x11u : (h == 5) ? 0x33u : (h == 6) ? 0x55u : 0xffu;
+    }
+    const int r = atomicAdd(&S.cnt[c], 1);
+    S.key[t] = ((u32)c << 16) | (u32)r;
+  }
+  tmask = __reduce_or_sync(0xffffffffu, tmask);
+  if ((tid & 31) == 0 && tmask) atomicOr(&S.touched, tmask);
+  __syncthreads();
+  if (tid < 32) {  // exclusive scan of 65 counts: lanes own entries 2l, 2l+1; entry 64 appended
+    const int a = S.cnt[2 * tid], b = S.cnt[2 * tid + 1];
+    int inc = a + b;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int tv = __shfl_up_sync(0xffffffffu, inc, d);
+      if (tid >= d) inc += tv;
+    }
+    S.start[2 * tid] = inc - a - b;
+    S.start[2 * tid + 1] = inc - b;
+    int mx = a > b ? a : b;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+    if (tid == 31) {
+      S.start[64] = inc;
+      S.start[65] = inc + S.cnt[64];
+      S.maxcnt = mx;
+    }
+  }
+  __syncthreads();
+  for (int t = tid; t < n; t += NT) {
+    const u32 k = S.key[t];
+    const int c = (int)(k >> 16);
+    if (c < 64) S.perm[S.start[c] + (int)(k & 0xffffu)] = (unsigned short)t;
+  }
+  __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------
+// P2G.  Thread (cell, i) accumulates its 9 nodes {mv, m} in registers; particles are fed in
+// rounds of <= 4 per cell so that all 192 threads stay busy whatever the sort order is.
+// ------------------------------------------------------------------------------------------
+#define P2G_THREADS 192
+#define P2G_R 4 /* particles per cell per round */
+__global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
+  __shared__ float4 sBuf[64 * 27];  // round staging (6 x 256 float4 = 24 KiB), later the per-cell partials R[64][27]
+  __shared__ MpmSortSmem S;
+  __shared__ int sSlot;
+  __shared__ float4 *sNb[8];
+  float4 *sSh = sBuf;            // [3][256]  {wy0,wy1,wy2,wz0} {wz1,wz2,A01,A11} {A21,A02,A12,A22}
+  float4 *sSp = sBuf + 3 * 256;  // [256][3]  {wx_i, V_i}
+
+  const int tid = threadIdx.x;
+  const int cell = tid / 3, plane = tid - cell * 3;
+  const u32 nslots = *M.nslots;
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[0], 1u);
+    __syncthreads();
+    const u32 slot = (u32)sSlot;
+    if (slot >= nslots) break;
+    const u32 total = M.count[gen][slot];
+    if (total == 0) continue;
+    const int key = M.slot_key[slot];
+    const int bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
+    const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
+    if (tid < (int)nchunks) S.chunk[tid] = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + tid]);
+    if (tid == 0) S.touched = M.activate_halo ? 0xffu : 0u;
+    // neighbour blocks that already exist are resolved now (latency hidden behind the sort);
+    // only touched-but-inactive ones are activated at the end
+    if (tid >= 160 && tid < 168) {
+      const int nbh = tid - 160;
+      sNb[nbh] = mpm_block_ptr<false>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
+    }
+    float4 acc[9];
+#pragma unroll
+    for (int q = 0; q < 9; q++) acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+    for (u32 q0 = 0; q0 < total; q0 += MPM_SB) {
+      const int n = (int)min((u32)MPM_SB, total - q0);
+      mpm_sort_pass<P2G_THREADS>(M, S, q0, n);  // (first barrier inside also publishes S.chunk)
+      const int rounds = (S.maxcnt + P2G_R - 1) / P2G_R;
+      for (int r = 0; r < rounds; r++) {
+        // loaders: slot (cell c, s) takes the (r*R + s)-th particle of cell c
+        for (int sl = tid; sl < 64 * P2G_R; sl += P2G_THREADS) {
+          const int c = sl / P2G_R, k = r * P2G_R + (sl % P2G_R);
+          if (k < S.cnt[c]) {
+            const u32 q = q0 + S.perm[S.start[c] + k];
+            const u8 *ch = S.chunk[q / MPM_CHUNK];
+            const u32 t = q % MPM_CHUNK;
+            const float4 p0 = ((const float4 *)ch)[t];
+            const float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[t];
+            const float4 p2 = ((const float4 *)(ch + 2 * MPM_PLANE_BYTES))[t];
+            const float4 p3 = ((const float4 *)(ch + 3 * MPM_PLANE_BYTES))[t];
+            MpmStencil s;
+            mpm_stencil(M, p0.x, p0.y, p0.z, s);
+            const float stress = M.stress_k * (p0.w - 1.0f);
+            // A' = (stress I + m C) dx ; b = m v - A' fx ; V_i = b + i A'[:,0]
+            const float m = M.p_mass;
+            const float A00 = (stress + m * p1.w) * M.dx, A01 = m * p2.x * M.dx, A02 = m * p2.y * M.dx;
+            const float A10 = m * p2.z * M.dx, A11 = (stress + m * p2.w) * M.dx, A12 = m * p3.x * M.dx;
+            const float A20 = m * p3.y * M.dx, A21 = m * p3.z * M.dx, A22 = (stress + m * p3.w) * M.dx;
+            const float b0 = m * p1.x - (A00 * s.fx[0] + A01 * s.fx[1] + A02 * s.fx[2]);
+            const float b1 = m * p1.y - (A10 * s.fx[0] + A11 * s.fx[1] + A12 * s.fx[2]);
+            const float b2 = m * p1.z - (A20 * s.fx[0] + A21 * s.fx[1] + A22 * s.fx[2]);
+            sSh[sl] = make_float4(s.w[0][1], s.w[1][1], s.w[2][1], s.w[0][2]);
+            sSh[256 + sl] = make_float4(s.w[1][2], s.w[2][2], A01, A11);
+            sSh[512 + sl] = make_float4(A21, A02, A12, A22);
+            sSp[sl * 3 + 0] = make_float4(s.w[0][0], b0, b1, b2);
+            sSp[sl * 3 + 1] = make_float4(s.w[1][0], b0 + A00, b1 + A10, b2 + A20);
+            sSp[sl * 3 + 2] = make_float4(s.w[2][0], b0 + 2.f * A00, b1 + 2.f * A10, b2 + 2.f * A20);
+          }
+        }
+        __syncthreads();
+        {
+          const int nk = min(P2G_R, S.cnt[cell] - r * P2G_R);
+          for (int k = 0; k < nk; k++) {
+            const int sl = cell * P2G_R + k;
+            const float4 h0 = sSh[sl], h1 = sSh[256 + sl], h2 = sSh[512 + sl];
+            const float4 pl = sSp[sl * 3 + plane];
+            const float wy[3] = {h0.x, h0.y, h0.z};
+            const float wz[3] = {h0.w, h1.x, h1.y};
+            float r0 = pl.y, r1 = pl.z, r2 = pl.w;  // value at (i, j, k=0), walks along j
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+              const float wxy = pl.x * wy[j];
+              float c0 = r0, c1 = r1, c2 = r2;  // walks along k
+#pragma unroll
+              for (int kk = 0; kk < 3; kk++) {
+                const float w = wxy * wz[kk];
+                float4 &a = acc[j * 3 + kk];
+                a.x = fmaf(w, c0, a.x);
+                a.y = fmaf(w, c1, a.y);
+                a.z = fmaf(w, c2, a.z);
+                a.w += w;
+                c0 += h2.y, c1 += h2.z, c2 += h2.w;  // + A'[:,2]
+              }
+              r0 += h1.z, r1 += h1.w, r2 += h2.x;  // + A'[:,1]
+            }
+          }
+        }
+        __syncthreads();  // staging is overwritten by the next round / by R
+      }
+    }
+    // per-cell partials -> shared
+#pragma unroll
+    for (int q = 0; q < 9; q++) {
+      float4 a = acc[q];
+      a.w *= M.p_mass;
+      sBuf[cell * 27 + plane * 9 + q] = a;
+    }
+    // touched neighbour blocks that do not exist yet are activated now (rare in steady state)
+    if (tid >= 160 && tid < 168) {
+      const int nbh = tid - 160;
+      if (!((S.touched >> nbh) & 1u))
+        sNb[nbh] = nullptr;
+      else if (sNb[nbh] == nullptr)
+        sNb[nbh] = mpm_block_ptr<true>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
+    }
+    __syncthreads();
+    // pad node = sum of the partials of the <=27 cells whose stencil covers it; one vector red each
+    for (int nidx = tid; nidx < 216; nidx += P2G_THREADS) {
+      const int px = nidx / 36, py = (nidx / 6) % 6, pz = nidx % 6;
+      float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        const int cx = px - i;
+        if ((unsigned)cx > 3u) continue;
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+          const int cy = py - j;
+          if ((unsigned)cy > 3u) continue;
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+            const int cz = pz - k;
+            if ((unsigned)cz > 3u) continue;
+            const float4 rr = sBuf[((cx << 4) | (cy << 2) | cz) * 27 + i * 9 + j * 3 + k];
+            s4.x += rr.x, s4.y += rr.y, s4.z += rr.z, s4.w += rr.w;
+          }
+        }
+      }
+      float4 *dst = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
+      if (dst && (s4.x != 0.f || s4.y != 0.f || s4.z != 0.f || s4.w != 0.f)) red_add_v4(dst + (((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)), s4);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// G2P + re-binning.  Particles are processed in cell-sorted order (same-cell lanes read the same
+// pad addresses).  A particle that stays in its block is written to the next generation's bin of
+// the SAME slot at a position inside a range the CTA reserved with ONE atomicAdd per pass; only
+// particles that change block go through the generic warp-aggregated append (mpm_insert).  The
+// unused tail of the reserved range (= number of leavers) is filled with tombstones.
+// ------------------------------------------------------------------------------------------
+#define G2P_THREADS 256
+__global__ void __launch_bounds__(G2P_THREADS, 3) k_mpm_g2p_bls(MpmDev M, int gen) {
+  __shared__ float4 sPad[216];
+  __shared__ MpmSortSmem S;
+  __shared__ u8 *sOut[65];
+  __shared__ u32 sBase, sStay;
+  __shared__ int sSlot;
+  __shared__ float4 *sNb[8];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const u32 nslots = *M.nslots;
+  const int g1 = gen ^ 1;
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[1], 1u);
+    __syncthreads();
+    const u32 slot = (u32)sSlot;
+    if (slot >= nslots) break;
+    const u32 total = M.count[gen][slot];
+    if (total == 0) continue;
+    const int key = M.slot_key[slot];
+    const int bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
+    const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
+    if (tid < (int)nchunks) S.chunk[tid] = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + tid]);
+    if (tid >= 32 && tid < 40) {
+      const int nbh = tid - 32;
+      sNb[nbh] = mpm_block_ptr<false>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
+    }
+    __syncthreads();
+    if (tid < 216) {
+      const int px = tid / 36, py = (tid / 6) % 6, pz = tid % 6;
+      const float4 *src = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
+      sPad[tid] = src ? src[((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (u32 q0 = 0; q0 < total; q0 += MPM_SB) {
+      const int n = (int)min((u32)MPM_SB, total - q0);
+      mpm_sort_pass<G2P_THREADS>(M, S, q0, n);
+      const int nlive = S.start[64];
+      if (nlive == 0) continue;  // uniform
+      if (tid == 0) {
+        sBase = atomicAdd(&M.count[g1][slot], (u32)nlive);
+        sStay = 0;
+      }
+      __syncthreads();
+      const u32 base = sBase;
+      const u32 c0 = base / MPM_CHUNK;
+      u32 c1 = (base + (u32)nlive - 1) / MPM_CHUNK;
+      if (c1 >= (u32)M.maxc) {
+        if (tid == 0) b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, key);
+        c1 = (u32)M.maxc - 1;
+      }
+      // chunks of the reserved range: the holder of position c*256 allocates chunk c
+      for (u32 c = c0 + tid; c <= c1; c += G2P_THREADS) {
+        u32 *cs = &M.chunk_of[g1][(u64)slot * M.maxc + c];
+        u32 id1;
+        if (c * MPM_CHUNK >= base) {
+          u32 cid = atomicAdd(M.arena_next[g1], 1u);
+          if (cid >= M.arena_cap) {
+            b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, -1);
+            cid = M.arena_cap - 1;
+          }
+          id1 = cid + 1;
+          __threadfence();
+          *(volatile u32 *)cs = id1;
+        } else {
+          unsigned ns = 8;
+          while ((id1 = ld_volatile_u32(cs)) == 0) {
+            __nanosleep(ns);
+            if (ns < 256) ns *= 2;
+          }
+        }
+        sOut[c - c0] = mpm_chunk_ptr(M, g1, id1);
+      }
+      __syncthreads();
+      for (int t0 = 0; t0 < nlive; t0 += G2P_THREADS) {
+        const int t = t0 + tid;
+        const bool valid = t < nlive;
+        float4 o0 = make_float4(0.f, 0.f, 0.f, 1.f), o1 = make_float4(0.f, 0.f, 0.f, 0.f), o2 = o1, o3 = o1;
+        int nkey = -1;
+        u32 id = 0;
+        if (valid) {
+          const u32 q = q0 + S.perm[t];
+          const u8 *ch = S.chunk[q / MPM_CHUNK];
+          const float4 p0 = ((const float4 *)ch)[q % MPM_CHUNK];
+          id = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[q % MPM_CHUNK];
+          MpmStencil s;
+          mpm_stencil(M, p0.x, p0.y, p0.z, s);
+          float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+          float Sx0 = 0.f, Sx1 = 0.f, Sx2 = 0.f, Sy0 = 0.f, Sy1 = 0.f, Sy2 = 0.f, Sz0 = 0.f, Sz1 = 0.f, Sz2 = 0.f;
+          const int l0 = s.base[0] & 3, l1 = s.base[1] & 3, l2 = s.base[2] & 3;
+          const float wz0 = s.w[0][2], wz1 = s.w[1][2], wz2 = s.w[2][2];
+#pragma unroll
+          for (int i = 0; i < 3; i++) {
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+              const float wxy = s.w[i][0] * s.w[j][1];
+              const int pidx = ((l0 + i) * 6 + (l1 + j)) * 6 + l2;
+              const float4 g0 = sPad[pidx], g1v = sPad[pidx + 1], g2 = sPad[pidx + 2];
+              // row = sum_k wz_k g_k ; rz = sum_k k wz_k g_k
+              const float t1x = wz1 * g1v.x, t1y = wz1 * g1v.y, t1z = wz1 * g1v.z;
+              const float t2x = wz2 * g2.x, t2y = wz2 * g2.y, t2z = wz2 * g2.z;
+              const float rx = fmaf(wz0, g0.x, t1x + t2x), ry = fmaf(wz0, g0.y, t1y + t2y), rzv = fmaf(wz0, g0.z, t1z + t2z);
+              const float zx = fmaf(2.f, t2x, t1x), zy = fmaf(2.f, t2y, t1y), zz = fmaf(2.f, t2z, t1z);
+              v0 = fmaf(wxy, rx, v0), v1 = fmaf(wxy, ry, v1), v2 = fmaf(wxy, rzv, v2);
+              Sz0 = fmaf(wxy, zx, Sz0), Sz1 = fmaf(wxy, zy, Sz1), Sz2 = fmaf(wxy, zz, Sz2);
+              if (j > 0) {
+                const float wj = (float)j * wxy;
+                Sy0 = fmaf(wj, rx, Sy0), Sy1 = fmaf(wj, ry, Sy1), Sy2 = fmaf(wj, rzv, Sy2);
+              }
+              if (i > 0) {
+                const float wi = (float)i * wxy;
+                Sx0 = fmaf(wi, rx, Sx0), Sx1 = fmaf(wi, ry, Sx1), Sx2 = fmaf(wi, rzv, Sx2);
+              }
+            }
+          }
+          // C[a][b] = 4/dx * (sum w g_a o_b - fx_b v_a)   (mpm3d.py:75 with dpos = (o - fx) dx)
+          const float k4 = 4.0f * M.inv_dx;
+          const float C00 = k4 * (Sx0 - s.fx[0] * v0), C01 = k4 * (Sy0 - s.fx[1] * v0), C02 = k4 * (Sz0 - s.fx[2] * v0);
+          const float C10 = k4 * (Sx1 - s.fx[0] * v1), C11 = k4 * (Sy1 - s.fx[1] * v1), C12 = k4 * (Sz1 - s.fx[2] * v1);
+          const float C20 = k4 * (Sx2 - s.fx[0] * v2), C21 = k4 * (Sy2 - s.fx[1] * v2), C22 = k4 * (Sz2 - s.fx[2] * v2);
+          const float nx = p0.x + M.dt * v0, ny = p0.y + M.dt * v1, nz = p0.z + M.dt * v2;
+          const float nJ = p0.w * (1.0f + M.dt * (C00 + C11 + C22));
+          o0 = make_float4(nx, ny, nz, nJ);
+          o1 = make_float4(v0, v1, v2, C00);
+          o2 = make_float4(C01, C02, C10, C11);
+          o3 = make_float4(C12, C20, C21, C22);
+          bool ok;
+          nkey = mpm_key_of_position(M, nx, ny, nz, &ok);
+          if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)id);
+        }
+        const bool stay = valid && nkey == key;
+        const unsigned smask = __ballot_sync(0xffffffffu, stay);
+        if (smask) {
+          u32 off = 0;
+          const int leader = __ffs(smask) - 1;
+          if (lane == leader) off = atomicAdd(&sStay, (u32)__popc(smask));
+          off = __shfl_sync(0xffffffffu, off, leader);
+          if (stay) {
+            const u32 pos = base + off + __popc(smask & ((1u << lane) - 1u));
+            const u32 c = pos / MPM_CHUNK, i = pos % MPM_CHUNK;
+            if (c <= c1) {
+              u8 *ch = sOut[c - c0];
+              ((float4 *)ch)[i] = o0;
+              ((float4 *)(ch + MPM_PLANE_BYTES))[i] = o1;
+              ((float4 *)(ch + 2 * MPM_PLANE_BYTES))[i] = o2;
+              ((float4 *)(ch + 3 * MPM_PLANE_BYTES))[i] = o3;
+              ((u32 *)(ch + 4 * MPM_PLANE_BYTES))[i] = id;
+            }
+          }
+        }
+        if (__any_sync(0xffffffffu, valid && !stay)) mpm_insert(M, g1, nkey, valid && !stay, o0, o1, o2, o3, id);
+      }
+      __syncthreads();
+      // unused tail of the reservation (one entry per particle that left the block)
+      for (u32 pos = base + sStay + tid; pos < base + (u32)nlive; pos += G2P_THREADS) {
+        const u32 c = pos / MPM_CHUNK;
+        if (c <= c1) ((float4 *)sOut[c - c0])[pos % MPM_CHUNK] = make_float4(MPM_TOMB, 0.f, 0.f, 1.f);
+      }
+    }
+    // this generation's bin is consumed: leave it empty for the generation after next
+    for (int t = tid; t < (int)nchunks; t += G2P_THREADS) M.chunk_of[gen][(u64)slot * M.maxc + t] = 0;
+    if (tid == 0) M.count[gen][slot] = 0;
+  }
+}

@@ -235,11 +235,17 @@ B2Path B2Tree_t::path_to(int target) const {
     total[a] = 1;
     for (int id : ids) total[a] *= s[id].shape[a];
   }
+  P.pot = 1;
+  auto ispot = [](int v) { return v > 0 && (v & (v - 1)) == 0; };
   for (int l = 0; l < P.n; l++) {
     P.id[l] = ids[l];
     for (int a = 0; a < B2_MAX_AXES; a++) {
       total[a] /= s[ids[l]].shape[a];
       P.div[l][a] = total[a];
+      if (!ispot(total[a]) || !ispot(s[ids[l]].shape[a])) P.pot = 0;
+      int sh = 0;
+      while ((1 << sh) < total[a]) sh++;
+      P.shift[l][a] = sh;
     }
   }
   return P;
