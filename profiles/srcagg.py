@@ -9,7 +9,7 @@ for r in rows:
     if len(r) == 2 and r[0] == "Function Name": fn = r[1]; hdr = None; continue
     if len(r) == 2 and r[0] == "File Path": cur_file = r[1]; continue
     if r and r[0] == "Line No": hdr = r; continue
-    if hdr is None or fn is None or want not in fn or len(r) < 10: continue
+    if hdr is None or fn is None or want not in fn or len(r) < 10 or r[0] == '': continue
     d = dict(zip(hdr, r))
     # sass rows carry "Source" twice: first col = cuda line text? use positional
     try:

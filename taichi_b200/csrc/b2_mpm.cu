@@ -24,6 +24,7 @@
 //    block fully coalesced.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "b2_host.h"
@@ -43,13 +44,31 @@ __device__ __forceinline__ u32 ld_volatile_u32(const u32 *p) { return *(const vo
 template <bool ACT>
 __device__ __forceinline__ float4 *mpm_block_ptr(const MpmDev &M, int bx, int by, int bz) {
   if ((unsigned)bx >= (unsigned)M.nb || (unsigned)by >= (unsigned)M.nb || (unsigned)bz >= (unsigned)M.nb) return nullptr;
+  // fast path: the three layouts' address arithmetic straight from kernel parameters (no
+  // descriptor loads, at most two dependent reads); anything inactive falls through
+  if (M.layout == 0) return (float4 *)(M.top + ((u64)((bx * M.nb + by) * M.nb + bz) << 10));
+  {
+    const int pc = ((bx >> 3) * M.np + (by >> 3)) * M.np + (bz >> 3);
+    const u64 c = b2_ld_volatile((const u64 *)M.top + pc);
+    const int li = ((bx & 7) << 6) | ((by & 7) << 3) | (bz & 7);
+    if (c > B2_BUSY) {
+      if (M.layout == 1) {
+        const u32 w = *(const volatile u32 *)((const u8 *)c + M.mask_off + (li >> 5) * 4);
+        if ((w >> (li & 31)) & 1u) return (float4 *)((u8 *)c + ((u64)li << 10));
+      } else {
+        const u64 c2 = b2_ld_volatile((const u64 *)c + li);
+        if (c2 > B2_BUSY) return (float4 *)c2;
+      }
+    }
+  }
+  if (!ACT) return nullptr;
   int I[B2_MAX_AXES];
 #pragma unroll
   for (int a = 0; a < B2_MAX_AXES; a++) I[a] = 0;
   I[0] = bx * 4, I[1] = by * 4, I[2] = bz * 4;
   int cell;
   bool dead;
-  u8 *node = b2_walk<ACT>(M.T, M.leaf, I, &cell, &dead);
+  u8 *node = b2_walk<true>(M.T, M.leaf, I, &cell, &dead);
   if (dead) return nullptr;
   return (float4 *)node;
 }
@@ -350,8 +369,9 @@ __global__ void __launch_bounds__(256) k_mpm_p2g_plain(MpmDev M, int gen) {
 // ------------------------------------------------------------------------------------------
 // G2P + re-binning
 // ------------------------------------------------------------------------------------------
+#define G2P_PLAIN_THREADS 256
 template <bool BLS>
-__global__ void __launch_bounds__(G2P_THREADS, 3) k_mpm_g2p(MpmDev M, int gen) {
+__global__ void __launch_bounds__(G2P_PLAIN_THREADS, 3) k_mpm_g2p(MpmDev M, int gen) {
   __shared__ float4 sPad[216];
   __shared__ float4 sP0[MPM_CHUNK];
   __shared__ u32 sId[MPM_CHUNK];
@@ -492,7 +512,7 @@ __global__ void __launch_bounds__(G2P_THREADS, 3) k_mpm_g2p(MpmDev M, int gen) {
     }
     // this generation's bin is consumed: leave it empty for the generation after next
     if (tid < (int)nchunks) M.chunk_of[gen][(u64)slot * M.maxc + tid] = 0;
-    for (int t = tid + G2P_THREADS; t < (int)nchunks; t += G2P_THREADS) M.chunk_of[gen][(u64)slot * M.maxc + t] = 0;
+    for (int t = tid + G2P_PLAIN_THREADS; t < (int)nchunks; t += G2P_PLAIN_THREADS) M.chunk_of[gen][(u64)slot * M.maxc + t] = 0;
     if (tid == 0) M.count[gen][slot] = 0;
   }
 }
@@ -597,6 +617,13 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   M.T = tree->dev;
   M.leaf = tree->path_to(leaf);
   M.leaf_sid = leaf;
+  M.layout = p.layout;
+  M.np = nb / 8;
+  M.top = tree->host_copy.root + tree->s[1].offset_in_parent_cell;
+  M.mask_off = tree->s[2].aux_offset;
+  if (tree->s[2].offset_in_parent_cell != 0 || tree->s[leaf].offset_in_parent_cell != 0 || (p.layout == 1 && tree->s[2].cell_size != 1024) ||
+      (p.layout == 0 && tree->s[1].cell_size != 1024))
+    throw B2Error(TI_ERROR_INVALID_STATE, "unexpected grid layout");
   const int64_t nblocks = (int64_t)nb * nb * nb;
   M.max_slots = (int)std::min<int64_t>(nblocks, std::max<int64_t>(4096, p.max_particles / 64));
   M.maxc = 32;
@@ -668,9 +695,17 @@ void B2Mpm_t::g2p() {
   B2_CUDA(cudaMemsetAsync(M.arena_next[gen ^ 1], 0, 16, st));
   B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
   if (prm.block_local)
-    k_mpm_g2p_bls<<<rt->num_sms * 3, G2P_THREADS, 0, st>>>(M, gen);
+  {
+    static int nt = getenv("B2_G2P_NT") ? atoi(getenv("B2_G2P_NT")) : 128;
+    if (nt == 256)
+      k_mpm_g2p_bls<256, 3><<<rt->num_sms * 3, 256, 0, st>>>(M, gen);
+    else if (nt == 64)
+      k_mpm_g2p_bls<64, 12><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
+    else
+      k_mpm_g2p_bls<128, 6><<<rt->num_sms * 6, 128, 0, st>>>(M, gen);
+  }
   else
-    k_mpm_g2p<false><<<rt->num_sms * 3, G2P_THREADS, 0, st>>>(M, gen);
+    k_mpm_g2p<false><<<rt->num_sms * 3, G2P_PLAIN_THREADS, 0, st>>>(M, gen);
   rt->count_launch();
   gen ^= 1;
 }

@@ -21,6 +21,10 @@ struct MpmDev {
   B2TreeDev *T;
   B2Path leaf;  // path to the dense(4^3) SNode holding {vx,vy,vz,m}
   int leaf_sid;
+  // fast non-activating block lookup (layout known at create time)
+  int layout, np;       // np = pointer cells per axis (layouts 1, 2)
+  u8 *top;              // the container directly under root
+  long long mask_off;   // layout 1: byte offset of the bitmasked container's mask words
   // block slots (a block gets a slot the first time a particle lands in it)
   int *slot_of;    // [nb^3] -> slot, -1 none, -2 being created
   int *slot_key;   // [max_slots]

@@ -10,13 +10,12 @@
 
 
 struct MpmSortSmem {
-  u32 key[MPM_SB];             // cell << 16 | rank
   unsigned short perm[MPM_SB]; // cell-sorted -> index inside the pass
   int cnt[65];
   int start[66];
   int maxcnt;
   u32 touched;
-  const u8 *chunk[64];         // chunk base pointers of the block's bin (maxc <= 64)
+  const u8 *chunk[32];         // chunk base pointers of the bin (maxc <= 32)
 };
 
 __device__ __forceinline__ int mpm_cell_of(const MpmDev &M, const float4 p0) {
@@ -34,7 +33,7 @@ __device__ __forceinline__ int mpm_cell_of(const MpmDev &M, const float4 p0) {
 // On return (after its final barrier): S.cnt / S.start / S.perm / S.maxcnt / S.touched are valid;
 // S.start[64] = number of live particles in the pass.
 template <int NT>
-__device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u32 q0, int n) {
+__device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u32 *key, u32 q0, int n) {  // key[MPM_SB]: cell << 16 | rank
   const int tid = threadIdx.x;
   if (tid < 65) S.cnt[tid] = 0;
   __syncthreads();
@@ -50,7 +49,7 @@ __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u
       tmask |= (h == 0) ? 0x01u : (h == 1) ? 0x03u : (h == 2) ? 0x05u : (h == 3) ? 0x0fu : (h == 4) ? 0x11u : (h == 5) ? 0x33u : (h == 6) ? 0x55u : 0xffu;
     }
     const int r = atomicAdd(&S.cnt[c], 1);
-    S.key[t] = ((u32)c << 16) | (u32)r;
+    key[t] = ((u32)c << 16) | (u32)r;
   }
   tmask = __reduce_or_sync(0xffffffffu, tmask);
   if ((tid & 31) == 0 && tmask) atomicOr(&S.touched, tmask);
@@ -76,7 +75,7 @@ __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u
   }
   __syncthreads();
   for (int t = tid; t < n; t += NT) {
-    const u32 k = S.key[t];
+    const u32 k = key[t];
     const int c = (int)(k >> 16);
     if (c < 64) S.perm[S.start[c] + (int)(k & 0xffffu)] = (unsigned short)t;
   }
@@ -91,9 +90,11 @@ __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u
 #define P2G_R 4 /* particles per cell per round */
 __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
   __shared__ float4 sBuf[64 * 27];  // round staging (6 x 256 float4 = 24 KiB), later the per-cell partials R[64][27]
+  __shared__ float4 sRaw[4 * 64 * P2G_R];  // next round's particle planes (cp.async); the sort keys alias it
   __shared__ MpmSortSmem S;
   __shared__ int sSlot;
   __shared__ float4 *sNb[8];
+  u32 *sKey = (u32 *)sRaw;
   float4 *sSh = sBuf;            // [3][256]  {wy0,wy1,wy2,wz0} {wz1,wz2,A01,A11} {A21,A02,A12,A22}
   float4 *sSp = sBuf + 3 * 256;  // [256][3]  {wx_i, V_i}
 
@@ -126,20 +127,32 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
 
     for (u32 q0 = 0; q0 < total; q0 += MPM_SB) {
       const int n = (int)min((u32)MPM_SB, total - q0);
-      mpm_sort_pass<P2G_THREADS>(M, S, q0, n);  // (first barrier inside also publishes S.chunk)
+      mpm_sort_pass<P2G_THREADS>(M, S, sKey, q0, n);  // (first barrier inside also publishes S.chunk)
       const int rounds = (S.maxcnt + P2G_R - 1) / P2G_R;
-      for (int r = 0; r < rounds; r++) {
-        // loaders: slot (cell c, s) takes the (r*R + s)-th particle of cell c
+      // loaders: slot (cell c, s) takes the (r*R + s)-th particle of cell c.  The four planes of
+      // round r+1 are fetched with cp.async while stage 1 of round r runs.
+      auto issue = [&](int r) {
         for (int sl = tid; sl < 64 * P2G_R; sl += P2G_THREADS) {
           const int c = sl / P2G_R, k = r * P2G_R + (sl % P2G_R);
           if (k < S.cnt[c]) {
             const u32 q = q0 + S.perm[S.start[c] + k];
-            const u8 *ch = S.chunk[q / MPM_CHUNK];
-            const u32 t = q % MPM_CHUNK;
-            const float4 p0 = ((const float4 *)ch)[t];
-            const float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[t];
-            const float4 p2 = ((const float4 *)(ch + 2 * MPM_PLANE_BYTES))[t];
-            const float4 p3 = ((const float4 *)(ch + 3 * MPM_PLANE_BYTES))[t];
+            const u8 *src = S.chunk[q / MPM_CHUNK] + (q % MPM_CHUNK) * 16;
+#pragma unroll
+            for (int pl4 = 0; pl4 < 4; pl4++) {
+              const unsigned dst = (unsigned)__cvta_generic_to_shared(&sRaw[pl4 * 64 * P2G_R + sl]);
+              asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src + pl4 * MPM_PLANE_BYTES) : "memory");
+            }
+          }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+      };
+      issue(0);
+      for (int r = 0; r < rounds; r++) {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        for (int sl = tid; sl < 64 * P2G_R; sl += P2G_THREADS) {
+          const int c = sl / P2G_R, k = r * P2G_R + (sl % P2G_R);
+          if (k < S.cnt[c]) {
+            const float4 p0 = sRaw[sl], p1 = sRaw[64 * P2G_R + sl], p2 = sRaw[2 * 64 * P2G_R + sl], p3 = sRaw[3 * 64 * P2G_R + sl];
             MpmStencil s;
             mpm_stencil(M, p0.x, p0.y, p0.z, s);
             const float stress = M.stress_k * (p0.w - 1.0f);
@@ -160,6 +173,7 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
           }
         }
         __syncthreads();
+        if (r + 1 < rounds) issue(r + 1);
         {
           const int nk = min(P2G_R, S.cnt[cell] - r * P2G_R);
           for (int k = 0; k < nk; k++) {
@@ -240,10 +254,11 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
 // particles that change block go through the generic warp-aggregated append (mpm_insert).  The
 // unused tail of the reserved range (= number of leavers) is filled with tombstones.
 // ------------------------------------------------------------------------------------------
-#define G2P_THREADS 256
-__global__ void __launch_bounds__(G2P_THREADS, 3) k_mpm_g2p_bls(MpmDev M, int gen) {
+template <int G2P_THREADS, int G2P_MINB>
+__global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M, int gen) {
   __shared__ float4 sPad[216];
   __shared__ MpmSortSmem S;
+  __shared__ u32 sKey[MPM_SB];
   __shared__ u8 *sOut[65];
   __shared__ u32 sBase, sStay;
   __shared__ int sSlot;
@@ -269,14 +284,14 @@ __global__ void __launch_bounds__(G2P_THREADS, 3) k_mpm_g2p_bls(MpmDev M, int ge
       sNb[nbh] = mpm_block_ptr<false>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
     }
     __syncthreads();
-    if (tid < 216) {
-      const int px = tid / 36, py = (tid / 6) % 6, pz = tid % 6;
+    for (int nidx = tid; nidx < 216; nidx += G2P_THREADS) {
+      const int px = nidx / 36, py = (nidx / 6) % 6, pz = nidx % 6;
       const float4 *src = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
-      sPad[tid] = src ? src[((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)] : make_float4(0.f, 0.f, 0.f, 0.f);
+      sPad[nidx] = src ? src[((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)] : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     for (u32 q0 = 0; q0 < total; q0 += MPM_SB) {
       const int n = (int)min((u32)MPM_SB, total - q0);
-      mpm_sort_pass<G2P_THREADS>(M, S, q0, n);
+      mpm_sort_pass<G2P_THREADS>(M, S, sKey, q0, n);
       const int nlive = S.start[64];
       if (nlive == 0) continue;  // uniform
       if (tid == 0) {
