@@ -91,6 +91,13 @@ __device__ __forceinline__ void mpm_stencil(const MpmDev &M, float x, float y, f
   }
 }
 __device__ __forceinline__ int mpm_key(const MpmDev &M, int bx, int by, int bz) { return (bx * M.nb + by) * M.nb + bz; }
+__device__ __forceinline__ void mpm_unkey(const MpmDev &M, int key, int &bx, int &by, int &bz) {
+  if (M.pot) {
+    bz = key & (M.nb - 1), by = (key >> M.nb_shift) & (M.nb - 1), bx = key >> (2 * M.nb_shift);
+  } else {
+    bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
+  }
+}
 
 __device__ __forceinline__ u8 *mpm_chunk_ptr(const MpmDev &M, int gen, u32 id1) { return M.arena[gen] + (u64)(id1 - 1) * MPM_CHUNK_BYTES; }
 
@@ -602,6 +609,8 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   M.n_grid = p.n_grid;
   M.nb = nb;
   M.pot = (p.n_grid & (p.n_grid - 1)) == 0;
+  M.nb_shift = 0;
+  while ((1 << M.nb_shift) < nb) M.nb_shift++;
   M.dx = 1.0f / (float)p.n_grid;
   M.inv_dx = (float)p.n_grid;
   M.dt = p.dt;
@@ -678,7 +687,13 @@ void B2Mpm_t::p2g() {
   cudaStream_t st = rt->stream();
   B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
   if (prm.block_local)
-    k_mpm_p2g<<<rt->num_sms * 4, P2G_THREADS, 0, st>>>(M, gen);
+  {
+    static int r = getenv("B2_P2G_R") ? atoi(getenv("B2_P2G_R")) : 4;
+    if (r == 3)
+      k_mpm_p2g<3><<<rt->num_sms * 4, P2G_THREADS, 0, st>>>(M, gen);
+    else
+      k_mpm_p2g<4><<<rt->num_sms * 4, P2G_THREADS, 0, st>>>(M, gen);
+  }
   else
     k_mpm_p2g_plain<<<rt->num_sms * 8, 256, 0, st>>>(M, gen);
   rt->count_launch();
@@ -696,7 +711,7 @@ void B2Mpm_t::g2p() {
   B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
   if (prm.block_local)
   {
-    static int nt = getenv("B2_G2P_NT") ? atoi(getenv("B2_G2P_NT")) : 128;
+    static int nt = getenv("B2_G2P_NT") ? atoi(getenv("B2_G2P_NT")) : 64;
     if (nt == 256)
       k_mpm_g2p_bls<256, 3><<<rt->num_sms * 3, 256, 0, st>>>(M, gen);
     else if (nt == 64)

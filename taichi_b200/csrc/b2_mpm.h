@@ -13,6 +13,7 @@ struct MpmDev {
   // physics (mpm3d.py:13-23)
   int n_grid, nb;  // cells / 4^3-blocks per axis
   int pot;         // n_grid is a power of two (x*inv_dx is then exact = x/dx)
+  int nb_shift;    // log2(nb) when pot
   float dx, inv_dx, dt, p_vol, p_mass, E, gravity, stress_k;  // stress_k = -dt*4*E*p_vol/dx^2
   int bound;
   int activate_halo;  // reproduce the CUDA-BLS epilogue's wider active set

@@ -87,10 +87,10 @@ __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u
 // rounds of <= 4 per cell so that all 192 threads stay busy whatever the sort order is.
 // ------------------------------------------------------------------------------------------
 #define P2G_THREADS 192
-#define P2G_R 4 /* particles per cell per round */
+template <int P2G_R> /* particles per cell per round */
 __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
   __shared__ float4 sBuf[64 * 27];  // round staging (6 x 256 float4 = 24 KiB), later the per-cell partials R[64][27]
-  __shared__ float4 sRaw[4 * 64 * P2G_R];  // next round's particle planes (cp.async); the sort keys alias it
+  __shared__ float4 sRaw[4 * 64 * 4];  // next round's particle planes (cp.async); the sort keys alias it
   __shared__ MpmSortSmem S;
   __shared__ int sSlot;
   __shared__ float4 *sNb[8];
@@ -111,7 +111,8 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
     const u32 total = M.count[gen][slot];
     if (total == 0) continue;
     const int key = M.slot_key[slot];
-    const int bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
+    int bx, by, bz;
+    mpm_unkey(M, key, bx, by, bz);
     const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
     if (tid < (int)nchunks) S.chunk[tid] = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + tid]);
     if (tid == 0) S.touched = M.activate_halo ? 0xffu : 0u;
@@ -224,23 +225,16 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
     for (int nidx = tid; nidx < 216; nidx += P2G_THREADS) {
       const int px = nidx / 36, py = (nidx / 6) % 6, pz = nidx % 6;
       float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-      for (int i = 0; i < 3; i++) {
-        const int cx = px - i;
-        if ((unsigned)cx > 3u) continue;
-#pragma unroll
-        for (int j = 0; j < 3; j++) {
-          const int cy = py - j;
-          if ((unsigned)cy > 3u) continue;
-#pragma unroll
-          for (int k = 0; k < 3; k++) {
-            const int cz = pz - k;
-            if ((unsigned)cz > 3u) continue;
-            const float4 rr = sBuf[((cx << 4) | (cy << 2) | cz) * 27 + i * 9 + j * 3 + k];
+      // cell = node - (i,j,k) must lie in [0,4)^3: i in [max(0,px-3), min(2,px)] etc.
+      const int i0 = max(0, px - 3), i1 = min(2, px), j0 = max(0, py - 3), j1 = min(2, py), k0 = max(0, pz - 3), k1 = min(2, pz);
+      for (int i = i0; i <= i1; i++)
+        for (int j = j0; j <= j1; j++) {
+          const float4 *row = &sBuf[((((px - i) << 4) | ((py - j) << 2)) + pz) * 27 + i * 9 + j * 3];
+          for (int k = k0; k <= k1; k++) {
+            const float4 rr = row[k - 27 * k];  // cell z = pz - k  ->  -27 k ; node k -> + k
             s4.x += rr.x, s4.y += rr.y, s4.z += rr.z, s4.w += rr.w;
           }
         }
-      }
       float4 *dst = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
       if (dst && (s4.x != 0.f || s4.y != 0.f || s4.z != 0.f || s4.w != 0.f)) red_add_v4(dst + (((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)), s4);
     }
@@ -276,7 +270,8 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
     const u32 total = M.count[gen][slot];
     if (total == 0) continue;
     const int key = M.slot_key[slot];
-    const int bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
+    int bx, by, bz;
+    mpm_unkey(M, key, bx, by, bz);
     const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
     if (tid < (int)nchunks) S.chunk[tid] = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + tid]);
     if (tid >= 32 && tid < 40) {
