@@ -33,7 +33,7 @@ __device__ __forceinline__ int mpm_cell_of(const MpmDev &M, const float4 p0) {
 // On return (after its final barrier): S.cnt / S.start / S.perm / S.maxcnt / S.touched are valid;
 // S.start[64] = number of live particles in the pass.
 template <int NT>
-__device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u32 *key, u32 q0, int n) {  // key[MPM_SB]: cell << 16 | rank
+__device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u32 *key, u32 q0, int n, int cbase = 0, int ncell = 64) {  // key[MPM_SB]: cell << 16 | rank
   const int tid = threadIdx.x;
   if (tid < 65) S.cnt[tid] = 0;
   __syncthreads();
@@ -46,7 +46,11 @@ __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u
       c = mpm_cell_of(M, p0);
       const int h = (((c >> 4) & 3) >> 1) << 2 | (((c >> 2) & 3) >> 1) << 1 | ((c & 3) >> 1);
       // neighbour blocks {0,1}^3 whose nodes this particle's stencil reaches
-      tmask |= (h == 0) ? 0x01u : (h == 1) ? 0x03u : (h == 2) ? 0x05u : (h == 3) ? 0x0fu : (h == 4) ? 0x11u : (h == 5) ? 0x33u : (h == 6) ? 0x55u : 0xffu;
+      c -= cbase;  // cells outside this CTA's window sort into the dead bin
+      if ((unsigned)c >= (unsigned)ncell)
+        c = 64;
+      else
+        tmask |= (h == 0) ? 0x01u : (h == 1) ? 0x03u : (h == 2) ? 0x05u : (h == 3) ? 0x0fu : (h == 4) ? 0x11u : (h == 5) ? 0x33u : (h == 6) ? 0x55u : 0xffu;
     }
     const int r = atomicAdd(&S.cnt[c], 1);
     key[t] = ((u32)c << 16) | (u32)r;
@@ -84,30 +88,35 @@ __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u
 
 // ------------------------------------------------------------------------------------------
 // P2G.  Thread (cell, i) accumulates its 9 nodes {mv, m} in registers; particles are fed in
-// rounds of <= 4 per cell so that all 192 threads stay busy whatever the sort order is.
+// rounds of <= R per cell so that all threads stay busy whatever the sort order is.
+// H = 1: one CTA (192 threads) per block.  H = 2: two CTAs (96 threads) per block, each owning the
+// cells of one x-half (more blocks in flight per SM, cheaper barriers; the sort pass is repeated).
 // ------------------------------------------------------------------------------------------
-#define P2G_THREADS 192
-template <int P2G_R> /* particles per cell per round */
-__global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
-  __shared__ float4 sBuf[64 * 27];  // round staging (6 x 256 float4 = 24 KiB), later the per-cell partials R[64][27]
-  __shared__ float4 sRaw[4 * 64 * 4];  // next round's particle planes (cp.async); the sort keys alias it
+template <int R, int H>
+__global__ void __launch_bounds__(192 / H, 4 * H) k_mpm_p2g(MpmDev M, int gen) {
+  constexpr int NT = 192 / H, NC = 64 / H, SL = NC * R, XC = 4 / H, PXN = XC + 2;
+  __shared__ float4 sBuf[NC * 27];  // round staging (6 x SL float4), later the per-cell partials R[NC][27]
+  __shared__ float4 sRaw[4 * SL > 512 ? 4 * SL : 512];  // next round's particle planes (cp.async); the 8 KiB of sort keys alias it
   __shared__ MpmSortSmem S;
-  __shared__ int sSlot;
+  __shared__ int sItem;
   __shared__ float4 *sNb[8];
   u32 *sKey = (u32 *)sRaw;
-  float4 *sSh = sBuf;            // [3][256]  {wy0,wy1,wy2,wz0} {wz1,wz2,A01,A11} {A21,A02,A12,A22}
-  float4 *sSp = sBuf + 3 * 256;  // [256][3]  {wx_i, V_i}
+  float4 *sSh = sBuf;           // [3][SL]  {wy0,wy1,wy2,wz0} {wz1,wz2,A01,A11} {A21,A02,A12,A22}
+  float4 *sSp = sBuf + 3 * SL;  // [SL][3]  {wx_i, V_i}
+  static_assert(6 * SL <= NC * 27, "staging must fit under the partials");
 
   const int tid = threadIdx.x;
   const int cell = tid / 3, plane = tid - cell * 3;
-  const u32 nslots = *M.nslots;
+  const u32 nitems = *M.nslots * H;
 
   for (;;) {
     __syncthreads();
-    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[0], 1u);
+    if (tid == 0) sItem = (int)atomicAdd(&M.work_counter[0], 1u);
     __syncthreads();
-    const u32 slot = (u32)sSlot;
-    if (slot >= nslots) break;
+    const u32 item = (u32)sItem;
+    if (item >= nitems) break;
+    const u32 slot = item / H;
+    const int half = (int)(item % H);
     const u32 total = M.count[gen][slot];
     if (total == 0) continue;
     const int key = M.slot_key[slot];
@@ -118,8 +127,8 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
     if (tid == 0) S.touched = M.activate_halo ? 0xffu : 0u;
     // neighbour blocks that already exist are resolved now (latency hidden behind the sort);
     // only touched-but-inactive ones are activated at the end
-    if (tid >= 160 && tid < 168) {
-      const int nbh = tid - 160;
+    if (tid >= 64 && tid < 72) {
+      const int nbh = tid - 64;
       sNb[nbh] = mpm_block_ptr<false>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
     }
     float4 acc[9];
@@ -128,19 +137,19 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
 
     for (u32 q0 = 0; q0 < total; q0 += MPM_SB) {
       const int n = (int)min((u32)MPM_SB, total - q0);
-      mpm_sort_pass<P2G_THREADS>(M, S, sKey, q0, n);  // (first barrier inside also publishes S.chunk)
-      const int rounds = (S.maxcnt + P2G_R - 1) / P2G_R;
+      mpm_sort_pass<NT>(M, S, sKey, q0, n, half * NC, NC);  // (first barrier inside also publishes S.chunk)
+      const int rounds = (S.maxcnt + R - 1) / R;
       // loaders: slot (cell c, s) takes the (r*R + s)-th particle of cell c.  The four planes of
       // round r+1 are fetched with cp.async while stage 1 of round r runs.
       auto issue = [&](int r) {
-        for (int sl = tid; sl < 64 * P2G_R; sl += P2G_THREADS) {
-          const int c = sl / P2G_R, k = r * P2G_R + (sl % P2G_R);
+        for (int sl = tid; sl < SL; sl += NT) {
+          const int c = sl / R, k = r * R + (sl % R);
           if (k < S.cnt[c]) {
             const u32 q = q0 + S.perm[S.start[c] + k];
             const u8 *src = S.chunk[q / MPM_CHUNK] + (q % MPM_CHUNK) * 16;
 #pragma unroll
             for (int pl4 = 0; pl4 < 4; pl4++) {
-              const unsigned dst = (unsigned)__cvta_generic_to_shared(&sRaw[pl4 * 64 * P2G_R + sl]);
+              const unsigned dst = (unsigned)__cvta_generic_to_shared(&sRaw[pl4 * SL + sl]);
               asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src + pl4 * MPM_PLANE_BYTES) : "memory");
             }
           }
@@ -150,10 +159,10 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
       issue(0);
       for (int r = 0; r < rounds; r++) {
         asm volatile("cp.async.wait_group 0;" ::: "memory");
-        for (int sl = tid; sl < 64 * P2G_R; sl += P2G_THREADS) {
-          const int c = sl / P2G_R, k = r * P2G_R + (sl % P2G_R);
+        for (int sl = tid; sl < SL; sl += NT) {
+          const int c = sl / R, k = r * R + (sl % R);
           if (k < S.cnt[c]) {
-            const float4 p0 = sRaw[sl], p1 = sRaw[64 * P2G_R + sl], p2 = sRaw[2 * 64 * P2G_R + sl], p3 = sRaw[3 * 64 * P2G_R + sl];
+            const float4 p0 = sRaw[sl], p1 = sRaw[SL + sl], p2 = sRaw[2 * SL + sl], p3 = sRaw[3 * SL + sl];
             MpmStencil s;
             mpm_stencil(M, p0.x, p0.y, p0.z, s);
             const float stress = M.stress_k * (p0.w - 1.0f);
@@ -166,8 +175,8 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
             const float b1 = m * p1.y - (A10 * s.fx[0] + A11 * s.fx[1] + A12 * s.fx[2]);
             const float b2 = m * p1.z - (A20 * s.fx[0] + A21 * s.fx[1] + A22 * s.fx[2]);
             sSh[sl] = make_float4(s.w[0][1], s.w[1][1], s.w[2][1], s.w[0][2]);
-            sSh[256 + sl] = make_float4(s.w[1][2], s.w[2][2], A01, A11);
-            sSh[512 + sl] = make_float4(A21, A02, A12, A22);
+            sSh[SL + sl] = make_float4(s.w[1][2], s.w[2][2], A01, A11);
+            sSh[2 * SL + sl] = make_float4(A21, A02, A12, A22);
             sSp[sl * 3 + 0] = make_float4(s.w[0][0], b0, b1, b2);
             sSp[sl * 3 + 1] = make_float4(s.w[1][0], b0 + A00, b1 + A10, b2 + A20);
             sSp[sl * 3 + 2] = make_float4(s.w[2][0], b0 + 2.f * A00, b1 + 2.f * A10, b2 + 2.f * A20);
@@ -176,10 +185,10 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
         __syncthreads();
         if (r + 1 < rounds) issue(r + 1);
         {
-          const int nk = min(P2G_R, S.cnt[cell] - r * P2G_R);
+          const int nk = min(R, S.cnt[cell] - r * R);
           for (int k = 0; k < nk; k++) {
-            const int sl = cell * P2G_R + k;
-            const float4 h0 = sSh[sl], h1 = sSh[256 + sl], h2 = sSh[512 + sl];
+            const int sl = cell * R + k;
+            const float4 h0 = sSh[sl], h1 = sSh[SL + sl], h2 = sSh[2 * SL + sl];
             const float4 pl = sSp[sl * 3 + plane];
             const float wy[3] = {h0.x, h0.y, h0.z};
             const float wz[3] = {h0.w, h1.x, h1.y};
@@ -213,8 +222,8 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
       sBuf[cell * 27 + plane * 9 + q] = a;
     }
     // touched neighbour blocks that do not exist yet are activated now (rare in steady state)
-    if (tid >= 160 && tid < 168) {
-      const int nbh = tid - 160;
+    if (tid >= 64 && tid < 72) {
+      const int nbh = tid - 64;
       if (!((S.touched >> nbh) & 1u))
         sNb[nbh] = nullptr;
       else if (sNb[nbh] == nullptr)
@@ -222,19 +231,20 @@ __global__ void __launch_bounds__(P2G_THREADS, 4) k_mpm_p2g(MpmDev M, int gen) {
     }
     __syncthreads();
     // pad node = sum of the partials of the <=27 cells whose stencil covers it; one vector red each
-    for (int nidx = tid; nidx < 216; nidx += P2G_THREADS) {
-      const int px = nidx / 36, py = (nidx / 6) % 6, pz = nidx % 6;
+    for (int nidx = tid; nidx < PXN * 36; nidx += NT) {
+      const int pxl = nidx / 36, py = (nidx / 6) % 6, pz = nidx % 6;  // pxl: x inside this CTA's cell range
       float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
-      // cell = node - (i,j,k) must lie in [0,4)^3: i in [max(0,px-3), min(2,px)] etc.
-      const int i0 = max(0, px - 3), i1 = min(2, px), j0 = max(0, py - 3), j1 = min(2, py), k0 = max(0, pz - 3), k1 = min(2, pz);
+      // cell = node - (i,j,k) must lie inside the CTA's cells
+      const int i0 = max(0, pxl - (XC - 1)), i1 = min(2, pxl), j0 = max(0, py - 3), j1 = min(2, py), k0 = max(0, pz - 3), k1 = min(2, pz);
       for (int i = i0; i <= i1; i++)
         for (int j = j0; j <= j1; j++) {
-          const float4 *row = &sBuf[((((px - i) << 4) | ((py - j) << 2)) + pz) * 27 + i * 9 + j * 3];
+          const float4 *row = &sBuf[((((pxl - i) << 4) | ((py - j) << 2)) + pz) * 27 + i * 9 + j * 3];
           for (int k = k0; k <= k1; k++) {
             const float4 rr = row[k - 27 * k];  // cell z = pz - k  ->  -27 k ; node k -> + k
             s4.x += rr.x, s4.y += rr.y, s4.z += rr.z, s4.w += rr.w;
           }
         }
+      const int px = pxl + XC * half;
       float4 *dst = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
       if (dst && (s4.x != 0.f || s4.y != 0.f || s4.z != 0.f || s4.w != 0.f)) red_add_v4(dst + (((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)), s4);
     }
