@@ -367,6 +367,16 @@ TI_DLL_EXPORT int32_t b2_mpm_stats(B2Mpm mpm, double *out_host);
 TI_DLL_EXPORT int32_t b2_mpm_set_profiling(B2Mpm mpm, int32_t on);
 TI_DLL_EXPORT int32_t b2_mpm_phase_ms(B2Mpm mpm, float *out_host6);
 
+/* slab decomposition (new: no reference counterpart). Messages are device buffers
+   {u32 count; u32 pad[3]; records[cap]}: block records are 1040 B {i32 key; pad; float4 cells[64]},
+   particle records 80 B {float4 x4; u32 id; pad}. All calls are asynchronous; counts stay on the device. */
+TI_DLL_EXPORT int32_t b2_mpm_pack_blocks(B2Mpm mpm, int32_t block_layer_i, void *buf_dev, int64_t cap_records);
+TI_DLL_EXPORT int32_t b2_mpm_unpack_blocks(B2Mpm mpm, const void *buf_dev, int64_t cap_records, int32_t mode); /* 0 activate+add, 1 overwrite-if-active */
+TI_DLL_EXPORT int32_t b2_mpm_extract_migrants(B2Mpm mpm, int32_t side, void *buf_dev, int64_t cap_records);   /* 0: below slab_lo, 1: at/above slab_hi */
+TI_DLL_EXPORT int32_t b2_mpm_insert_records(B2Mpm mpm, const void *buf_dev, int64_t cap_records);
+/* compact copy of the live particles + their ids; returns how many (synchronises) */
+TI_DLL_EXPORT int64_t b2_mpm_export(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *J_any, int32_t *ids_any, int64_t cap);
+
 #ifdef __cplusplus
 }
 #endif

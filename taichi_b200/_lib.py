@@ -166,6 +166,11 @@ SIGNATURES = {
     "b2_mpm_stats": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "b2_mpm_set_profiling": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b2_mpm_phase_ms": (C.c_int32, [C.c_void_p, f32p]),
+    "b2_mpm_pack_blocks": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]),
+    "b2_mpm_unpack_blocks": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32]),
+    "b2_mpm_extract_migrants": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]),
+    "b2_mpm_insert_records": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64]),
+    "b2_mpm_export": (C.c_int64, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
 }
 
 

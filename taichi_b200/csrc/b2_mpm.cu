@@ -524,6 +524,8 @@ __global__ void __launch_bounds__(G2P_PLAIN_THREADS, 3) k_mpm_g2p(MpmDev M, int 
   }
 }
 
+#include "b2_mpm_slab.cuh"
+
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
@@ -898,5 +900,81 @@ int32_t b2_mpm_phase_ms(B2Mpm m, float *out) {
   if (!m || !out) return -1;
   for (int k = 0; k < 6; k++) out[k] = m->phase_count ? (float)(m->phase_sum[k] / (double)m->phase_count) : 0.f;
   return 0;
+}
+// ---- slab decomposition (see b2_mpm_slab.cuh) ----------------------------------------------
+static void check_msg(const void *buf, int64_t cap) {
+  require(buf != nullptr, TI_ERROR_ARGUMENT_NULL, "buf");
+  require(cap >= 0, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "cap");
+  require(b2_is_device_pointer(buf), TI_ERROR_INVALID_ARGUMENT, "message buffers must be device memory");
+}
+int32_t b2_mpm_pack_blocks(B2Mpm m, int32_t layer, void *buf, int64_t cap) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  check_msg(buf, cap);
+  cudaStream_t st = m->rt->stream();
+  B2_CUDA(cudaMemsetAsync(buf, 0, MPM_MSG_HEADER, st));
+  m->ensure_lists();
+  k_mpm_pack_blocks<<<m->rt->num_sms * 4, 256, 0, st>>>(m->M, layer, (u8 *)buf, cap);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_unpack_blocks(B2Mpm m, const void *buf, int64_t cap, int32_t mode) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  check_msg(buf, cap);
+  require(mode == 0 || mode == 1, TI_ERROR_INVALID_ARGUMENT, "mode");
+  k_mpm_unpack_blocks<<<m->rt->num_sms * 4, 256, 0, m->rt->stream()>>>(m->M, (const u8 *)buf, cap, mode);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  if (mode == 0 && m->sparse) m->lists_valid = false;  // may have activated blocks
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_extract_migrants(B2Mpm m, int32_t side, void *buf, int64_t cap) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  check_msg(buf, cap);
+  require(side == 0 || side == 1, TI_ERROR_INVALID_ARGUMENT, "side");
+  cudaStream_t st = m->rt->stream();
+  B2_CUDA(cudaMemsetAsync(buf, 0, MPM_MSG_HEADER, st));
+  k_mpm_extract_migrants<<<m->rt->num_sms * 4, 256, 0, st>>>(m->M, m->gen, side, (u8 *)buf, cap);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_insert_records(B2Mpm m, const void *buf, int64_t cap) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  check_msg(buf, cap);
+  k_mpm_insert_records<<<m->rt->grid_for(std::max<int64_t>(cap, 1), 256, 4), 256, 0, m->rt->stream()>>>(m->M, m->gen, (const u8 *)buf, cap);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  return 0;
+  B2_API_END(-1)
+}
+int64_t b2_mpm_export(B2Mpm m, float *x, float *v, float *C, float *J, int32_t *ids, int64_t cap) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  cudaStream_t st = m->rt->stream();
+  B2Staged sx, sv, sc, sj, si;
+  if (x) sx.init(x, (size_t)cap * 12, false, true, st);
+  if (v) sv.init(v, (size_t)cap * 12, false, true, st);
+  if (C) sc.init(C, (size_t)cap * 36, false, true, st);
+  if (J) sj.init(J, (size_t)cap * 4, false, true, st);
+  if (ids) si.init(ids, (size_t)cap * 4, false, true, st);
+  unsigned long long *counter = (unsigned long long *)(m->M.stats + 7);
+  B2_CUDA(cudaMemsetAsync(counter, 0, 8, st));
+  k_mpm_export<<<m->rt->num_sms * 8, 256, 0, st>>>(m->M, m->gen, sx.as<float>(), sv.as<float>(), sc.as<float>(), sj.as<float>(), si.as<int>(), cap, counter);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  unsigned long long n = 0;
+  B2_CUDA(cudaMemcpyAsync(&n, counter, 8, cudaMemcpyDeviceToHost, st));
+  m->rt->sync();
+  sx.finish(), sv.finish(), sc.finish(), sj.finish(), si.finish();
+  return (int64_t)n;
+  B2_API_END(-1)
 }
 }  // extern "C"

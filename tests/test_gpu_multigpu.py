@@ -1,0 +1,118 @@
+"""Slab decomposition on the GPU: every CUDA kernel of the exchange path (pack/unpack block layers,
+migrant extraction/insertion, compact export) through the C ABI.
+ * several slabs emulated on ONE GPU in one process (lockstep phases, messages handed over by copy);
+ * with >= 2 GPUs: the same over torch.distributed / NCCL, one process per GPU.
+The decomposed result must match the single-domain CUDA solver and the CPU oracle."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from _b2 import have_gpu, runtime
+from test_gpu_mpm import oracle_mpm3d
+
+pytestmark = pytest.mark.gpu
+N_GRID, DT, STEPS, N = 64, 2e-4, 16, 30000
+
+
+def cloud():
+    rng = np.random.default_rng(8)
+    x = (rng.random((N, 3)) * np.array([0.6, 0.3, 0.3]) + np.array([0.2, 0.3, 0.3])).astype(np.float32)
+    v = np.tile(np.array([3.0, -1.0, 0.5], np.float32), (N, 1))
+    v[N // 2:, 0] *= -1
+    return x, v, np.zeros((N, 3, 3), np.float32), np.ones(N, np.float32), np.arange(N, dtype=np.int32)
+
+
+def get_rt():
+    import taichi_b200 as tb
+    r = tb.Runtime.__new__(tb.Runtime)
+    r.handle = runtime()
+    r.memories = []
+    return r
+
+
+def compare(parts, ref):
+    x = np.concatenate([p[0] for p in parts])
+    v = np.concatenate([p[1] for p in parts])
+    J = np.concatenate([p[3] for p in parts])
+    ids = np.concatenate([p[4] for p in parts])
+    assert len(ids) == N and len(np.unique(ids)) == N
+    o = np.argsort(ids)
+    xs, vs, Cs, Js = ref
+    assert np.allclose(x[o], xs, rtol=0, atol=2e-6)
+    assert np.allclose(v[o], vs, rtol=1e-4, atol=2e-4)
+    assert np.allclose(J[o], Js, rtol=1e-4)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_emulated_slabs_on_one_gpu(world):
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    from taichi_b200 import multigpu as mg
+    rt = get_rt()
+    x, v, Cm, J, ids = cloud()
+    owner = mg.partition_particles(x, N_GRID, world)
+    slabs, drivers = [], []
+    for r in range(world):
+        lo, hi = mg.slab_bounds(N_GRID // 4, world, r)
+        s = mg.CudaSlab(rt, N_GRID, N, DT, lo, hi)
+        sel = owner == r
+        s.set_particles(x[sel], v[sel], Cm[sel], J[sel], ids[sel])
+        slabs.append(s)
+        drivers.append(mg.SlabDriver(s, r, world, cap_blocks=1024, cap_particles=8192))
+    before = [len(s.export(N)[4]) for s in slabs]
+    mg.substep_local(drivers, STEPS)
+    parts = [s.export(N) for s in slabs]
+    assert [len(p[4]) for p in parts] != before                   # particles migrated
+    for s, p in zip(slabs, parts):                                # ownership invariant
+        if len(p[0]):
+            bx = (p[0][:, 0] * np.float32(N_GRID) - np.float32(0.5)).astype(np.int32) >> 2
+            assert ((bx >= s.lo) & (bx < s.hi)).all()
+    xs, vs, Cs, Js, *_ = oracle_mpm3d(N_GRID, x, v, Cm, J, DT, STEPS)
+    compare(parts, (xs, vs, Cs, Js))
+    buf = C.create_string_buffer(256)
+    from taichi_b200 import _lib as L
+    assert L.lib.b2_check_runtime_error(rt.handle, buf, 256) == 0, buf.value
+    for s in slabs:
+        s.destroy()
+
+
+def _nccl_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import torch
+    import torch.distributed as dist
+    import taichi_b200 as tb
+    from taichi_b200 import multigpu as mg
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    rt = tb.Runtime(rank, device_memory_GB=1)
+    x, v, Cm, J, ids = cloud()
+    owner = mg.partition_particles(x, N_GRID, world)
+    lo, hi = mg.slab_bounds(N_GRID // 4, world, rank)
+    s = mg.CudaSlab(rt, N_GRID, N, DT, lo, hi)
+    sel = owner == rank
+    s.set_particles(x[sel], v[sel], Cm[sel], J[sel], ids[sel])
+    d = mg.SlabDriver(s, rank, world, cap_blocks=1024, cap_particles=8192)
+    mg.substep_distributed(d, STEPS)
+    torch.cuda.synchronize()
+    gathered = [None] * world
+    dist.all_gather_object(gathered, s.export(N))
+    if rank == 0:
+        torch.save(gathered, out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_nccl_two_gpus(tmp_path):
+    import torch
+    if not have_gpu() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "g.pt")
+    mp.spawn(_nccl_worker, args=(2, 29700 + os.getpid() % 1000, out), nprocs=2, join=True)
+    x, v, Cm, J, ids = cloud()
+    xs, vs, Cs, Js, *_ = oracle_mpm3d(N_GRID, x, v, Cm, J, DT, STEPS)
+    compare(torch.load(out, weights_only=False), (xs, vs, Cs, Js))
