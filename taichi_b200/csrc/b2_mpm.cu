@@ -716,6 +716,7 @@ void B2Mpm_t::g2p() {
       k_mpm_g2p_bls<256, 3><<<rt->num_sms * 3, 256, 0, st>>>(M, gen);
     else if (nt == 64)
       k_mpm_g2p_bls<64, 12><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
+
     else
       k_mpm_g2p_bls<128, 6><<<rt->num_sms * 6, 128, 0, st>>>(M, gen);
   }

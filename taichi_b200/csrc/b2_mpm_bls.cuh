@@ -32,28 +32,41 @@ __device__ __forceinline__ int mpm_cell_of(const MpmDev &M, const float4 p0) {
 // Sorts particles [q0, q0+n) of the bin. All threads of the CTA must call it. NT = blockDim.x.
 // On return (after its final barrier): S.cnt / S.start / S.perm / S.maxcnt / S.touched are valid;
 // S.start[64] = number of live particles in the pass.
-template <int NT>
+template <int NT, int U>
 __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u32 *key, u32 q0, int n, int cbase = 0, int ncell = 64) {  // key[MPM_SB]: cell << 16 | rank
   const int tid = threadIdx.x;
   if (tid < 65) S.cnt[tid] = 0;
   __syncthreads();
   u32 tmask = 0;
-  for (int t = tid; t < n; t += NT) {
-    const u32 q = q0 + t;
-    const float4 p0 = ((const float4 *)S.chunk[q / MPM_CHUNK])[q % MPM_CHUNK];
-    int c = 64;
-    if (p0.x != MPM_TOMB) {
-      c = mpm_cell_of(M, p0);
-      const int h = (((c >> 4) & 3) >> 1) << 2 | (((c >> 2) & 3) >> 1) << 1 | ((c & 3) >> 1);
-      // neighbour blocks {0,1}^3 whose nodes this particle's stencil reaches
-      c -= cbase;  // cells outside this CTA's window sort into the dead bin
-      if ((unsigned)c >= (unsigned)ncell)
-        c = 64;
-      else
-        tmask |= (h == 0) ? 0x01u : (h == 1) ? 0x03u : (h == 2) ? 0x05u : (h == 3) ? 0x0fu : (h == 4) ? 0x11u : (h == 5) ? 0x33u : (h == 6) ? 0x55u : 0xffu;
+  for (int tb = tid; tb < n; tb += U * NT) {  // U independent 16-B loads in flight per thread
+    float4 pv[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int t = tb + u * NT;
+      if (t < n) {
+        const u32 q = q0 + t;
+        pv[u] = ((const float4 *)S.chunk[q / MPM_CHUNK])[q % MPM_CHUNK];
+      }
     }
-    const int r = atomicAdd(&S.cnt[c], 1);
-    key[t] = ((u32)c << 16) | (u32)r;
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int t = tb + u * NT;
+      if (t >= n) break;
+      const float4 p0 = pv[u];
+      int c = 64;
+      if (p0.x != MPM_TOMB) {
+        c = mpm_cell_of(M, p0);
+        const int h = (((c >> 4) & 3) >> 1) << 2 | (((c >> 2) & 3) >> 1) << 1 | ((c & 3) >> 1);
+        // neighbour blocks {0,1}^3 whose nodes this particle's stencil reaches
+        c -= cbase;  // cells outside this CTA's window sort into the dead bin
+        if ((unsigned)c >= (unsigned)ncell)
+          c = 64;
+        else
+          tmask |= (h == 0) ? 0x01u : (h == 1) ? 0x03u : (h == 2) ? 0x05u : (h == 3) ? 0x0fu : (h == 4) ? 0x11u : (h == 5) ? 0x33u : (h == 6) ? 0x55u : 0xffu;
+      }
+      const int r = atomicAdd(&S.cnt[c], 1);
+      key[t] = ((u32)c << 16) | (u32)r;
+    }
   }
   tmask = __reduce_or_sync(0xffffffffu, tmask);
   if ((tid & 31) == 0 && tmask) atomicOr(&S.touched, tmask);
@@ -132,12 +145,13 @@ __global__ void __launch_bounds__(192 / H, 4 * H) k_mpm_p2g(MpmDev M, int gen) {
       sNb[nbh] = mpm_block_ptr<false>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
     }
     float4 acc[9];
-#pragma unroll
-    for (int q = 0; q < 9; q++) acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-
     for (u32 q0 = 0; q0 < total; q0 += MPM_SB) {
       const int n = (int)min((u32)MPM_SB, total - q0);
-      mpm_sort_pass<NT>(M, S, sKey, q0, n, half * NC, NC);  // (first barrier inside also publishes S.chunk)
+      mpm_sort_pass<NT, 2>(M, S, sKey, q0, n, half * NC, NC);  // (first barrier inside also publishes S.chunk)
+      if (q0 == 0) {  // accumulators start after the first sort pass (keeps them out of its register budget)
+#pragma unroll
+        for (int q = 0; q < 9; q++) acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       const int rounds = (S.maxcnt + R - 1) / R;
       // loaders: slot (cell c, s) takes the (r*R + s)-th particle of cell c.  The four planes of
       // round r+1 are fetched with cp.async while stage 1 of round r runs.
@@ -296,7 +310,7 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
     }
     for (u32 q0 = 0; q0 < total; q0 += MPM_SB) {
       const int n = (int)min((u32)MPM_SB, total - q0);
-      mpm_sort_pass<G2P_THREADS>(M, S, sKey, q0, n);
+      mpm_sort_pass<G2P_THREADS, 4>(M, S, sKey, q0, n);
       const int nlive = S.start[64];
       if (nlive == 0) continue;  // uniform
       if (tid == 0) {
@@ -334,17 +348,28 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
         sOut[c - c0] = mpm_chunk_ptr(M, g1, id1);
       }
       __syncthreads();
+      float4 np0 = make_float4(0.f, 0.f, 0.f, 1.f);
+      u32 nid = 0;
+      if (tid < nlive) {  // software pipeline: particle t0+NT is loaded while particle t0 is computed
+        const u32 q = q0 + S.perm[tid];
+        const u8 *ch = S.chunk[q / MPM_CHUNK];
+        np0 = ((const float4 *)ch)[q % MPM_CHUNK];
+        nid = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[q % MPM_CHUNK];
+      }
       for (int t0 = 0; t0 < nlive; t0 += G2P_THREADS) {
         const int t = t0 + tid;
         const bool valid = t < nlive;
         float4 o0 = make_float4(0.f, 0.f, 0.f, 1.f), o1 = make_float4(0.f, 0.f, 0.f, 0.f), o2 = o1, o3 = o1;
         int nkey = -1;
-        u32 id = 0;
-        if (valid) {
-          const u32 q = q0 + S.perm[t];
+        const float4 p0 = np0;
+        u32 id = nid;
+        if (t + G2P_THREADS < nlive) {
+          const u32 q = q0 + S.perm[t + G2P_THREADS];
           const u8 *ch = S.chunk[q / MPM_CHUNK];
-          const float4 p0 = ((const float4 *)ch)[q % MPM_CHUNK];
-          id = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[q % MPM_CHUNK];
+          np0 = ((const float4 *)ch)[q % MPM_CHUNK];
+          nid = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[q % MPM_CHUNK];
+        }
+        if (valid) {
           MpmStencil s;
           mpm_stencil(M, p0.x, p0.y, p0.z, s);
           float v0 = 0.f, v1 = 0.f, v2 = 0.f;

@@ -236,7 +236,8 @@ def test_bls_activate_halo_mode(rt):
         assert np.array_equal(s.active_blocks(), expected_blocks(x0, n_grid, halo=halo))
         out[halo] = s.grid_to_numpy()
         s.destroy()
-    assert np.allclose(out[False], out[True], rtol=1e-6, atol=1e-12)  # values identical: only zeros are added
+    # values identical up to the order of the fp32 reductions (only zeros are added by the halo mode)
+    assert np.allclose(out[False], out[True], rtol=1e-5, atol=1e-6 * np.abs(out[False]).max())
 
 
 def test_bls_equals_plain(rt):
