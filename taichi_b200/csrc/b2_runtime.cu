@@ -515,6 +515,76 @@ __global__ void __launch_bounds__(256) k_listgen_nonroot(B2TreeDev *T, int pid, 
   }
 }
 
+// Bitmasked parent whose child containers are single Elements (static child, <= 1024 cells): one
+// WARP per parent Element.  Lane l owns mask word l: popc -> warp prefix sum -> one atomicAdd per
+// warp -> every lane writes the Elements of its set bits (the "warp-ballot prefix-sum listgen";
+// the reference takes one atomic per Element, runtime.cpp:451-456,1367-1379).
+__global__ void __launch_bounds__(256) k_listgen_bitmasked(B2TreeDev *T, int pid, int cid) {
+  const B2SNodeDev &ps = T->s[pid];
+  const B2SNodeDev &cs = T->s[cid];
+  B2CList *PL = T->lists[pid];
+  B2CList *CL = T->lists[cid];
+  const u32 np = PL->count;
+  const int lane = threadIdx.x & 31;
+  const u32 wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+  const int ncc = (int)cs.num_cells;
+  // work unit = (parent Element, run of S mask words); S shrinks when there are few parents so that
+  // the whole chip stays busy (np = 200 containers -> one word per warp, np >= #warps -> 32 words)
+  int S = 32;
+  while (S > 1 && (unsigned long long)np * (32 / S) < 2ull * nw) S >>= 1;
+  const u32 upe = 32 / S;  // units per Element (an Element spans <= 1024 cells = 32 words)
+  for (u32 u = wid; u < np * upe; u += nw) {
+    const u32 e = u / upe;
+    const B2Element E = *(const B2Element *)b2_list_get(PL, e);
+    const u32 *mask = b2_mask_words(ps, E.node);
+    {
+      const int w0 = (E.lo >> 5) + (int)(u % upe) * S;
+      const int w = w0 + lane;
+      u32 word = 0;
+      if (lane < S && w * 32 < E.hi) {
+        word = mask[w];
+        const int first = w * 32;
+        if (first < E.lo) word &= ~0u << (E.lo - first);
+        if (first + 32 > E.hi) word &= ~0u >> (first + 32 - E.hi);
+      }
+      const int cnt = __popc(word);
+      int inc = cnt;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int tv = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += tv;
+      }
+      const int total = __shfl_sync(0xffffffffu, inc, 31);
+      if (total == 0) continue;
+      u32 base = 0;
+      if (lane == 31) base = atomicAdd(&CL->count, (u32)total);
+      base = __shfl_sync(0xffffffffu, base, 31);
+      // cooperative expansion: lane handles output ranks lane, lane+32, ... so that the 64-byte
+      // Element stores of a warp are contiguous; rank k -> (word holding it, bit inside the word)
+      for (int k0 = 0; k0 < total; k0 += 32) {
+        const int k = k0 + lane;
+        const int kk = k < total ? k : total - 1;
+        int l = 0;  // smallest lane with inc > kk (binary search over the inclusive prefix)
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+          const int probe = __shfl_sync(0xffffffffu, inc, l + step - 1);
+          if (probe <= kk) l += step;
+        }
+        const u32 wsel = __shfl_sync(0xffffffffu, word, l);
+        const int excl = __shfl_sync(0xffffffffu, inc - cnt, l);
+        if (k < total) {
+          const int bit = (int)__fns(wsel, 0, kk - excl + 1);
+          const int j = (w0 + l) * 32 + bit;
+          int rc[B2_MAX_AXES];
+          b2_refine(ps, E.pcoord, rc, j);
+          B2Element *dst = (B2Element *)b2_list_slot(T->pool, CL, base + (u32)k);
+          if (dst) b2_store_element(dst, E.node + ps.cell_size * j + cs.offset_in_parent_cell, 0, ncc, rc);
+        }
+      }
+    }
+  }
+}
+
 void B2Tree_t::listgen_async(int target) {
   check_snode(target, "listgen");
   if (s[target].type == B2T_PLACE) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "listgen: target is a place");
@@ -528,8 +598,13 @@ void B2Tree_t::listgen_async(int target) {
   }
   for (int l = 2; l < P.n; l++) {
     // parent elements in flight: one CTA each, capped at a few waves of the chip
-    int block = (int)std::min<int64_t>(256, std::max<int64_t>(32, roundup(std::min<int64_t>(s[P.id[l - 1]].num_cells, 1024), 32)));
-    k_listgen_nonroot<<<rt->num_sms * 16, block, 0, st>>>(dev, P.id[l - 1], P.id[l]);
+    const B2SNodeHost &par = s[P.id[l - 1]], &ch = s[P.id[l]];
+    if (par.type == B2T_BITMASKED && ch.type != B2T_DYNAMIC && ch.num_cells <= B2_LISTGEN_MAX_ELEMENT) {
+      k_listgen_bitmasked<<<rt->num_sms * 8, 256, 0, st>>>(dev, P.id[l - 1], P.id[l]);
+    } else {
+      int block = (int)std::min<int64_t>(256, std::max<int64_t>(32, roundup(std::min<int64_t>(par.num_cells, 1024), 32)));
+      k_listgen_nonroot<<<rt->num_sms * 16, block, 0, st>>>(dev, P.id[l - 1], P.id[l]);
+    }
     rt->count_launch();
   }
   B2_CUDA(cudaGetLastError());
