@@ -54,27 +54,35 @@ def make_cloud(name, n_particles, seed, rank=0):
 
 
 def make_slab_cloud(world, rank, per_rank, n_grid):
-    """3*world balls (radius = 41 cells, ~8 particles/cell like C3) strung along i so that
-    every slab is populated and the balls straddle slab boundaries; each rank builds only the balls that
-    can reach its slab and keeps the particles it owns.  v = (0.5,-1,0): migration across slabs."""
+    """SURVEY 8d C5 (weak-scaling form): every rank owns exactly ~per_rank particles: one ball in the
+    middle of its slab plus half of a ball sitting ON each interior slab boundary (radius 41 cells,
+    like C3's 0.08 at 512^3), so ghost-layer exchange and migration are exercised at every boundary
+    and the load is even.  v = (0.5,-1,0): particles drift across slab boundaries."""
     from taichi_b200 import multigpu as mg
     nb = n_grid // 4
-    lo, hi = mg.slab_bounds(nb, world, rank)
-    nballs = 3 * world
-    per_ball = per_rank * world // nballs
     radius = 41.0 / n_grid
-    xs, ids = [], []
-    for k in range(nballs):
-        cx = 0.1 + 0.8 * (k + 0.5) / nballs
-        if (cx + radius + 2.0 / n_grid) * nb < lo or (cx - radius - 2.0 / n_grid) * nb > hi:
-            continue
-        rng = np.random.default_rng(5000 + k)
-        d = rng.standard_normal((per_ball, 3)).astype(np.float32)
+    n_b = per_rank // 4                      # particles each side receives from one boundary ball
+
+    def ball(seed, n, cx, cy, id0):
+        rng = np.random.default_rng(seed)
+        d = rng.standard_normal((n, 3)).astype(np.float32)
         d /= np.linalg.norm(d, axis=1, keepdims=True)
-        r = radius * rng.random(per_ball, dtype=np.float32) ** (1.0 / 3.0)
-        c = np.array([cx, 0.3 + 0.2 * (k % 3), 0.5], np.float32)
-        xs.append((c + d * r[:, None]).astype(np.float32))
-        ids.append(np.arange(k * per_ball, (k + 1) * per_ball, dtype=np.int32))
+        r = radius * rng.random(n, dtype=np.float32) ** (1.0 / 3.0)
+        return (np.array([cx, cy, 0.5], np.float32) + d * r[:, None]).astype(np.float32), np.arange(id0, id0 + n, dtype=np.int32)
+
+    lo, hi = mg.slab_bounds(nb, world, rank)
+    n_bound = (rank > 0) + (rank + 1 < world)
+    n_c = per_rank - n_bound * n_b
+    stride = 2 * per_rank                    # id space reserved per rank / boundary
+    xs, ids = [], []
+    x, i = ball(7000 + rank, n_c, 0.5 * (lo + hi) / nb, 0.45, rank * stride)
+    xs.append(x), ids.append(i)
+    for side, bnd in ((0, lo), (1, hi)):
+        if (side == 0 and rank == 0) or (side == 1 and rank + 1 == world):
+            continue
+        bidx = rank if side == 1 else rank - 1          # boundary index = lower rank
+        x, i = ball(9000 + bidx, 2 * n_b, bnd / nb, 0.6, bidx * stride + per_rank)
+        xs.append(x), ids.append(i)
     x, ids = np.concatenate(xs), np.concatenate(ids)
     keep = mg.partition_particles(x, n_grid, world) == rank
     x, ids = np.ascontiguousarray(x[keep]), np.ascontiguousarray(ids[keep])
@@ -164,7 +172,7 @@ def run_reference(args):
             "config": {"workload": desc, "n_grid": n_grid, "particles": n_p, "substeps_per_step": 1, "dt": dt},
             "cpu_baseline": {"value": val, "unit": "particle-updates/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "particle-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args):
@@ -264,7 +272,7 @@ def run_ours(args):
         if world == 1 and not args.no_cpu:
             cv, cms, threads, sample = cpu_reference(args.workload, 1, 1)
             line["cpu_baseline"] = {"value": cv, "unit": "particle-updates/s", "cores": threads, "kind": "port", "sample": sample}
-        print(json.dumps(line))
+        emit(line)
     solver.destroy()
     if world > 1:
         dist.destroy_process_group()
@@ -286,7 +294,7 @@ def run_slabs(args, world, rank, local):
     n_local = len(x)
     hx, hv, hC, hJ, hid = (torch.from_numpy(a).pin_memory() for a in (x, v, Cm, J, ids))
     slab.set_particles(hx, hv, hC, hJ, hid)
-    drv = mg.SlabDriver(slab, rank, world, cap_blocks=8192, cap_particles=131072)
+    drv = mg.NativeSlabDriver(slab, rank, world, cap_blocks=8192, cap_particles=131072)
     ntot = torch.tensor([n_local], device="cuda", dtype=torch.int64)
     dist.all_reduce(ntot)
     n_total = int(ntot.item())
@@ -308,18 +316,19 @@ def run_slabs(args, world, rank, local):
         return float(ms.item())
 
     def step_resident():
-        mg.substep_distributed(drv, SUBSTEPS)
+        drv.substep(SUBSTEPS)
 
     hx_out = np.empty((2 * per_rank, 3), np.float32)
 
     def step_e2e():
         slab.set_particles(hx, hv, hC, hJ, hid)
-        mg.substep_distributed(drv, SUBSTEPS)
+        drv.substep(SUBSTEPS)
         from taichi_b200.mpm import _ptr
         tb._lib.lib.b2_mpm_export(slab.handle, _ptr(hx_out), None, None, None, None, 2 * per_rank)
 
     for _ in range(args.warmup):
         step_resident()
+    drv.tune()  # messages shrink from the fixed capacity to 2x the observed record counts
     l0 = rt.launches()
     with ClockSampler(local) as clocks:
         total_ms = timed(step_resident, args.steps)
@@ -342,7 +351,7 @@ def run_slabs(args, world, rank, local):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "n_grid": n_grid, "particles_total": n_total, "substeps_per_step": SUBSTEPS, "dt": dt,
                    "l2": "particle state per GPU (>=512 MiB/substep) exceeds the 126 MB L2: no flush needed",
-                   "parallelism": f"slab{world}: 1 process/GPU, NCCL P2P ghost-layer + migrant exchange, no data-path collective"},
+                   "parallelism": f"slab{world}: 1 process/GPU, ncclSend/ncclRecv ghost-layer + migrant exchange enqueued from C++, no data-path collective"},
         "e2e": {"value": e2e_value, "unit": "particle-updates/s", "h2d_bytes_per_step": int(n_total * 68), "d2h_bytes_per_step": int(n_total * 12)},
         "gpu_launches": int(launches) * world,
         "clocks": clocks.summary(),
@@ -350,12 +359,25 @@ def run_slabs(args, world, rank, local):
                      "traffic": None, "peak_kind": peak_kind, "alg_bytes_per_launch": sub_alg, "ms_per_launch": sub_ms},
     }
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     slab.destroy()
     dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; fd 1 itself is routed to stderr for the whole run
+    because libraries (NCCL's version banner) write to it directly."""
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=4)

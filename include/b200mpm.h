@@ -271,6 +271,8 @@ typedef struct B2SNodeDesc {
 
 typedef struct B2Tree_t *B2Tree;
 typedef struct B2Mpm_t *B2Mpm;
+typedef struct B2Comm_t *B2Comm; /* NCCL communicator of the slab layer */
+typedef struct B2Slab_t *B2Slab; /* one rank's slab driver */
 
 /* Program::add_snode_tree + materialize_snode_tree (program.cpp:238-255,
    llvm_runtime_executor.cpp:391-469): layout, zeroed root buffer, one element list per SNode,
@@ -376,6 +378,20 @@ TI_DLL_EXPORT int32_t b2_mpm_extract_migrants(B2Mpm mpm, int32_t side, void *buf
 TI_DLL_EXPORT int32_t b2_mpm_insert_records(B2Mpm mpm, const void *buf_dev, int64_t cap_records);
 /* compact copy of the live particles + their ids; returns how many (synchronises) */
 TI_DLL_EXPORT int64_t b2_mpm_export(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *J_any, int32_t *ids_any, int64_t cap);
+
+/* Native slab driver: the whole decomposed substep (kernels + ncclSend/ncclRecv over NVLink) is
+   enqueued from C++ on the runtime's stream; no host synchronisation.  NCCL is bound at run time
+   (dlopen libnccl.so.2).  Rank 0 creates the id and shares its 128 bytes with the other ranks
+   (e.g. torch.distributed.broadcast), then every rank calls b2_comm_init. */
+TI_DLL_EXPORT TiRuntime b2_mpm_runtime(B2Mpm mpm);
+TI_DLL_EXPORT int32_t b2_comm_unique_id(uint8_t *out128);
+TI_DLL_EXPORT B2Comm b2_comm_init(TiRuntime runtime, const uint8_t *id128, int32_t rank, int32_t world);
+TI_DLL_EXPORT void b2_comm_destroy(B2Comm comm);
+TI_DLL_EXPORT B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_t world, int32_t block_lo, int32_t block_hi,
+                                    int64_t cap_blocks, int64_t cap_particles);
+TI_DLL_EXPORT void b2_slab_destroy(B2Slab slab);
+TI_DLL_EXPORT int32_t b2_slab_substep(B2Slab slab, int32_t nsteps);
+TI_DLL_EXPORT int32_t b2_slab_tune(B2Slab slab); /* message sizes := 2x last counts (synchronises) */
 
 #ifdef __cplusplus
 }

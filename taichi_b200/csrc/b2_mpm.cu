@@ -776,6 +776,7 @@ B2Mpm b2_mpm_create(TiRuntime runtime, const B2MpmParams *params) {
 }
 void b2_mpm_destroy(B2Mpm mpm) { delete mpm; }
 B2Tree b2_mpm_tree(B2Mpm mpm) { return mpm ? mpm->tree : nullptr; }
+TiRuntime b2_mpm_runtime(B2Mpm mpm) { return mpm ? mpm->rt : nullptr; }
 int32_t b2_mpm_leaf_snode(B2Mpm mpm) { return mpm ? mpm->M.leaf_sid : -1; }
 
 int32_t b2_mpm_add_particles(B2Mpm m, int64_t n, const float *x, const float *v, const float *C, const float *J, const int32_t *ids) {

@@ -1,0 +1,257 @@
+// b2_slab.cu -- native driver of the slab-decomposed substep: the whole sequence
+//   clear, P2G | A: ghost layer -> r+1 | grid-op | B: owned layer -> r-1 | G2P | C: migrants <-> r+-1
+// is enqueued from C++ on ONE CUDA stream: the pack/unpack kernels of b2_mpm_slab.cuh plus
+// ncclSend/ncclRecv (NCCL over NVLink/NVSwitch) inside ncclGroupStart/End.  No Python and no host
+// synchronisation in the loop.  (New: the reference has no multi-GPU path, cuda_context.cpp:22.)
+// NCCL is bound at run time (dlopen of the libnccl.so.2 that torch already loaded), so the
+// library has no link-time dependency on it and single-GPU users never touch it.
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstring>
+
+#include "b2_host.h"
+
+typedef struct ncclComm *ncclComm_t;
+typedef struct {
+  char internal[128];
+} ncclUniqueId;
+enum { NCCL_UINT8 = 1 };
+
+struct NcclApi {
+  int (*GetUniqueId)(ncclUniqueId *);
+  int (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int);
+  int (*CommDestroy)(ncclComm_t);
+  int (*Send)(const void *, size_t, int, int, ncclComm_t, cudaStream_t);
+  int (*Recv)(void *, size_t, int, int, ncclComm_t, cudaStream_t);
+  int (*GroupStart)();
+  int (*GroupEnd)();
+  const char *(*GetErrorString)(int);
+  bool ok = false;
+};
+static NcclApi &nccl() {
+  static NcclApi a;
+  if (a.ok) return a;
+  void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) throw B2Error(TI_ERROR_NOT_SUPPORTED, std::string("libnccl.so.2 not found: ") + dlerror());
+#define B2_SYM(field, name)                                                    \
+  a.field = (decltype(a.field))dlsym(h, name);                                 \
+  if (!a.field) throw B2Error(TI_ERROR_NOT_SUPPORTED, std::string("NCCL symbol missing: ") + name)
+  B2_SYM(GetUniqueId, "ncclGetUniqueId");
+  B2_SYM(CommInitRank, "ncclCommInitRank");
+  B2_SYM(CommDestroy, "ncclCommDestroy");
+  B2_SYM(Send, "ncclSend");
+  B2_SYM(Recv, "ncclRecv");
+  B2_SYM(GroupStart, "ncclGroupStart");
+  B2_SYM(GroupEnd, "ncclGroupEnd");
+  B2_SYM(GetErrorString, "ncclGetErrorString");
+#undef B2_SYM
+  a.ok = true;
+  return a;
+}
+#define B2_NCCL(expr)                                                                                     \
+  do {                                                                                                    \
+    int _r = (expr);                                                                                      \
+    if (_r != 0) throw B2Error(TI_ERROR_INVALID_STATE, std::string(#expr) + ": " + nccl().GetErrorString(_r)); \
+  } while (0)
+
+struct B2Comm_t {
+  ncclComm_t comm = nullptr;
+  int rank = 0, world = 1;
+};
+
+static const int64_t BLOCK_REC = 1040, PART_REC = 80, HEADER = 16;
+
+struct B2Slab_t {
+  B2Mpm mpm;
+  B2Comm_t *comm;
+  TiRuntime_t *rt;
+  int rank, world, up, down, lo, hi;
+  int64_t cap_blocks, cap_particles;
+  // bytes actually put on the wire per message (<= capacity; see b2_slab_tune)
+  int64_t sendA_bytes, recvA_bytes, sendB_bytes, recvB_bytes, sendL_bytes, recvL_bytes, sendR_bytes, recvR_bytes;
+  uint8_t *sendA, *recvA, *sendB, *recvB, *sendL, *sendR, *recvL, *recvR;
+  uint32_t *sizes_dev;  // tune: 4 counts out, 4 counts in
+  std::vector<void *> allocs;
+  uint8_t *buf(int64_t bytes) {
+    void *p = nullptr;
+    B2_CUDA(cudaMalloc(&p, bytes));
+    B2_CUDA(cudaMemsetAsync(p, 0, bytes, b2_current_stream()));
+    allocs.push_back(p);
+    return (uint8_t *)p;
+  }
+};
+
+static void require(bool ok, TiError code, const char *msg) {
+  if (!ok) throw B2Error(code, msg);
+}
+static void ok0(int32_t rc) {
+  if (rc != 0) {
+    uint64_t n = 0;
+    ti_get_last_error(&n, nullptr);
+    std::string m(n ? n : 1, 0);
+    ti_get_last_error(&n, &m[0]);
+    throw B2Error(TI_ERROR_INVALID_STATE, m);
+  }
+}
+
+// one phase's messages: (send -> dst) and (recv <- src), both optional
+static void exchange(B2Slab_t *s, const void *send, int64_t sbytes, int dst, void *recv, int64_t rbytes, int src) {
+  if (dst < 0 && src < 0) return;
+  NcclApi &n = nccl();
+  cudaStream_t st = s->rt->stream();
+  B2_NCCL(n.GroupStart());
+  if (dst >= 0) B2_NCCL(n.Send(send, (size_t)sbytes, NCCL_UINT8, dst, s->comm->comm, st));
+  if (src >= 0) B2_NCCL(n.Recv(recv, (size_t)rbytes, NCCL_UINT8, src, s->comm->comm, st));
+  B2_NCCL(n.GroupEnd());
+}
+
+extern "C" {
+int32_t b2_comm_unique_id(uint8_t *out128) {
+  B2_API_BEGIN
+  require(out128 != nullptr, TI_ERROR_ARGUMENT_NULL, "out");
+  ncclUniqueId id;
+  B2_NCCL(nccl().GetUniqueId(&id));
+  memcpy(out128, id.internal, 128);
+  return 0;
+  B2_API_END(-1)
+}
+B2Comm b2_comm_init(TiRuntime rt, const uint8_t *id128, int32_t rank, int32_t world) {
+  B2_API_BEGIN
+  require(rt != nullptr && id128 != nullptr, TI_ERROR_ARGUMENT_NULL, "runtime/id");
+  require(world >= 1 && rank >= 0 && rank < world, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "rank/world");
+  B2_CUDA(cudaSetDevice(rt->device));
+  B2Comm_t *c = new B2Comm_t();
+  c->rank = rank, c->world = world;
+  ncclUniqueId id;
+  memcpy(id.internal, id128, 128);
+  B2_NCCL(nccl().CommInitRank(&c->comm, world, id, rank));
+  return c;
+  B2_API_END(nullptr)
+}
+void b2_comm_destroy(B2Comm c) {
+  if (!c) return;
+  if (c->comm) nccl().CommDestroy(c->comm);
+  delete c;
+}
+
+B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_t world, int32_t lo, int32_t hi, int64_t cap_blocks, int64_t cap_particles) {
+  B2_API_BEGIN
+  require(mpm != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  require(world == 1 || comm != nullptr, TI_ERROR_ARGUMENT_NULL, "comm");
+  require(cap_blocks > 0 && cap_particles > 0, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "capacities");
+  B2Slab_t *s = new B2Slab_t();
+  s->mpm = mpm, s->comm = comm, s->rank = rank, s->world = world, s->lo = lo, s->hi = hi;
+  s->rt = (TiRuntime_t *)b2_mpm_runtime(mpm);
+  s->up = rank + 1 < world ? rank + 1 : -1;
+  s->down = rank > 0 ? rank - 1 : -1;
+  s->cap_blocks = cap_blocks, s->cap_particles = cap_particles;
+  const int64_t bb = HEADER + cap_blocks * BLOCK_REC, pb = HEADER + cap_particles * PART_REC;
+  s->sendA = s->buf(bb), s->recvA = s->buf(bb), s->sendB = s->buf(bb), s->recvB = s->buf(bb);
+  s->sendL = s->buf(pb), s->sendR = s->buf(pb), s->recvL = s->buf(pb), s->recvR = s->buf(pb);
+  s->sizes_dev = (uint32_t *)s->buf(64);
+  s->sendA_bytes = s->recvA_bytes = s->sendB_bytes = s->recvB_bytes = bb;
+  s->sendL_bytes = s->recvL_bytes = s->sendR_bytes = s->recvR_bytes = pb;
+  return s;
+  B2_API_END(nullptr)
+}
+void b2_slab_destroy(B2Slab s) {
+  if (!s) return;
+  cudaStreamSynchronize(b2_current_stream());
+  for (void *p : s->allocs) cudaFree(p);
+  delete s;
+}
+
+int32_t b2_slab_substep(B2Slab s, int32_t nsteps) {
+  B2_API_BEGIN
+  require(s != nullptr, TI_ERROR_ARGUMENT_NULL, "slab");
+  B2Mpm m = s->mpm;
+  const int64_t cb = s->cap_blocks, cp = s->cap_particles;
+  // capacities the kernels enforce = what fits into the bytes that travel
+  const int64_t capA = (s->sendA_bytes - HEADER) / BLOCK_REC, capB = (s->sendB_bytes - HEADER) / BLOCK_REC;
+  const int64_t capL = (s->sendL_bytes - HEADER) / PART_REC, capR = (s->sendR_bytes - HEADER) / PART_REC;
+  (void)cb, (void)cp;
+  for (int it = 0; it < nsteps; it++) {
+    ok0(b2_mpm_clear_grid(m));
+    ok0(b2_mpm_p2g(m));
+    if (s->up >= 0) ok0(b2_mpm_pack_blocks(m, s->hi, s->sendA, capA));
+    exchange(s, s->sendA, s->sendA_bytes, s->up, s->recvA, s->recvA_bytes, s->down);
+    if (s->down >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvA, (s->recvA_bytes - HEADER) / BLOCK_REC, 0));
+    ok0(b2_mpm_grid_op(m));
+    if (s->down >= 0) ok0(b2_mpm_pack_blocks(m, s->lo, s->sendB, capB));
+    exchange(s, s->sendB, s->sendB_bytes, s->down, s->recvB, s->recvB_bytes, s->up);
+    if (s->up >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvB, (s->recvB_bytes - HEADER) / BLOCK_REC, 1));
+    ok0(b2_mpm_g2p(m));
+    if (s->down >= 0) ok0(b2_mpm_extract_migrants(m, 0, s->sendL, capL));
+    if (s->up >= 0) ok0(b2_mpm_extract_migrants(m, 1, s->sendR, capR));
+    if (s->world > 1) {  // both directions in one NCCL group
+      NcclApi &n = nccl();
+      cudaStream_t st = s->rt->stream();
+      B2_NCCL(n.GroupStart());
+      if (s->down >= 0) {
+        B2_NCCL(n.Send(s->sendL, (size_t)s->sendL_bytes, NCCL_UINT8, s->down, s->comm->comm, st));
+        B2_NCCL(n.Recv(s->recvL, (size_t)s->recvL_bytes, NCCL_UINT8, s->down, s->comm->comm, st));
+      }
+      if (s->up >= 0) {
+        B2_NCCL(n.Send(s->sendR, (size_t)s->sendR_bytes, NCCL_UINT8, s->up, s->comm->comm, st));
+        B2_NCCL(n.Recv(s->recvR, (size_t)s->recvR_bytes, NCCL_UINT8, s->up, s->comm->comm, st));
+      }
+      B2_NCCL(n.GroupEnd());
+    }
+    if (s->up >= 0) ok0(b2_mpm_insert_records(m, s->recvR, (s->recvR_bytes - HEADER) / PART_REC));
+    if (s->down >= 0) ok0(b2_mpm_insert_records(m, s->recvL, (s->recvL_bytes - HEADER) / PART_REC));
+  }
+  return 0;
+  B2_API_END(-1)
+}
+
+// Shrinks the bytes put on the wire to 2x the record counts of the last substep (+256 records,
+// never above the capacity); neighbours learn each other's sizes through one tiny exchange.
+// Synchronises.  An overflow after tuning raises the device-side error flag (bin overflow).
+int32_t b2_slab_tune(B2Slab s) {
+  B2_API_BEGIN
+  require(s != nullptr, TI_ERROR_ARGUMENT_NULL, "slab");
+  if (s->world == 1) return 0;
+  cudaStream_t st = s->rt->stream();
+  uint32_t cnt[4] = {0, 0, 0, 0};  // A (to up), B (to down), L (to down), R (to up)
+  const uint8_t *src[4] = {s->sendA, s->sendB, s->sendL, s->sendR};
+  for (int k = 0; k < 4; k++) B2_CUDA(cudaMemcpyAsync(&cnt[k], src[k], 4, cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  auto want = [&](uint32_t c, int64_t cap, int64_t rec) { return HEADER + std::min<int64_t>(cap, 2 * (int64_t)c + 256) * rec; };
+  uint32_t out[4];
+  int64_t sb[4] = {want(cnt[0], s->cap_blocks, BLOCK_REC), want(cnt[1], s->cap_blocks, BLOCK_REC), want(cnt[2], s->cap_particles, PART_REC),
+                   want(cnt[3], s->cap_particles, PART_REC)};
+  for (int k = 0; k < 4; k++) out[k] = (uint32_t)((sb[k] - HEADER) / (k < 2 ? BLOCK_REC : PART_REC));
+  // to up: {A, R}; to down: {B, L}.  from down: its {A, R}; from up: its {B, L}
+  uint32_t to_up[2] = {out[0], out[3]}, to_down[2] = {out[1], out[2]}, from_down[2] = {0, 0}, from_up[2] = {0, 0};
+  B2_CUDA(cudaMemcpyAsync(s->sizes_dev, to_up, 8, cudaMemcpyHostToDevice, st));
+  B2_CUDA(cudaMemcpyAsync(s->sizes_dev + 2, to_down, 8, cudaMemcpyHostToDevice, st));
+  NcclApi &n = nccl();
+  B2_NCCL(n.GroupStart());
+  if (s->up >= 0) {
+    B2_NCCL(n.Send(s->sizes_dev, 8, NCCL_UINT8, s->up, s->comm->comm, st));
+    B2_NCCL(n.Recv(s->sizes_dev + 4, 8, NCCL_UINT8, s->up, s->comm->comm, st));
+  }
+  if (s->down >= 0) {
+    B2_NCCL(n.Send(s->sizes_dev + 2, 8, NCCL_UINT8, s->down, s->comm->comm, st));
+    B2_NCCL(n.Recv(s->sizes_dev + 6, 8, NCCL_UINT8, s->down, s->comm->comm, st));
+  }
+  B2_NCCL(n.GroupEnd());
+  B2_CUDA(cudaMemcpyAsync(from_up, s->sizes_dev + 4, 8, cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaMemcpyAsync(from_down, s->sizes_dev + 6, 8, cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  s->sendA_bytes = sb[0], s->sendB_bytes = sb[1], s->sendL_bytes = sb[2], s->sendR_bytes = sb[3];
+  if (s->down >= 0) {  // down's {A, R} land in my recvA / recvL
+    s->recvA_bytes = HEADER + (int64_t)from_down[0] * BLOCK_REC;
+    s->recvL_bytes = HEADER + (int64_t)from_down[1] * PART_REC;
+  }
+  if (s->up >= 0) {  // up's {B, L} land in my recvB / recvR
+    s->recvB_bytes = HEADER + (int64_t)from_up[0] * BLOCK_REC;
+    s->recvR_bytes = HEADER + (int64_t)from_up[1] * PART_REC;
+  }
+  return 0;
+  B2_API_END(-1)
+}
+}  // extern "C"

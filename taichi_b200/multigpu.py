@@ -104,6 +104,50 @@ class CudaSlab:
             self.handle = None
 
 
+class NativeSlabDriver:
+    """The production driver: b2_slab_substep runs the whole decomposed substep from C++ (kernels +
+    ncclSend/ncclRecv on one stream).  torch.distributed is only used once, to hand rank 0's NCCL
+    unique id to the other ranks."""
+
+    def __init__(self, slab, rank, world, cap_blocks=8192, cap_particles=131072):
+        import torch
+        import torch.distributed as dist
+        L = slab.L
+        self.slab, self.L, self.lib = slab, L, L.lib
+        self.comm = None
+        if world > 1:
+            idt = torch.zeros(128, dtype=torch.uint8)
+            if rank == 0:
+                buf = (C.c_uint8 * 128)()
+                assert self.lib.b2_comm_unique_id(buf) == 0, L.last_error()
+                idt = torch.tensor(list(buf), dtype=torch.uint8)
+            idt = idt.cuda()
+            dist.broadcast(idt, 0)
+            raw = (C.c_uint8 * 128)(*idt.cpu().tolist())
+            self.comm = self.lib.b2_comm_init(self.lib.b2_mpm_runtime(slab.handle), raw, rank, world)
+            L.check()
+        self.handle = self.lib.b2_slab_create(slab.handle, self.comm, rank, world, slab.lo, slab.hi, cap_blocks, cap_particles)
+        L.check()
+
+    def substep(self, n=1):
+        rc = self.lib.b2_slab_substep(self.handle, n)
+        self.L.check()
+        assert rc == 0
+
+    def tune(self):
+        rc = self.lib.b2_slab_tune(self.handle)
+        self.L.check()
+        assert rc == 0
+
+    def destroy(self):
+        if self.handle:
+            self.lib.b2_slab_destroy(self.handle)
+            self.handle = None
+        if self.comm:
+            self.lib.b2_comm_destroy(self.comm)
+            self.comm = None
+
+
 class SlabDriver:
     """Host logic of one rank.  The substep is a fixed sequence of (compute, message) phases so that
     it can be driven by a torch.distributed communicator or stepped in lockstep in one process."""

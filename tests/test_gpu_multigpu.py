@@ -79,7 +79,25 @@ def test_emulated_slabs_on_one_gpu(world):
         s.destroy()
 
 
-def _nccl_worker(rank, world, port, out):
+def test_native_driver_world1_equals_plain_substep():
+    """b2_slab_substep with world = 1 is the plain substep sequence (no NCCL touched)."""
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    from taichi_b200 import multigpu as mg
+    rt = get_rt()
+    x, v, Cm, J, ids = cloud()
+    s = mg.CudaSlab(rt, N_GRID, N, DT, 0, N_GRID // 4)
+    s.set_particles(x, v, Cm, J, ids)
+    d = mg.NativeSlabDriver(s, 0, 1)
+    d.substep(STEPS)
+    d.tune()
+    xs, vs, Cs, Js, *_ = oracle_mpm3d(N_GRID, x, v, Cm, J, DT, STEPS)
+    compare([s.export(N)], (xs, vs, Cs, Js))
+    d.destroy()
+    s.destroy()
+
+
+def _nccl_worker(rank, world, port, out, native):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
     import torch
@@ -95,9 +113,17 @@ def _nccl_worker(rank, world, port, out):
     s = mg.CudaSlab(rt, N_GRID, N, DT, lo, hi)
     sel = owner == rank
     s.set_particles(x[sel], v[sel], Cm[sel], J[sel], ids[sel])
-    d = mg.SlabDriver(s, rank, world, cap_blocks=1024, cap_particles=8192)
-    mg.substep_distributed(d, STEPS)
+    if native:
+        d = mg.NativeSlabDriver(s, rank, world, cap_blocks=1024, cap_particles=8192)
+        d.substep(STEPS // 2)
+        d.tune()                      # shrink the messages to 2x the observed counts, then continue
+        d.substep(STEPS - STEPS // 2)
+    else:
+        d = mg.SlabDriver(s, rank, world, cap_blocks=1024, cap_particles=8192)
+        mg.substep_distributed(d, STEPS)
     torch.cuda.synchronize()
+    buf = C.create_string_buffer(256)
+    assert tb._lib.lib.b2_check_runtime_error(rt.handle, buf, 256) == 0, buf.value
     gathered = [None] * world
     dist.all_gather_object(gathered, s.export(N))
     if rank == 0:
@@ -106,13 +132,14 @@ def _nccl_worker(rank, world, port, out):
     dist.destroy_process_group()
 
 
-def test_nccl_two_gpus(tmp_path):
+@pytest.mark.parametrize("native", [True, False])
+def test_nccl_two_gpus(tmp_path, native):
     import torch
     if not have_gpu() or torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
     out = str(tmp_path / "g.pt")
-    mp.spawn(_nccl_worker, args=(2, 29700 + os.getpid() % 1000, out), nprocs=2, join=True)
+    mp.spawn(_nccl_worker, args=(2, 29700 + os.getpid() % 1000 + int(native), out, native), nprocs=2, join=True)
     x, v, Cm, J, ids = cloud()
     xs, vs, Cs, Js, *_ = oracle_mpm3d(N_GRID, x, v, Cm, J, DT, STEPS)
     compare(torch.load(out, weights_only=False), (xs, vs, Cs, Js))
