@@ -1,30 +1,58 @@
-"""Aggregate an `ncu --page source --csv --print-source sass,cuda` dump by CUDA source line.
-usage: python profiles/srcagg.py dump.csv [kernel-substring] [top]"""
-import csv, sys, collections
-path = sys.argv[1]; want = sys.argv[2] if len(sys.argv) > 2 else ""; top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
+"""Aggregate an `ncu --page source --csv --print-source sass,cuda` dump by (file, CUDA source line).
+usage: python profiles/srcagg.py dump.csv [kernel-substring] [top]
+Only the per-source-line summary rows are used (rows whose first column is a line number)."""
+import collections
+import csv
+import os
+import sys
+
+path = sys.argv[1]
+want = sys.argv[2] if len(sys.argv) > 2 else ""
+top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
 rows = list(csv.reader(open(path, errors="replace")))
-fn = None; hdr = None; agg = collections.defaultdict(lambda: [0, 0, 0, 0.0]); cur_file = ""
-srcline = {}
+fn = None
+hdr = None
+cur_file = ""
+agg = {}
 for r in rows:
-    if len(r) == 2 and r[0] == "Function Name": fn = r[1]; hdr = None; continue
-    if len(r) == 2 and r[0] == "File Path": cur_file = r[1]; continue
-    if r and r[0] == "Line No": hdr = r; continue
-    if hdr is None or fn is None or want not in fn or len(r) < 10 or r[0] == '': continue
-    d = dict(zip(hdr, r))
-    # sass rows carry "Source" twice: first col = cuda line text? use positional
-    try:
-        samples = int(r[hdr.index("# Samples")] or 0); inst = int(r[hdr.index("Instructions Executed")] or 0)
-    except ValueError:
+    if len(r) == 2 and r[0] == "File Path":
+        cur_file = os.path.basename(r[1])
         continue
-    key = (fn.split("(")[0], r[0])
-    a = agg[key]; a[0] += samples; a[1] += inst
-    try: a[2] += int(r[hdr.index("L1 Wavefronts Shared")] or 0)
-    except ValueError: pass
-    srcline.setdefault(key, r[1][:110])
-tot = collections.Counter(); toti = collections.Counter()
-for (f, l), a in agg.items(): tot[f] += a[0]; toti[f] += a[1]
-for f in tot:
-    print(f"== {f}: samples {tot[f]} warp-inst {toti[f]}")
-    items = sorted(((k, a) for k, a in agg.items() if k[0] == f), key=lambda x: -x[1][0])[:top]
-    for (ff, l), a in items:
-        print(f"  L{l:>5} samp {a[0]/max(tot[f],1)*100:5.1f}% inst {a[1]/max(toti[f],1)*100:5.1f}% smemwf {a[2]:>9}  {srcline[(ff,l)]}")
+    if len(r) == 2 and r[0] == "Function Name":
+        fn = r[1]
+        hdr = None
+        continue
+    if r and r[0] == "Line No":
+        hdr = r
+        col = {}
+        for i, h in enumerate(hdr):
+            col.setdefault(h, i)
+        continue
+    if hdr is None or fn is None or want not in fn or len(r) < 10 or not r[0].isdigit():
+        continue
+
+    def g(name):
+        try:
+            return int(r[col[name]] or 0)
+        except (ValueError, KeyError):
+            return 0
+    stalls = {h[6:]: g(h) for h in col if h.startswith("stall_") and "Not Issued" not in h}
+    agg[(fn.split("(")[0], cur_file, int(r[0]))] = dict(
+        samples=g("# Samples"), inst=g("Instructions Executed"), tinst=g("Thread Instructions Executed"),
+        wf=g("L1 Wavefronts Shared"), wfx=g("L1 Wavefronts Shared Excessive"), src=r[1][:90], stalls=stalls)
+by_fn = collections.defaultdict(list)
+for k, a in agg.items():
+    by_fn[k[0]].append((k, a))
+for f, items in by_fn.items():
+    ts = sum(a["samples"] for _, a in items) or 1
+    ti = sum(a["inst"] for _, a in items) or 1
+    tt = sum(a["tinst"] for _, a in items)
+    tw = sum(a["wf"] for _, a in items)
+    print(f"== {f}: samples {ts} warp-inst {ti} lanes/inst {tt / ti:.1f} smem wavefronts {tw}")
+    items.sort(key=lambda x: -x[1]["samples"])
+    for (ff, file, l), a in items[:top]:
+        st = sorted(a["stalls"].items(), key=lambda x: -x[1])[:2]
+        sts = " ".join(f"{n}:{v}" for n, v in st if v)
+        lanes = a["tinst"] / a["inst"] if a["inst"] else 0
+        print(f"  {file[:14]:14s}:{l:<4d} samp {a['samples'] / ts * 100:5.1f}% inst {a['inst'] / ti * 100:5.1f}% lanes {lanes:4.1f} "
+              f"wf {a['wf'] / max(tw, 1) * 100:4.1f}% (x{a['wfx']})  [{sts}]  {a['src']}")

@@ -333,6 +333,7 @@ __global__ void __launch_bounds__(256) k_mpm_grid_to_dense(MpmDev M, float4 *out
 }
 
 #include "b2_mpm_bls.cuh"
+#include "b2_mpm_p2g.cuh"
 
 // Plain path (ti.block_local off): every particle walks the SNode tree with activation and issues
 // one vector red per node -- the reference's non-BLS access pattern (K15) on the binned particles.
@@ -651,8 +652,40 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
     M.arena[g] = (u8 *)a;
     M.arena_next[g] = dalloc<u32>(4);
   }
+  M.dbg = getenv("B2_DBG") ? atoi(getenv("B2_DBG")) : 0;
   M.work_counter = dalloc<u32>(8);
   M.stats = dalloc<double>(8);
+  {  // P2G flush tasks: for every pad node the (cell, offset) partials that reach it, in groups of <= 9,
+     // biggest groups first (equal trip counts inside a warp); short groups are padded with the zero slot
+    static P2GTab tab;
+    std::vector<std::vector<unsigned short>> src(216);
+    for (int c = 0; c < 64; c++)
+      for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++)
+          for (int k = 0; k < 3; k++) {
+            const int px = (c >> 4) + i, py = ((c >> 2) & 3) + j, pz = (c & 3) + k;
+            src[(px * 6 + py) * 6 + pz].push_back((unsigned short)(c * 27 + i * 9 + j * 3 + k));
+          }
+    struct Task { int node; std::vector<unsigned short> s; };
+    std::vector<Task> tasks;
+    for (int nd = 0; nd < 216; nd++)
+      for (size_t o = 0; o < src[nd].size(); o += 9) {
+        Task t;
+        t.node = nd;
+        t.s.assign(src[nd].begin() + o, src[nd].begin() + std::min(src[nd].size(), o + 9));
+        tasks.push_back(t);
+      }
+    if ((int)tasks.size() != P2G_TASKS) throw B2Error(TI_ERROR_INVALID_STATE, "flush task table");
+    std::stable_sort(tasks.begin(), tasks.end(), [](const Task &a, const Task &b) { return a.s.size() > b.s.size(); });
+    for (int t = 0; t < P2G_TASKS; t++) {
+      for (int q = 0; q < 9; q++) tab.task[t][q] = q < (int)tasks[t].s.size() ? tasks[t].s[q] : (unsigned short)P2G_ZERO;
+      tab.task[t][9] = (unsigned short)tasks[t].node;
+    }
+    void *d = dalloc<unsigned char>(sizeof(P2GTab));
+    B2_CUDA(cudaMemcpyAsync(d, &tab, sizeof(tab), cudaMemcpyHostToDevice, rt->stream()));
+    M.p2g_tab = d;
+    B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(P2GShared)));
+  }
   rt->sync();
 }
 B2Mpm_t::~B2Mpm_t() {
@@ -690,9 +723,7 @@ void B2Mpm_t::p2g() {
   B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
   if (prm.block_local)
   {
-    // one CTA of 192 threads per block; the two-CTAs-per-block variant (H = 2) measured slower
-    // on C3 (0.525 vs 0.490 ms) and is not instantiated
-    k_mpm_p2g<4, 1><<<rt->num_sms * 4, 192, 0, st>>>(M, gen);
+    k_mpm_p2g<<<rt->num_sms * 3, P2G_NT, sizeof(P2GShared), st>>>(M, gen);
   }
   else
     k_mpm_p2g_plain<<<rt->num_sms * 8, 256, 0, st>>>(M, gen);

@@ -1,6 +1,6 @@
-// b2_mpm_bls.cuh -- the block-local (ti.block_local) P2G and G2P kernels, included by b2_mpm.cu.
+// b2_mpm_bls.cuh -- the block-local (ti.block_local) G2P kernel, included by b2_mpm.cu (P2G: b2_mpm_p2g.cuh).
 //
-// Both kernels process one occupied 4^3 block per CTA (persistent CTAs fetch block slots from an
+// The kernel processes one occupied 4^3 block per CTA (persistent CTAs fetch block slots from an
 // atomic work counter) and start with the same step: a counting sort of the block's particles by
 // cell in shared memory (64 integer bins; ranks come from the native integer ATOMS.ADD), which
 // gives   sStart[cell], sCnt[cell]   and   sPerm[start + rank] = particle index.
@@ -97,172 +97,6 @@ __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u
     if (c < 64) S.perm[S.start[c] + (int)(k & 0xffffu)] = (unsigned short)t;
   }
   __syncthreads();
-}
-
-// ------------------------------------------------------------------------------------------
-// P2G.  Thread (cell, i) accumulates its 9 nodes {mv, m} in registers; particles are fed in
-// rounds of <= R per cell so that all threads stay busy whatever the sort order is.
-// H = 1: one CTA (192 threads) per block.  H = 2: two CTAs (96 threads) per block, each owning the
-// cells of one x-half (more blocks in flight per SM, cheaper barriers; the sort pass is repeated).
-// ------------------------------------------------------------------------------------------
-template <int R, int H>
-__global__ void __launch_bounds__(192 / H, 4 * H) k_mpm_p2g(MpmDev M, int gen) {
-  constexpr int NT = 192 / H, NC = 64 / H, SL = NC * R, XC = 4 / H, PXN = XC + 2;
-  __shared__ float4 sBuf[NC * 27];  // round staging (6 x SL float4), later the per-cell partials R[NC][27]
-  __shared__ float4 sRaw[4 * SL > 512 ? 4 * SL : 512];  // next round's particle planes (cp.async); the 8 KiB of sort keys alias it
-  __shared__ MpmSortSmem S;
-  __shared__ int sItem;
-  __shared__ float4 *sNb[8];
-  u32 *sKey = (u32 *)sRaw;
-  float4 *sSh = sBuf;           // [3][SL]  {wy0,wy1,wy2,wz0} {wz1,wz2,A01,A11} {A21,A02,A12,A22}
-  float4 *sSp = sBuf + 3 * SL;  // [SL][3]  {wx_i, V_i}
-  static_assert(6 * SL <= NC * 27, "staging must fit under the partials");
-
-  const int tid = threadIdx.x;
-  const int cell = tid / 3, plane = tid - cell * 3;
-  const u32 nitems = *M.nslots * H;
-
-  for (;;) {
-    __syncthreads();
-    if (tid == 0) sItem = (int)atomicAdd(&M.work_counter[0], 1u);
-    __syncthreads();
-    const u32 item = (u32)sItem;
-    if (item >= nitems) break;
-    const u32 slot = item / H;
-    const int half = (int)(item % H);
-    const u32 total = M.count[gen][slot];
-    if (total == 0) continue;
-    const int key = M.slot_key[slot];
-    int bx, by, bz;
-    mpm_unkey(M, key, bx, by, bz);
-    const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
-    if (tid < (int)nchunks) S.chunk[tid] = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + tid]);
-    if (tid == 0) S.touched = M.activate_halo ? 0xffu : 0u;
-    // neighbour blocks that already exist are resolved now (latency hidden behind the sort);
-    // only touched-but-inactive ones are activated at the end
-    if (tid >= 64 && tid < 72) {
-      const int nbh = tid - 64;
-      sNb[nbh] = mpm_block_ptr<false>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
-    }
-    float4 acc[9];
-    for (u32 q0 = 0; q0 < total; q0 += MPM_SB) {
-      const int n = (int)min((u32)MPM_SB, total - q0);
-      mpm_sort_pass<NT, 2>(M, S, sKey, q0, n, half * NC, NC);  // (first barrier inside also publishes S.chunk)
-      if (q0 == 0) {  // accumulators start after the first sort pass (keeps them out of its register budget)
-#pragma unroll
-        for (int q = 0; q < 9; q++) acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-      const int rounds = (S.maxcnt + R - 1) / R;
-      // loaders: slot (cell c, s) takes the (r*R + s)-th particle of cell c.  The four planes of
-      // round r+1 are fetched with cp.async while stage 1 of round r runs.
-      auto issue = [&](int r) {
-        for (int sl = tid; sl < SL; sl += NT) {
-          const int c = sl / R, k = r * R + (sl % R);
-          if (k < S.cnt[c]) {
-            const u32 q = q0 + S.perm[S.start[c] + k];
-            const u8 *src = S.chunk[q / MPM_CHUNK] + (q % MPM_CHUNK) * 16;
-#pragma unroll
-            for (int pl4 = 0; pl4 < 4; pl4++) {
-              const unsigned dst = (unsigned)__cvta_generic_to_shared(&sRaw[pl4 * SL + sl]);
-              asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src + pl4 * MPM_PLANE_BYTES) : "memory");
-            }
-          }
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-      };
-      issue(0);
-      for (int r = 0; r < rounds; r++) {
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        for (int sl = tid; sl < SL; sl += NT) {
-          const int c = sl / R, k = r * R + (sl % R);
-          if (k < S.cnt[c]) {
-            const float4 p0 = sRaw[sl], p1 = sRaw[SL + sl], p2 = sRaw[2 * SL + sl], p3 = sRaw[3 * SL + sl];
-            MpmStencil s;
-            mpm_stencil(M, p0.x, p0.y, p0.z, s);
-            const float stress = M.stress_k * (p0.w - 1.0f);
-            // A' = (stress I + m C) dx ; b = m v - A' fx ; V_i = b + i A'[:,0]
-            const float m = M.p_mass;
-            const float A00 = (stress + m * p1.w) * M.dx, A01 = m * p2.x * M.dx, A02 = m * p2.y * M.dx;
-            const float A10 = m * p2.z * M.dx, A11 = (stress + m * p2.w) * M.dx, A12 = m * p3.x * M.dx;
-            const float A20 = m * p3.y * M.dx, A21 = m * p3.z * M.dx, A22 = (stress + m * p3.w) * M.dx;
-            const float b0 = m * p1.x - (A00 * s.fx[0] + A01 * s.fx[1] + A02 * s.fx[2]);
-            const float b1 = m * p1.y - (A10 * s.fx[0] + A11 * s.fx[1] + A12 * s.fx[2]);
-            const float b2 = m * p1.z - (A20 * s.fx[0] + A21 * s.fx[1] + A22 * s.fx[2]);
-            sSh[sl] = make_float4(s.w[0][1], s.w[1][1], s.w[2][1], s.w[0][2]);
-            sSh[SL + sl] = make_float4(s.w[1][2], s.w[2][2], A01, A11);
-            sSh[2 * SL + sl] = make_float4(A21, A02, A12, A22);
-            sSp[sl * 3 + 0] = make_float4(s.w[0][0], b0, b1, b2);
-            sSp[sl * 3 + 1] = make_float4(s.w[1][0], b0 + A00, b1 + A10, b2 + A20);
-            sSp[sl * 3 + 2] = make_float4(s.w[2][0], b0 + 2.f * A00, b1 + 2.f * A10, b2 + 2.f * A20);
-          }
-        }
-        __syncthreads();
-        if (r + 1 < rounds) issue(r + 1);
-        {
-          const int nk = min(R, S.cnt[cell] - r * R);
-          for (int k = 0; k < nk; k++) {
-            const int sl = cell * R + k;
-            const float4 h0 = sSh[sl], h1 = sSh[SL + sl], h2 = sSh[2 * SL + sl];
-            const float4 pl = sSp[sl * 3 + plane];
-            const float wy[3] = {h0.x, h0.y, h0.z};
-            const float wz[3] = {h0.w, h1.x, h1.y};
-            float r0 = pl.y, r1 = pl.z, r2 = pl.w;  // value at (i, j, k=0), walks along j
-#pragma unroll
-            for (int j = 0; j < 3; j++) {
-              const float wxy = pl.x * wy[j];
-              float c0 = r0, c1 = r1, c2 = r2;  // walks along k
-#pragma unroll
-              for (int kk = 0; kk < 3; kk++) {
-                const float w = wxy * wz[kk];
-                float4 &a = acc[j * 3 + kk];
-                a.x = fmaf(w, c0, a.x);
-                a.y = fmaf(w, c1, a.y);
-                a.z = fmaf(w, c2, a.z);
-                a.w += w;
-                c0 += h2.y, c1 += h2.z, c2 += h2.w;  // + A'[:,2]
-              }
-              r0 += h1.z, r1 += h1.w, r2 += h2.x;  // + A'[:,1]
-            }
-          }
-        }
-        __syncthreads();  // staging is overwritten by the next round / by R
-      }
-    }
-    // per-cell partials -> shared
-#pragma unroll
-    for (int q = 0; q < 9; q++) {
-      float4 a = acc[q];
-      a.w *= M.p_mass;
-      sBuf[cell * 27 + plane * 9 + q] = a;
-    }
-    // touched neighbour blocks that do not exist yet are activated now (rare in steady state)
-    if (tid >= 64 && tid < 72) {
-      const int nbh = tid - 64;
-      if (!((S.touched >> nbh) & 1u))
-        sNb[nbh] = nullptr;
-      else if (sNb[nbh] == nullptr)
-        sNb[nbh] = mpm_block_ptr<true>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
-    }
-    __syncthreads();
-    // pad node = sum of the partials of the <=27 cells whose stencil covers it; one vector red each
-    for (int nidx = tid; nidx < PXN * 36; nidx += NT) {
-      const int pxl = nidx / 36, py = (nidx / 6) % 6, pz = nidx % 6;  // pxl: x inside this CTA's cell range
-      float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
-      // cell = node - (i,j,k) must lie inside the CTA's cells
-      const int i0 = max(0, pxl - (XC - 1)), i1 = min(2, pxl), j0 = max(0, py - 3), j1 = min(2, py), k0 = max(0, pz - 3), k1 = min(2, pz);
-      for (int i = i0; i <= i1; i++)
-        for (int j = j0; j <= j1; j++) {
-          const float4 *row = &sBuf[((((pxl - i) << 4) | ((py - j) << 2)) + pz) * 27 + i * 9 + j * 3];
-          for (int k = k0; k <= k1; k++) {
-            const float4 rr = row[k - 27 * k];  // cell z = pz - k  ->  -27 k ; node k -> + k
-            s4.x += rr.x, s4.y += rr.y, s4.z += rr.z, s4.w += rr.w;
-          }
-        }
-      const int px = pxl + XC * half;
-      float4 *dst = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
-      if (dst && (s4.x != 0.f || s4.y != 0.f || s4.z != 0.f || s4.w != 0.f)) red_add_v4(dst + (((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)), s4);
-    }
-  }
 }
 
 // ------------------------------------------------------------------------------------------
