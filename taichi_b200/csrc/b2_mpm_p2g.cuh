@@ -137,13 +137,19 @@ __device__ __forceinline__ void p2g_publish(const MpmDev &M, int gen, u32 nslots
 }
 
 // Cuts the cells (counts in S.cnt) into units of <= L particles and ranks the units by length.
-__device__ __forceinline__ void p2g_order(const MpmDev &M, P2GShared &S, P2GUnit &U) {
+#ifdef P2G_TIMING
+#define OCK(i) do { const long long _n = clock64(); ot[i] += _n - *ol; *ol = _n; } while (0)
+#else
+#define OCK(i) do { } while (0)
+#endif
+__device__ __forceinline__ void p2g_order(const MpmDev &M, P2GShared &S, P2GUnit &U, long long *ot = nullptr, long long *ol = nullptr) {
   const int lane = threadIdx.x & 31;
   const int cA = 2 * lane, cB = cA + 1;
   const int nA = S.cnt[cA], nB = S.cnt[cB];
   u32 tm = (nA > 0 ? p2g_touch_mask(cA) : 0u) | (nB > 0 ? p2g_touch_mask(cB) : 0u);
   tm = __reduce_or_sync(0xffffffffu, tm);
   const int nlive = __reduce_add_sync(0xffffffffu, nA + nB);
+  OCK(5);
   int L = max(1, (nlive + P2G_UNITS - 1) / P2G_UNITS), fA, fB, F;
   float invL;
   for (;; L++) {  // smallest L whose full units fit the spare triples; L <= 53 for n <= 576
@@ -153,6 +159,7 @@ __device__ __forceinline__ void p2g_order(const MpmDev &M, P2GShared &S, P2GUnit
     F = __reduce_add_sync(0xffffffffu, fA + fB);
     if (F <= P2G_XUNITS) break;
   }
+  OCK(6);
   const int remA = nA - L * fA, remB = nB - L * fB;  // length of the cell's last unit: 1..L (0: empty cell)
   int inc = fA + fB;  // ranks of the full units: cell order
 #pragma unroll
@@ -164,6 +171,7 @@ __device__ __forceinline__ void p2g_order(const MpmDev &M, P2GShared &S, P2GUnit
   const int maxfull = __reduce_max_sync(0xffffffffu, max(fA, fB));
   const int wA = atomicAdd(&S.hist[remA], 1), wB = atomicAdd(&S.hist[remB], 1);
   __syncwarp();
+  OCK(7);
   const int hA = S.hist[cA], hB = S.hist[cB];  // lengths 2*lane, 2*lane+1
   int sfx = hA + hB;  // inclusive suffix sum over lanes
 #pragma unroll
@@ -183,6 +191,7 @@ __device__ __forceinline__ void p2g_order(const MpmDev &M, P2GShared &S, P2GUnit
   }
   U.rowstart[cA] = ps - lenA - lenB, U.rowstart[cB] = ps - lenB;
   __syncwarp();
+  OCK(8);
   const int rkA = F + S.nk[remA] + wA, rkB = F + S.nk[remB] + wB;
   U.cinfo[cA] = (u32)fA | (u32)baseA << 8 | (u32)rkA << 16;
   U.cinfo[cB] = (u32)fB | (u32)baseB << 8 | (u32)rkB << 16;
@@ -243,7 +252,16 @@ __device__ __forceinline__ void p2g_flush_task(const MpmDev &M, const P2GShared 
   if (dst && (s4.x != 0.f || s4.y != 0.f || s4.z != 0.f || s4.w != 0.f)) red_add_v4(dst + (((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)), s4);
 }
 
+#ifdef P2G_TIMING
+#define TCK(i) do { const long long _n = clock64(); tacc[i] += _n - tlast; tlast = _n; } while (0)
+#else
+#define TCK(i) do { } while (0)
+#endif
 __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
+#ifdef P2G_TIMING
+  long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
+  int nun = 0;
+#endif
   extern __shared__ __align__(16) unsigned char p2g_smem[];
   P2GShared &S = *(P2GShared *)p2g_smem;
   const int tid = threadIdx.x, lane = tid & 31;
@@ -273,13 +291,25 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
           if (lane < 8) nxt = p2g_desc_field(M, gen, nslots, s2, 0u, lane);
         }
       }
+      TCK(0);
       bar_count_wait();  // the workers have counted unit k
+      TCK(1);
+#ifdef P2G_TIMING
+      if (slot < nslots) p2g_order(M, S, S.unit[k & 1], tacc, &tlast);
+#else
       if (slot < nslots) p2g_order(M, S, S.unit[k & 1]);
+#endif
+      TCK(2);
       p2g_publish(M, gen, nslots, S.unit[(k + 1) & 1], nxt);
+      TCK(3);
       __syncthreads();  // round k starts: tables k and header k + 1 are visible
+      TCK(4);
       if (slot >= nslots) break;
       dsc = nxt;
     }
+#ifdef P2G_TIMING
+    if (blockIdx.x == 7 && lane == 0) printf("helper: request %lld countwait %lld order[cnt %lld Lloop %lld scan1 %lld scan23 %lld tables %lld] publish %lld topbar %lld\n", tacc[0], tacc[1], tacc[5], tacc[6], tacc[7], tacc[8], tacc[2], tacc[3], tacc[4]);
+#endif
     return;
   }
   // ================================== workers ======================================================
@@ -293,7 +323,9 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
   bar_count_arrive();
 
   for (int it = 0;; it++) {
+    TCK(9);
     __syncthreads();  // tables of unit `it` and the header of unit it + 1 are published
+    TCK(0);
     const P2GUnit &U = S.unit[it & 1];
     if (U.slot >= nslots) break;
     const int n = p2g_unit_entries(U.total, U.q0);
@@ -351,11 +383,14 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
           S.stg[4][pos] = make_float4(b2, A20, A21, A22);
         }
     }
+    TCK(1);
     // ---- count the NEXT unit; the helper orders it while this unit is scattered and flushed -----------
     p2g_count(M, gen, nslots, S, S.unit[(it + 1) & 1]);
     bar_count_arrive();
+    TCK(2);
     if (n == 0) continue;
     bar_workers();
+    TCK(3);
     // ---- scatter: thread (unit u, plane) over the unit's particles ------------------------------------
     const u32 unit = u < U.nunits ? U.unit[u] : 0xffff0000u;
     const int cell = (int)(unit & 0xffu), np = (int)((unit >> 8) & 0xffu), turn = (int)(unit >> 16);
@@ -389,7 +424,9 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
         if (j < 2) r01 = f2_add(r01, j01), r2o = f2_add(r2o, j2);
       }
     }
+    TCK(4);
     bar_workers();  // staging is dead: the partials take its place
+    TCK(5);
     // a cell's last unit stores its partials (every cell has one), the cell's full units add theirs in turn
     ulonglong2 *const P2 = (ulonglong2 *)&P[cell * 27 + plane * 9];
     if (turn == 0) {
@@ -416,9 +453,19 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
       else if (S.nb[nbh] == nullptr)
         S.nb[nbh] = mpm_block_ptr<true>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
     }
+    TCK(6);
     bar_workers();
+    TCK(7);
     // ---- flush: every task sums <= 9 partials of one pad node and issues one vector red -----------------
     p2g_flush_task(M, S, (const ulonglong2 *)P, tid);
     if (tid >= 2 * P2G_NW - P2G_TASKS) p2g_flush_task(M, S, (const ulonglong2 *)P, P2G_NW + (P2G_NW - 1 - tid));
+    TCK(8);
+#ifdef P2G_TIMING
+    nun++;
+#endif
   }
+#ifdef P2G_TIMING
+  if (blockIdx.x == 7 && (tid == 0 || tid == 100 || tid == 200))
+    printf("worker %d units %d: topbar %lld loads+stage %lld count %lld bar1 %lld scatter %lld bar2 %lld partials %lld bar3 %lld flush %lld end %lld\n", tid, nun, tacc[0], tacc[1], tacc[2], tacc[3], tacc[4], tacc[5], tacc[6], tacc[7], tacc[8], tacc[9]);
+#endif
 }

@@ -222,6 +222,51 @@ def test_binned_ten_substeps_vs_oracle(rt, layout):
     s.destroy()
 
 
+@pytest.mark.parametrize("case", ["fat_cells", "multi_pass", "one_per_block", "mixed"])
+def test_p2g_ragged_bins_vs_oracle(rt, case):
+    """Edge cases of the unit-balanced block-local P2G (b2_mpm_p2g.cuh): bins of more than one 576-entry
+    pass, thousands of particles in one cell (unit length L > 31), blocks holding a single particle,
+    and a mix; grid after P2G per node against the oracle's fp64-accumulated P2G, active sets bit-exact."""
+    import taichi_b200 as tb
+    n_grid, dt = 32, 2e-4
+    rng = np.random.default_rng({"fat_cells": 21, "multi_pass": 22, "one_per_block": 23, "mixed": 24}[case])
+    dx = 1.0 / n_grid
+    if case == "fat_cells":      # 3000 particles inside ONE cell + 500 in a second cell of the same block
+        x = np.concatenate([(np.array([9.6, 9.7, 9.8]) + rng.random((3000, 3)) * 0.8) * dx,
+                            (np.array([10.6, 8.6, 11.6]) + rng.random((500, 3)) * 0.8) * dx])
+    elif case == "multi_pass":   # 40 particles per cell over two adjacent blocks: 2560 entries per bin
+        x = (np.array([8.5, 8.5, 8.5]) + rng.random((5120, 3)) * np.array([8.0, 4.0, 4.0])) * dx
+    elif case == "one_per_block":
+        bl = np.stack(np.meshgrid(np.arange(1, 7), np.arange(1, 7), np.arange(1, 7), indexing="ij"), -1).reshape(-1, 3)
+        x = (bl * 4 + 0.5 + rng.random((len(bl), 3)) * 3.9) * dx
+    else:
+        x = np.concatenate([(np.array([4.5, 4.5, 4.5]) + rng.random((7000, 3)) * 20.0) * dx,
+                            (np.array([13.2, 13.2, 13.2]) + rng.random((1500, 3)) * 0.5) * dx])
+    x = x.astype(np.float32)
+    N = len(x)
+    v = ((rng.random((N, 3)) - 0.5) * 2).astype(np.float32)
+    Cm = ((rng.random((N, 3, 3)) - 0.5) * 4).astype(np.float32)
+    J = (1 + (rng.random(N) - 0.5) * 0.1).astype(np.float32)
+    for layout in ("pointer_bitmasked", "dense"):
+        s = tb.Mpm3D(rt, n_grid, N, dt, layout=layout)
+        s.set_particles(x, v, Cm, J)
+        *_, pv, pm = oracle_mpm3d(n_grid, x, v, Cm, J, dt, 1)
+        s.clear_grid()
+        s.p2g()
+        g = s.grid_to_numpy()
+        assert np.allclose(g[..., 3], pm, rtol=2e-5, atol=1e-6 * pm.max())
+        assert np.allclose(g[..., :3], pv, rtol=2e-5, atol=2e-6 * np.abs(pv).max())
+        if layout != "dense":
+            assert np.array_equal(s.active_blocks(), expected_blocks(x, n_grid, halo=False))
+        # the whole substep keeps every particle (re-binning of the ragged bins) and stays finite
+        s.grid_op()
+        s.g2p()
+        s.substep(2)
+        xr, vr, Cr, Jr = s.get_particles()
+        assert s.stats()["particles"] == N and np.isfinite(xr).all() and np.isfinite(vr).all()
+        s.destroy()
+
+
 def test_bls_activate_halo_mode(rt):
     """the reference's CUDA-BLS epilogue activates all 8 blocks {0,+1}^3."""
     import taichi_b200 as tb
