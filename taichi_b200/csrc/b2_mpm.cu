@@ -538,6 +538,7 @@ struct B2Mpm_t {
   int gen = 0;
   int64_t n_particles = 0;
   bool lists_valid = false;
+  bool order_valid = false;  // P2G has left the cell order of the current generation in the chunks (G2P skips its sort)
   bool sparse = false;
   bool profiling = false;
   std::vector<cudaEvent_t> prof_events;
@@ -646,6 +647,7 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   for (int g = 0; g < 2; g++) {
     M.count[g] = dalloc<u32>(M.max_slots);
     M.chunk_of[g] = dalloc<u32>((size_t)M.max_slots * M.maxc);
+    M.live[g] = dalloc<u32>((size_t)M.max_slots * MPM_MAXPASS);
     void *a = nullptr;
     B2_CUDA(cudaMalloc(&a, (size_t)M.arena_cap * MPM_CHUNK_BYTES));
     allocs.push_back(a);
@@ -706,6 +708,7 @@ void B2Mpm_t::reset_bins() {
   }
   gen = 0;
   n_particles = 0;
+  order_valid = false;
 }
 void B2Mpm_t::ensure_lists() {
   if (!lists_valid) {
@@ -724,6 +727,7 @@ void B2Mpm_t::p2g() {
   if (prm.block_local)
   {
     k_mpm_p2g<<<rt->num_sms * 3, P2G_NT, sizeof(P2GShared), st>>>(M, gen);
+    order_valid = true;
   }
   else
     k_mpm_p2g_plain<<<rt->num_sms * 8, 256, 0, st>>>(M, gen);
@@ -742,19 +746,24 @@ void B2Mpm_t::g2p() {
   B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
   if (prm.block_local)
   {
-    static int nt = getenv("B2_G2P_NT") ? atoi(getenv("B2_G2P_NT")) : 64;
-    if (nt == 256)
-      k_mpm_g2p_bls<256, 3><<<rt->num_sms * 3, 256, 0, st>>>(M, gen);
-    else if (nt == 64)
-      k_mpm_g2p_bls<64, 12><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
-
+    static const bool no_order = getenv("B2_G2P_SORT") != nullptr;  // experiment switch: always sort
+    static const int occ = getenv("B2_G2P_OCC") ? atoi(getenv("B2_G2P_OCC")) : 20;
+    if (order_valid && !no_order && occ == 16)
+      k_mpm_g2p_bls<64, 16, true><<<rt->num_sms * 16, 64, 0, st>>>(M, gen);
+    else if (order_valid && !no_order && occ == 20)
+      k_mpm_g2p_bls<64, 20, true><<<rt->num_sms * 20, 64, 0, st>>>(M, gen);
+    else if (order_valid && !no_order && occ == 24)
+      k_mpm_g2p_bls<64, 24, true><<<rt->num_sms * 24, 64, 0, st>>>(M, gen);
+    else if (order_valid && !no_order)
+      k_mpm_g2p_bls<64, 12, true><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
     else
-      k_mpm_g2p_bls<128, 6><<<rt->num_sms * 6, 128, 0, st>>>(M, gen);
+      k_mpm_g2p_bls<64, 12, false><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
   }
   else
     k_mpm_g2p<false><<<rt->num_sms * 3, G2P_PLAIN_THREADS, 0, st>>>(M, gen);
   rt->count_launch();
   gen ^= 1;
+  order_valid = false;
 }
 void B2Mpm_t::substep(int n) {
   cudaStream_t st = rt->stream();
@@ -827,6 +836,7 @@ int32_t b2_mpm_add_particles(B2Mpm m, int64_t n, const float *x, const float *v,
   m->rt->count_launch();
   B2_CUDA(cudaGetLastError());
   m->n_particles += n;
+  m->order_valid = false;
   sx.finish(), sv.finish(), sc.finish(), sj.finish(), si.finish();
   return 0;
   B2_API_END(-1)
@@ -982,6 +992,7 @@ int32_t b2_mpm_insert_records(B2Mpm m, const void *buf, int64_t cap) {
   B2_API_BEGIN
   require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
   check_msg(buf, cap);
+  m->order_valid = false;
   k_mpm_insert_records<<<m->rt->grid_for(std::max<int64_t>(cap, 1), 256, 4), 256, 0, m->rt->stream()>>>(m->M, m->gen, (const u8 *)buf, cap);
   m->rt->count_launch();
   B2_CUDA(cudaGetLastError());

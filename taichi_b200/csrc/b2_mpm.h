@@ -4,7 +4,10 @@
 
 #define MPM_CHUNK 256            /* particles per bin chunk                      */
 #define MPM_PLANE_BYTES 4096     /* 256 x float4                                 */
-#define MPM_CHUNK_BYTES 17408    /* 4 float4 planes + 256 x u32 particle ids      */
+#define MPM_CHUNK_BYTES 17920    /* 4 float4 planes + 256 x u32 particle ids + 256 x u16 cell-sorted order */
+#define MPM_PERM_OFF 17408       /* byte offset of the u16 order plane (written by P2G, read by G2P) */
+#define MPM_PASS 576             /* bin entries per P2G work unit = per G2P pass when it follows P2G   */
+#define MPM_MAXPASS 16           /* passes per bin: maxc * 256 / MPM_PASS rounded up                   */
 #define MPM_SB 2048              /* particles cell-sorted per pass (shared-memory keys) */
 #define MPM_TOMB (-1.0e30f)      /* p0.x of a bin entry whose particle moved to another block */
 
@@ -34,6 +37,7 @@ struct MpmDev {
   // two particle generations (read g, write g^1)
   u32 *count[2];     // [max_slots]
   u32 *chunk_of[2];  // [max_slots * maxc] chunk id + 1
+  u32 *live[2];      // [max_slots * MPM_MAXPASS] live (non-tombstone) entries per pass, written by P2G
   u8 *arena[2];
   u32 *arena_next[2];
   u32 arena_cap;

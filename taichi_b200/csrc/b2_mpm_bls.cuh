@@ -9,8 +9,9 @@
 #pragma once
 
 
-struct MpmSortSmem {
-  unsigned short perm[MPM_SB]; // cell-sorted -> index inside the pass
+template <int SB>
+struct MpmSortSmemT {
+  unsigned short perm[SB]; // cell-sorted -> index inside the pass
   int cnt[65];
   int start[66];
   int maxcnt;
@@ -32,8 +33,8 @@ __device__ __forceinline__ int mpm_cell_of(const MpmDev &M, const float4 p0) {
 // Sorts particles [q0, q0+n) of the bin. All threads of the CTA must call it. NT = blockDim.x.
 // On return (after its final barrier): S.cnt / S.start / S.perm / S.maxcnt / S.touched are valid;
 // S.start[64] = number of live particles in the pass.
-template <int NT, int U>
-__device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u32 *key, u32 q0, int n, int cbase = 0, int ncell = 64) {  // key[MPM_SB]: cell << 16 | rank
+template <int NT, int U, int SB>
+__device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmemT<SB> &S, u32 *key, u32 q0, int n, int cbase = 0, int ncell = 64) {  // key[SB]: cell << 16 | rank
   const int tid = threadIdx.x;
   if (tid < 65) S.cnt[tid] = 0;
   __syncthreads();
@@ -106,11 +107,15 @@ __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmem &S, u
 // particles that change block go through the generic warp-aggregated append (mpm_insert).  The
 // unused tail of the reserved range (= number of leavers) is filled with tombstones.
 // ------------------------------------------------------------------------------------------
-template <int G2P_THREADS, int G2P_MINB>
+// PERM = true: P2G has just run on this generation and left the cell-major order of every pass of
+// MPM_PASS entries in the chunks' order plane (+ the live count per pass): no sort here.
+template <int G2P_THREADS, int G2P_MINB, bool PERM>
 __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M, int gen) {
+  constexpr int SB = PERM ? MPM_PASS : MPM_SB;  // entries per pass
   __shared__ float4 sPad[216];
-  __shared__ MpmSortSmem S;
-  __shared__ u32 sKey[MPM_SB];
+  __shared__ MpmSortSmemT<PERM ? 2 : MPM_SB> S;
+  __shared__ u32 sKey[PERM ? 2 : MPM_SB];
+  __shared__ __align__(4) unsigned short sOrder[PERM ? MPM_PASS : 2];  // the pass's order plane (one coalesced read)
   __shared__ u8 *sOut[65];
   __shared__ u32 sBase, sStay;
   __shared__ int sSlot;
@@ -142,10 +147,28 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
       const float4 *src = sNb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
       sPad[nidx] = src ? src[((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)] : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    for (u32 q0 = 0; q0 < total; q0 += MPM_SB) {
-      const int n = (int)min((u32)MPM_SB, total - q0);
-      mpm_sort_pass<G2P_THREADS, 4>(M, S, sKey, q0, n);
-      const int nlive = S.start[64];
+    if (PERM) __syncthreads();  // pad complete (the sort pass's barriers do this otherwise)
+    auto sorted_entry = [&](u32 q0, int j) -> u32 {  // j-th live entry of the pass in cell order
+      if constexpr (PERM) {
+        return q0 + sOrder[j];
+      } else {
+        return q0 + S.perm[j];
+      }
+    };
+    for (u32 q0 = 0; q0 < total; q0 += SB) {
+      int nlive;
+      if constexpr (PERM) {
+        nlive = (int)M.live[gen][(u64)slot * MPM_MAXPASS + q0 / MPM_PASS];
+        __syncthreads();  // the previous pass is done with sOrder
+        for (int w = tid; 2 * w < nlive; w += G2P_THREADS) {
+          const u32 qs = q0 + 2u * (u32)w;
+          ((u32 *)sOrder)[w] = ((const u32 *)(S.chunk[qs / MPM_CHUNK] + MPM_PERM_OFF))[(qs % MPM_CHUNK) / 2];
+        }
+      } else {
+        const int n = (int)min((u32)SB, total - q0);
+        mpm_sort_pass<G2P_THREADS, 4>(M, S, sKey, q0, n);
+        nlive = S.start[64];
+      }
       if (nlive == 0) continue;  // uniform
       if (tid == 0) {
         sBase = atomicAdd(&M.count[g1][slot], (u32)nlive);
@@ -185,7 +208,7 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
       float4 np0 = make_float4(0.f, 0.f, 0.f, 1.f);
       u32 nid = 0;
       if (tid < nlive) {  // software pipeline: particle t0+NT is loaded while particle t0 is computed
-        const u32 q = q0 + S.perm[tid];
+        const u32 q = sorted_entry(q0, tid);
         const u8 *ch = S.chunk[q / MPM_CHUNK];
         np0 = ((const float4 *)ch)[q % MPM_CHUNK];
         nid = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[q % MPM_CHUNK];
@@ -198,7 +221,7 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
         const float4 p0 = np0;
         u32 id = nid;
         if (t + G2P_THREADS < nlive) {
-          const u32 q = q0 + S.perm[t + G2P_THREADS];
+          const u32 q = sorted_entry(q0, t + G2P_THREADS);
           const u8 *ch = S.chunk[q / MPM_CHUNK];
           np0 = ((const float4 *)ch)[q % MPM_CHUNK];
           nid = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[q % MPM_CHUNK];

@@ -29,7 +29,7 @@
 
 #define P2G_NT 256
 #define P2G_NW 224                 /* worker threads (7 warps); warp 7 is the helper             */
-#define P2G_PASS 576               /* bin entries per work unit                                  */
+#define P2G_PASS MPM_PASS          /* bin entries per work unit                                  */
 #define P2G_UNITS 74               /* worker thread triples                                      */
 #define P2G_XUNITS (P2G_UNITS - 64)/* units beyond one per cell                                  */
 #define P2G_CAP (P2G_PASS + 64)    /* staging slots: rows are padded to odd lengths              */
@@ -51,6 +51,7 @@ struct P2GUnit {                   // one work unit; header by the helper, ck by
   int rowstart[64];
   u32 cinfo[64];                   // by cell: full units | rank of the first full unit << 8 | rank of the last unit << 16
   u32 unit[P2G_UNITS + 2];         // by rank: cell | length << 8 | turn in the partial sum << 16
+  unsigned short cstart[64];       // by cell: first position in cell-major order (the order G2P will use)
   unsigned short ck[P2G_PASS];     // by entry: cell << 10 | rank inside the cell; 0xffff = tombstone
 };
 
@@ -142,7 +143,7 @@ __device__ __forceinline__ void p2g_publish(const MpmDev &M, int gen, u32 nslots
 #else
 #define OCK(i) do { } while (0)
 #endif
-__device__ __forceinline__ void p2g_order(const MpmDev &M, P2GShared &S, P2GUnit &U, long long *ot = nullptr, long long *ol = nullptr) {
+__device__ __forceinline__ void p2g_order(const MpmDev &M, int gen, P2GShared &S, P2GUnit &U, long long *ot = nullptr, long long *ol = nullptr) {
   const int lane = threadIdx.x & 31;
   const int cA = 2 * lane, cB = cA + 1;
   const int nA = S.cnt[cA], nB = S.cnt[cB];
@@ -168,6 +169,14 @@ __device__ __forceinline__ void p2g_order(const MpmDev &M, P2GShared &S, P2GUnit
     if (lane >= d) inc += v;
   }
   const int baseA = inc - fA - fB, baseB = baseA + fA;
+  int cs = nA + nB;  // cell-major order of the live entries (handed to G2P through the chunks' order plane)
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, cs, d);
+    if (lane >= d) cs += v;
+  }
+  U.cstart[cA] = (unsigned short)(cs - nA - nB), U.cstart[cB] = (unsigned short)(cs - nB);
+  if (lane == 0) M.live[gen][(u64)U.slot * MPM_MAXPASS + U.q0 / P2G_PASS] = (u32)nlive;
   const int maxfull = __reduce_max_sync(0xffffffffu, max(fA, fB));
   const int wA = atomicAdd(&S.hist[remA], 1), wB = atomicAdd(&S.hist[remB], 1);
   __syncwarp();
@@ -295,9 +304,9 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
       bar_count_wait();  // the workers have counted unit k
       TCK(1);
 #ifdef P2G_TIMING
-      if (slot < nslots) p2g_order(M, S, S.unit[k & 1], tacc, &tlast);
+      if (slot < nslots) p2g_order(M, gen, S, S.unit[k & 1], tacc, &tlast);
 #else
-      if (slot < nslots) p2g_order(M, S, S.unit[k & 1]);
+      if (slot < nslots) p2g_order(M, gen, S, S.unit[k & 1]);
 #endif
       TCK(2);
       p2g_publish(M, gen, nslots, S.unit[(k + 1) & 1], nxt);
@@ -365,6 +374,11 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
           const int sgm = (int)(((float)r + 0.5f) * invL), k = r - sgm * L;
           const int uu = sgm < (int)(info & 0xffu) ? (int)((info >> 8) & 0xffu) + sgm : (int)(info >> 16);
           const int pos = U.rowstart[k] + uu;
+          {  // cell-major order for G2P: entry (cstart[c] + r) of the unit's order plane names this entry
+            const u32 qs = off0 + (u32)U.cstart[c] + (u32)r, ci = qs / MPM_CHUNK;
+            u8 *chn = mpm_chunk_ptr(M, gen, ci == 0 ? cid0 : ci == 1 ? cid1 : cid2);
+            ((unsigned short *)(chn + MPM_PERM_OFF))[qs % MPM_CHUNK] = (unsigned short)(tid + e * P2G_NW);
+          }
           MpmStencil s;
           mpm_stencil(M, p0[e].x, p0[e].y, p0[e].z, s);
           const float stress = M.stress_k * (p0[e].w - 1.0f);
