@@ -1,10 +1,14 @@
 #!/bin/bash
-# one gpurun call: GPU tests, bench, launch list, full ncu capture of P2G/G2P
+# one gpurun call: GPU tests, bench, launch list, full ncu capture of P2G/G2P (each profiler pass only after its
+# command exited 0 without ncu)
 set -x
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
 tail -5 gpurun_out/pytest_gpu.log
-timeout 600 python bench.py --steps 3 --warmup 3 > gpurun_out/bench_c3.json 2> gpurun_out/bench_c3.err; echo "bench rc=$?"
-tail -2 gpurun_out/bench_c3.json
+timeout 600 python bench.py --steps 4 --warmup 3 > gpurun_out/bench_c3.json 2> gpurun_out/bench_c3.err; echo "bench rc=$?"
+tail -2 gpurun_out/bench_c3.json | cut -c1-600
+timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
+timeout 600 python bench.py --workload c2 --steps 4 --warmup 3 --no-cpu > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; echo "bench c2 rc=$?"
+timeout 600 python bench_listgen.py > gpurun_out/listgen.jsonl 2> gpurun_out/listgen.err; echo "listgen rc=$?"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 1 --warmup 1 --no-cpu > gpurun_out/ncu_launches.log 2>&1; echo "ncu launches rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_mpm_p2g|k_mpm_g2p' -s 20 -c 2 -o gpurun_out/mpm_full -f python bench.py --steps 1 --warmup 1 --no-cpu > gpurun_out/ncu_full.log 2>&1; echo "ncu rc=$?"
-tail -3 gpurun_out/ncu_full.log
