@@ -366,6 +366,11 @@ TI_DLL_EXPORT int32_t b2_mpm_grid_to_dense(B2Mpm mpm, float *out_any);
 TI_DLL_EXPORT int32_t b2_mpm_stats(B2Mpm mpm, double *out_host);
 /* per-phase device time of the last b2_mpm_substep call with profiling on, ms:
    {clear, p2g, listgen, grid_op, g2p, rebin} */
+/* The solver keeps the leaf element list of its grid current incrementally (a block that P2G activates appends
+ * itself; the reference regenerates every list before every struct-for, transforms/offload.cpp:174-264).  Call this
+ * after changing the solver's tree through the b2_* tree API (activate / deactivate / gc): the next phase then
+ * regenerates the lists from the root. */
+TI_DLL_EXPORT int32_t b2_mpm_invalidate_lists(B2Mpm mpm);
 TI_DLL_EXPORT int32_t b2_mpm_set_profiling(B2Mpm mpm, int32_t on);
 TI_DLL_EXPORT int32_t b2_mpm_phase_ms(B2Mpm mpm, float *out_host6);
 

@@ -164,6 +164,7 @@ SIGNATURES = {
     "b2_mpm_g2p": (C.c_int32, [C.c_void_p]),
     "b2_mpm_grid_to_dense": (C.c_int32, [C.c_void_p, C.c_void_p]),
     "b2_mpm_stats": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
+    "b2_mpm_invalidate_lists": (C.c_int32, [C.c_void_p]),
     "b2_mpm_set_profiling": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b2_mpm_phase_ms": (C.c_int32, [C.c_void_p, f32p]),
     "b2_mpm_pack_blocks": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]),

@@ -70,6 +70,23 @@ __device__ __forceinline__ float4 *mpm_block_ptr(const MpmDev &M, int bx, int by
   bool dead;
   u8 *node = b2_walk<true>(M.T, M.leaf, I, &cell, &dead);
   if (dead) return nullptr;
+  // Keep the leaf element list current (the reference regenerates every list before every struct-for,
+  // offload.cpp:174-264; here a block is appended once, by the thread that wins its bit).
+  {
+    const int key = (bx * M.nb + by) * M.nb + bz;
+    const u32 bit = 1u << (key & 31);
+    if (!(atomicOr(&M.listed[key >> 5], bit) & bit)) {
+      B2CList *L = M.T->lists[M.leaf_sid];
+      uint4 *d = (uint4 *)b2_list_slot(M.T->pool, L, atomicAdd(&L->count, 1u));
+      if (d) {
+        const u64 p = (u64)node;
+        d[0] = make_uint4((u32)p, (u32)(p >> 32), 0u, 64u);
+        d[1] = make_uint4((u32)bx, (u32)by, (u32)bz, 0u);
+        d[2] = make_uint4(0u, 0u, 0u, 0u);
+        d[3] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+  }
   return (float4 *)node;
 }
 
@@ -332,6 +349,18 @@ __global__ void __launch_bounds__(256) k_mpm_grid_to_dense(MpmDev M, float4 *out
   }
 }
 
+// after a full listgen: every listed block gets its bit
+__global__ void __launch_bounds__(256) k_mpm_mark_listed(MpmDev M) {
+  B2CList *L = M.T->lists[M.leaf_sid];
+  const u32 ne = L->count;
+  for (u32 e = blockIdx.x * blockDim.x + threadIdx.x; e < ne; e += gridDim.x * blockDim.x) {
+    const B2Element *E = (const B2Element *)b2_list_get(L, e);
+    const int key = (E->pcoord[0] * M.nb + E->pcoord[1]) * M.nb + E->pcoord[2];
+    atomicOr(&M.listed[key >> 5], 1u << (key & 31));
+  }
+}
+
+#include "b2_f32x2.cuh"
 #include "b2_mpm_bls.cuh"
 #include "b2_mpm_p2g.cuh"
 
@@ -656,6 +685,7 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   }
   M.dbg = getenv("B2_DBG") ? atoi(getenv("B2_DBG")) : 0;
   M.work_counter = dalloc<u32>(8);
+  M.listed = dalloc<u32>((size_t)(nblocks + 31) / 32);
   M.stats = dalloc<double>(8);
   {  // P2G flush tasks: for every pad node the (cell, offset) partials that reach it, in groups of <= 9,
      // biggest groups first (equal trip counts inside a warp); short groups are padded with the zero slot
@@ -711,8 +741,12 @@ void B2Mpm_t::reset_bins() {
   order_valid = false;
 }
 void B2Mpm_t::ensure_lists() {
-  if (!lists_valid) {
+  if (!lists_valid) {  // full regeneration (first use, or after the tree was changed behind the solver's back)
+    const int64_t nblocks = (int64_t)M.nb * M.nb * M.nb;
+    B2_CUDA(cudaMemsetAsync(M.listed, 0, (size_t)(nblocks + 31) / 32 * 4, rt->stream()));
     tree->listgen_async(M.leaf_sid);
+    k_mpm_mark_listed<<<rt->num_sms * 4, 256, 0, rt->stream()>>>(M);
+    rt->count_launch();
     lists_valid = true;
   }
 }
@@ -732,7 +766,7 @@ void B2Mpm_t::p2g() {
   else
     k_mpm_p2g_plain<<<rt->num_sms * 8, 256, 0, st>>>(M, gen);
   rt->count_launch();
-  if (sparse) lists_valid = false;  // P2G may have activated blocks
+  // blocks that P2G activates append themselves to the leaf element list (mpm_block_ptr<true>)
 }
 void B2Mpm_t::grid_op() {
   ensure_lists();
@@ -932,6 +966,11 @@ int32_t b2_mpm_stats(B2Mpm m, double *out) {
   return 0;
   B2_API_END(-1)
 }
+int32_t b2_mpm_invalidate_lists(B2Mpm m) {
+  if (!m) return -1;
+  m->lists_valid = false;
+  return 0;
+}
 int32_t b2_mpm_set_profiling(B2Mpm m, int32_t on) {
   if (!m) return -1;
   m->profiling = on != 0;
@@ -971,7 +1010,6 @@ int32_t b2_mpm_unpack_blocks(B2Mpm m, const void *buf, int64_t cap, int32_t mode
   k_mpm_unpack_blocks<<<m->rt->num_sms * 4, 256, 0, m->rt->stream()>>>(m->M, (const u8 *)buf, cap, mode);
   m->rt->count_launch();
   B2_CUDA(cudaGetLastError());
-  if (mode == 0 && m->sparse) m->lists_valid = false;  // may have activated blocks
   return 0;
   B2_API_END(-1)
 }

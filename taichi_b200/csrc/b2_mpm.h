@@ -42,6 +42,7 @@ struct MpmDev {
   u32 *arena_next[2];
   u32 arena_cap;
   u32 *work_counter;  // dynamic slot fetch for the persistent kernels [8]
+  u32 *listed;        // [nb^3 / 32] bit per block: the block is in the leaf element list (kept current incrementally)
   int dbg;              // B2_DBG experiment switches (0 in production)
   const void *p2g_tab;  // P2GTab (b2_mpm_p2g.cuh): flush source table
   double *stats;      // [8]

@@ -65,28 +65,6 @@ struct P2GShared {
   float4 *nb[8];
 };
 
-// ---- packed fp32x2 (sm_100a FFMA2 / FADD2 / FMUL2) --------------------------------------------------
-__device__ __forceinline__ u64 f2_pack(float lo, float hi) {
-  u64 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void f2_unpack(u64 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ u64 f2_fma(u64 a, u64 b, u64 c) {
-  u64 d;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-  return d;
-}
-__device__ __forceinline__ u64 f2_add(u64 a, u64 b) {
-  u64 d;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
-__device__ __forceinline__ u64 f2_mul(u64 a, u64 b) {
-  u64 d;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
 __device__ __forceinline__ void bar_sync_64() { asm volatile("bar.sync 1, 64;" ::: "memory"); }
 
 // bins of the particle's stencil neighbours {0,1}^3 reached from cell c (bit nbh = dx*4 + dy*2 + dz)

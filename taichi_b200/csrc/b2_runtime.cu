@@ -73,6 +73,14 @@ TiRuntime_t::TiRuntime_t(int device_index) : device(device_index) {
   if (prop.major < 10)
     throw B2Error(TI_ERROR_NOT_SUPPORTED, "libb200mpm is built for sm_100a only");
   num_sms = prop.multiProcessorCount;
+  {  // host<->device staging buffers come from the stream-ordered pool: keep them cached across
+     // synchronisations (the default threshold of 0 hands the memory back at every sync)
+    cudaMemPool_t mp;
+    if (cudaDeviceGetDefaultMemPool(&mp, device_index) == cudaSuccess) {
+      unsigned long long keep = ~0ull;
+      cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+  }
   pool_size = g_pool_size;
   B2_CUDA(cudaMalloc(&pool_mem, pool_size));
   B2_CUDA(cudaMemsetAsync(pool_mem, 0, pool_size, stream()));
