@@ -319,61 +319,68 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
     int bx, by, bz;
     mpm_unkey(M, U.key, bx, by, bz);
     if (n > 0) {
-      // ---- loads: all four planes of this thread's <= 3 entries are in flight before anything waits ----
-      float4 p0[3], p1[3], p2[3], p3[3];
-      int ck[3];
+      // ---- loads + stage: the four planes of two entries are in flight at any time (a third entry only
+      // exists for threads < n - 448; its loads are issued once the first entry's registers are free) ----
       const u32 off0 = U.q0 % MPM_CHUNK, cid0 = U.cid[0], cid1 = U.cid[1], cid2 = U.cid[2];
-#pragma unroll
-      for (int e = 0; e < 3; e++) {
+      const int L = U.L;
+      const float invL = U.invL;
+      struct Ent {
+        float4 p0, p1, p2, p3;
+        int ck;
+      };
+      auto load = [&](int e, Ent &E) {
         const int t = tid + e * P2G_NW;
-        ck[e] = t < n ? (int)U.ck[t] : 0xffff;
-        if (ck[e] != 0xffff) {
+        E.ck = t < n ? (int)U.ck[t] : 0xffff;
+        if (E.ck != 0xffff) {
           const u8 *ent = p2g_entry_ptr(M, gen, off0, cid0, cid1, cid2, t);
-          p0[e] = *(const float4 *)ent;
-          p1[e] = *(const float4 *)(ent + MPM_PLANE_BYTES);
-          p2[e] = *(const float4 *)(ent + 2 * MPM_PLANE_BYTES);
-          p3[e] = *(const float4 *)(ent + 3 * MPM_PLANE_BYTES);
+          E.p0 = *(const float4 *)ent;
+          E.p1 = *(const float4 *)(ent + MPM_PLANE_BYTES);
+          E.p2 = *(const float4 *)(ent + 2 * MPM_PLANE_BYTES);
+          E.p3 = *(const float4 *)(ent + 3 * MPM_PLANE_BYTES);
         }
-      }
+      };
+      auto stage = [&](int e, const Ent &E) {
+        if (E.ck == 0xffff) return;
+        const int c = E.ck >> 10, r = E.ck & 1023;
+        const u32 info = U.cinfo[c];
+        const int sgm = (int)(((float)r + 0.5f) * invL), k = r - sgm * L;
+        const int uu = sgm < (int)(info & 0xffu) ? (int)((info >> 8) & 0xffu) + sgm : (int)(info >> 16);
+        const int pos = U.rowstart[k] + uu;
+        {  // cell-major order for G2P: entry (cstart[c] + r) of the unit's order plane names this entry
+          const u32 qs = off0 + (u32)U.cstart[c] + (u32)r, ci = qs / MPM_CHUNK;
+          u8 *chn = mpm_chunk_ptr(M, gen, ci == 0 ? cid0 : ci == 1 ? cid1 : cid2);
+          ((unsigned short *)(chn + MPM_PERM_OFF))[qs % MPM_CHUNK] = (unsigned short)(tid + e * P2G_NW);
+        }
+        MpmStencil s;
+        mpm_stencil(M, E.p0.x, E.p0.y, E.p0.z, s);
+        const float stress = M.stress_k * (E.p0.w - 1.0f);
+        // A' = (stress I + m C) dx ; b = m v - A' fx ; node value = b + A' o
+        const float m = M.p_mass;
+        const float A00 = (stress + m * E.p1.w) * M.dx, A01 = m * E.p2.x * M.dx, A02 = m * E.p2.y * M.dx;
+        const float A10 = m * E.p2.z * M.dx, A11 = (stress + m * E.p2.w) * M.dx, A12 = m * E.p3.x * M.dx;
+        const float A20 = m * E.p3.y * M.dx, A21 = m * E.p3.z * M.dx, A22 = (stress + m * E.p3.w) * M.dx;
+        const float b0 = m * E.p1.x - (A00 * s.fx[0] + A01 * s.fx[1] + A02 * s.fx[2]);
+        const float b1 = m * E.p1.y - (A10 * s.fx[0] + A11 * s.fx[1] + A12 * s.fx[2]);
+        const float b2 = m * E.p1.z - (A20 * s.fx[0] + A21 * s.fx[1] + A22 * s.fx[2]);
+        S.stg[0][pos] = make_float4(s.w[0][1], s.w[1][1], s.w[2][1], s.w[0][2]);
+        S.stg[1][pos] = make_float4(s.w[1][2], s.w[2][2], s.fx[0], 0.0f);
+        S.stg[2][pos] = make_float4(b0, b1, A00, A10);
+        S.stg[3][pos] = make_float4(A01, A11, A02, A12);
+        S.stg[4][pos] = make_float4(b2, A20, A21, A22);
+      };
+      Ent Ea, Eb;
+      load(0, Ea);
+      load(1, Eb);
       // neighbour blocks that already exist are resolved now (latency hidden behind the stage phase);
       // touched-but-inactive ones are activated before the flush
       if (tid >= P2G_NW - 8) {
         const int nbh = tid - (P2G_NW - 8);
         S.nb[nbh] = mpm_block_ptr<false>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
       }
-      // ---- stage ----------------------------------------------------------------------------------
-      const int L = U.L;
-      const float invL = U.invL;
-#pragma unroll
-      for (int e = 0; e < 3; e++)
-        if (ck[e] != 0xffff) {
-          const int c = ck[e] >> 10, r = ck[e] & 1023;
-          const u32 info = U.cinfo[c];
-          const int sgm = (int)(((float)r + 0.5f) * invL), k = r - sgm * L;
-          const int uu = sgm < (int)(info & 0xffu) ? (int)((info >> 8) & 0xffu) + sgm : (int)(info >> 16);
-          const int pos = U.rowstart[k] + uu;
-          {  // cell-major order for G2P: entry (cstart[c] + r) of the unit's order plane names this entry
-            const u32 qs = off0 + (u32)U.cstart[c] + (u32)r, ci = qs / MPM_CHUNK;
-            u8 *chn = mpm_chunk_ptr(M, gen, ci == 0 ? cid0 : ci == 1 ? cid1 : cid2);
-            ((unsigned short *)(chn + MPM_PERM_OFF))[qs % MPM_CHUNK] = (unsigned short)(tid + e * P2G_NW);
-          }
-          MpmStencil s;
-          mpm_stencil(M, p0[e].x, p0[e].y, p0[e].z, s);
-          const float stress = M.stress_k * (p0[e].w - 1.0f);
-          // A' = (stress I + m C) dx ; b = m v - A' fx ; node value = b + A' o
-          const float m = M.p_mass;
-          const float A00 = (stress + m * p1[e].w) * M.dx, A01 = m * p2[e].x * M.dx, A02 = m * p2[e].y * M.dx;
-          const float A10 = m * p2[e].z * M.dx, A11 = (stress + m * p2[e].w) * M.dx, A12 = m * p3[e].x * M.dx;
-          const float A20 = m * p3[e].y * M.dx, A21 = m * p3[e].z * M.dx, A22 = (stress + m * p3[e].w) * M.dx;
-          const float b0 = m * p1[e].x - (A00 * s.fx[0] + A01 * s.fx[1] + A02 * s.fx[2]);
-          const float b1 = m * p1[e].y - (A10 * s.fx[0] + A11 * s.fx[1] + A12 * s.fx[2]);
-          const float b2 = m * p1[e].z - (A20 * s.fx[0] + A21 * s.fx[1] + A22 * s.fx[2]);
-          S.stg[0][pos] = make_float4(s.w[0][1], s.w[1][1], s.w[2][1], s.w[0][2]);
-          S.stg[1][pos] = make_float4(s.w[1][2], s.w[2][2], s.fx[0], 0.0f);
-          S.stg[2][pos] = make_float4(b0, b1, A00, A10);
-          S.stg[3][pos] = make_float4(A01, A11, A02, A12);
-          S.stg[4][pos] = make_float4(b2, A20, A21, A22);
-        }
+      stage(0, Ea);
+      load(2, Ea);
+      stage(1, Eb);
+      stage(2, Ea);
     }
     TCK(1);
     // ---- count the NEXT unit; the helper orders it while this unit is scattered and flushed -----------
