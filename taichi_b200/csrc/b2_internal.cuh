@@ -84,6 +84,8 @@ struct B2SNodeDev {
   int chunk_size, dtype_bytes;
   // compact list of axes with shape > 1, ascending
   int nax, ax[B2_MAX_AXES];
+  // every shape of this SNode is a power of two: digit_a(l) = (l >> acc_shift[a]) & (shape[a] - 1)
+  int pot, acc_shift[B2_MAX_AXES];
 };
 
 struct B2TreeDev {
@@ -137,7 +139,11 @@ __device__ __forceinline__ u64 b2_pool_alloc(B2Pool *pool, u64 bytes) {
 // Claim-or-wait on a lazily created pointer-sized slot. `make` runs in exactly one thread.
 template <typename F>
 __device__ __forceinline__ u64 b2_ensure(u64 *slot, F make) {
-  u64 v = b2_ld_volatile(slot);
+  // a published pointer never changes again, so a (possibly stale) L1-cached read may be trusted when it
+  // shows one; 0 / BUSY go on to the coherent path
+  u64 v = *slot;
+  if (v > B2_BUSY) return v;
+  v = b2_ld_volatile(slot);
   if (v > B2_BUSY) return v;
   if (v == 0) {
     u64 old = atomicCAS(slot, 0ull, B2_BUSY);
@@ -343,6 +349,13 @@ __device__ __forceinline__ int b2_num_elements(const B2SNodeDev &s, u8 *node) {
 __device__ __forceinline__ void b2_refine(const B2SNodeDev &s, const int *in, int *out, int l) {
 #pragma unroll
   for (int a = 0; a < B2_MAX_AXES; a++) out[a] = in[a] * s.shape[a];
+  if (s.pot) {
+    for (int k = 0; k < s.nax; k++) {
+      int a = s.ax[k];
+      out[a] += (int)(((u32)l >> s.acc_shift[a]) & (u32)(s.shape[a] - 1));
+    }
+    return;
+  }
   for (int k = 0; k < s.nax; k++) {
     int a = s.ax[k];
     out[a] += (int)(((u32)l / (u32)s.acc[a]) % (u32)s.shape[a]);

@@ -32,7 +32,7 @@
 #define P2G_PASS MPM_PASS          /* bin entries per work unit                                  */
 #define P2G_UNITS 74               /* worker thread triples                                      */
 #define P2G_XUNITS (P2G_UNITS - 64)/* units beyond one per cell                                  */
-#define P2G_CAP (P2G_PASS + 64)    /* staging slots: rows are padded to odd lengths              */
+#define P2G_CAP (P2G_PASS + 32)    /* staging slots: the first 32 rows are padded to odd lengths */
 #define P2G_TASKS 280              /* flush tasks: pad nodes, the heavy ones split in groups of <= 9 sources */
 #define P2G_ZERO 1728              /* partial slot that is kept zero (padding of short tasks)    */
 
@@ -57,7 +57,6 @@ struct P2GUnit {                   // one work unit; header by the helper, ck by
 
 struct P2GShared {
   float4 stg[5][P2G_CAP];          // staging planes; the 64 x 27 per-cell partials (+ zero slot) alias them later
-  P2GTab tab;
   P2GUnit unit[2];
   int cnt[64];                     // particles per cell (counted by the workers, consumed and zeroed by the helper)
   int hist[64];                    // helper: cells per last-unit length
@@ -169,7 +168,8 @@ __device__ __forceinline__ void p2g_order(const MpmDev &M, int gen, P2GShared &S
   const int nkB = sfx - hA - hB, nkA = nkB + hB;  // last units longer than 2*lane+1 / 2*lane
   S.nk[cA] = nkA, S.nk[cB] = nkB;
   // row k: every full unit + the last units longer than k, padded to an odd length
-  const int lenA = cA < L ? ((F + nkA) | 1) : 0, lenB = cB < L ? ((F + nkB) | 1) : 0;
+  const int padr = lane < 16 ? 1 : 0;  // rows 0..31 only: P2G_CAP
+  const int lenA = cA < L ? ((F + nkA) | padr) : 0, lenB = cB < L ? ((F + nkB) | padr) : 0;
   int ps = lenA + lenB;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -222,9 +222,9 @@ __device__ __forceinline__ void p2g_count(const MpmDev &M, int gen, u32 nslots, 
 
 // one flush task: sum <= 9 partials of one pad node, one vector red into the destination block
 __device__ __forceinline__ void p2g_flush_task(const MpmDev &M, const P2GShared &S, const ulonglong2 *PP, int task) {
-  const u32 *row = (const u32 *)&S.tab.task[task][0];
-  const uint4 t0 = make_uint4(row[0], row[1], row[2], row[3]);  // sources 0..7
-  const u32 t1 = row[4];                                        // source 8, pad node
+  const u32 *row = (const u32 *)M.p2g_tab + task * 5;  // 20-B rows, read-only: stays in L1
+  const uint4 t0 = make_uint4(__ldg(row), __ldg(row + 1), __ldg(row + 2), __ldg(row + 3));  // sources 0..7
+  const u32 t1 = __ldg(row + 4);                                                             // source 8, pad node
   const ulonglong2 r0 = PP[t0.x & 0xffffu], r1 = PP[t0.x >> 16], r2 = PP[t0.y & 0xffffu], r3 = PP[t0.y >> 16], r4 = PP[t0.z & 0xffffu];
   const ulonglong2 r5 = PP[t0.z >> 16], r6 = PP[t0.w & 0xffffu], r7 = PP[t0.w >> 16], r8 = PP[t1 & 0xffffu];
   const u64 sxy = f2_add(f2_add(f2_add(r0.x, r1.x), f2_add(r2.x, r3.x)), f2_add(f2_add(r4.x, r5.x), f2_add(f2_add(r6.x, r7.x), r8.x)));
@@ -244,6 +244,7 @@ __device__ __forceinline__ void p2g_flush_task(const MpmDev &M, const P2GShared 
 #else
 #define TCK(i) do { } while (0)
 #endif
+static_assert(sizeof(P2GShared) <= 55 * 1024, "4 CTAs per SM");
 __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
 #ifdef P2G_TIMING
   long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
@@ -253,7 +254,6 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
   P2GShared &S = *(P2GShared *)p2g_smem;
   const int tid = threadIdx.x, lane = tid & 31;
   const u32 nslots = *M.nslots;
-  for (int i = tid; i < (int)(sizeof(P2GTab) / 4); i += P2G_NT) ((u32 *)&S.tab)[i] = ((const u32 *)M.p2g_tab)[i];
   if (tid < 64) S.cnt[tid] = 0, S.hist[tid] = 0;
 
   if (tid >= P2G_NW) {

@@ -345,6 +345,14 @@ B2Tree_t::B2Tree_t(TiRuntime_t *rt_, const B2SNodeDesc *desc, int n) : rt(rt_) {
       d.acc[a] = x.acc[a];
       if (x.shape[a] > 1) d.ax[d.nax++] = a;
     }
+    d.pot = 1;
+    for (int a = 0; a < B2_MAX_AXES; a++) {
+      auto is_pot = [](long long v) { return v > 0 && (v & (v - 1)) == 0; };
+      if (!is_pot(x.shape[a]) || !is_pot(x.acc[a])) d.pot = 0;
+      int sh = 0;
+      while ((1ll << (sh + 1)) <= (long long)x.acc[a]) sh++;
+      d.acc_shift[a] = sh;
+    }
     d.num_cells = x.num_cells;
     d.cell_size = x.cell_size;
     d.node_size = x.node_size;
@@ -490,9 +498,14 @@ __global__ void __launch_bounds__(256) k_listgen_nonroot(B2TreeDev *T, int pid, 
   B2CList *PL = T->lists[pid];
   B2CList *CL = T->lists[cid];
   const u32 np = PL->count;
-  for (u32 e = blockIdx.x; e < np; e += gridDim.x) {
-    const B2Element E = *(const B2Element *)b2_list_get(PL, e);
-    for (int j0 = E.lo; j0 < E.hi; j0 += blockDim.x) {
+  // work unit = blockDim consecutive cells of one parent Element (an Element spans <= 1024 cells), so a
+  // short parent list (C4: 32 Elements of 1024 pointer cells) still spreads over 128 CTAs
+  const u32 upe = (B2_LISTGEN_MAX_ELEMENT + blockDim.x - 1) / blockDim.x;
+  for (u32 u = blockIdx.x; u < np * upe; u += gridDim.x) {
+    const B2Element E = *(const B2Element *)b2_list_get(PL, u / upe);
+    {
+      const int j0 = E.lo + (int)((u % upe) * blockDim.x);
+      if (j0 >= E.hi) continue;  // uniform
       const int j = j0 + threadIdx.x;
       int cnt = 0, n = 0;
       u8 *chn = nullptr;
