@@ -348,12 +348,21 @@ TI_DLL_EXPORT B2Mpm b2_mpm_create(TiRuntime runtime, const B2MpmParams *params);
 TI_DLL_EXPORT void b2_mpm_destroy(B2Mpm mpm);
 TI_DLL_EXPORT B2Tree b2_mpm_tree(B2Mpm mpm);          /* the grid's SNode tree (leaf: dense 4^3 of {vx,vy,vz,m}) */
 TI_DLL_EXPORT int32_t b2_mpm_leaf_snode(B2Mpm mpm);   /* id of the dense(4^3) SNode   */
-/* x[N][3], v[N][3], C[N][3][3], J[N] in the reference's field layout; host or device. */
+/* x[N][3], v[N][3], C[N][3][3], J[N] in the reference's field layout; host or device.
+ * Host arrays are uploaded on a copy stream into double-buffered device staging (the role of the launcher's
+ * H2D staging of host ndarray args, kernel_launcher.cpp:78-107) and binned on the compute stream behind an
+ * event: with page-locked arrays the call returns at once and the upload overlaps earlier work still running;
+ * the arrays must stay unchanged until ti_wait() / b2_mpm_wait_io(). Pageable arrays are read before return. */
 TI_DLL_EXPORT int32_t b2_mpm_set_particles(B2Mpm mpm, int64_t n, const float *x_any, const float *v_any, const float *C_any, const float *J_any);
 TI_DLL_EXPORT int32_t b2_mpm_add_particles(B2Mpm mpm, int64_t n, const float *x_any, const float *v_any, const float *C_any, const float *J_any, const int32_t *ids_any);
 TI_DLL_EXPORT int64_t b2_mpm_num_particles(B2Mpm mpm);
 /* Any pointer may be NULL. Output is in original particle-id order. */
 TI_DLL_EXPORT int32_t b2_mpm_get_particles(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *J_any);
+/* Same, but host arrays are filled by a copy stream after return (the D2H half of kernel_launcher.cpp:175-186
+ * without its synchronisation): valid after b2_mpm_wait_io(). Two downloads may be in flight. */
+TI_DLL_EXPORT int32_t b2_mpm_get_particles_async(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *J_any);
+/* Blocks until every upload and download issued through this solver has finished. */
+TI_DLL_EXPORT int32_t b2_mpm_wait_io(B2Mpm mpm);
 TI_DLL_EXPORT int32_t b2_mpm_substep(B2Mpm mpm, int32_t nsteps);
 /* individual phases (mpm88_graph_aot.py kernel split) */
 TI_DLL_EXPORT int32_t b2_mpm_clear_grid(B2Mpm mpm);

@@ -157,6 +157,8 @@ SIGNATURES = {
     "b2_mpm_add_particles": (C.c_int32, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2_mpm_num_particles": (C.c_int64, [C.c_void_p]),
     "b2_mpm_get_particles": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2_mpm_get_particles_async": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2_mpm_wait_io": (C.c_int32, [C.c_void_p]),
     "b2_mpm_substep": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b2_mpm_clear_grid": (C.c_int32, [C.c_void_p]),
     "b2_mpm_p2g": (C.c_int32, [C.c_void_p]),

@@ -575,6 +575,21 @@ struct B2Mpm_t {
   long long phase_count = 0;
   std::vector<void *> allocs;
 
+  // Host <-> device particle I/O runs on two copy streams with double-buffered device staging, so that the
+  // upload of the next state and the download of the last result overlap the substeps in between.
+  struct Io {
+    cudaStream_t h2d = nullptr, d2h = nullptr;
+    void *stage[2] = {nullptr, nullptr}, *out[2] = {nullptr, nullptr};
+    size_t stage_cap[2] = {0, 0}, out_cap[2] = {0, 0};
+    cudaEvent_t up_done[2], stage_free[2], out_ready[2], out_free[2];
+    bool ready = false;
+    unsigned up_i = 0, out_i = 0;
+    void ensure();
+    void *reserve(void **buf, size_t *cap, size_t need);
+    void wait();
+    void destroy();
+  } io;
+
   template <typename T>
   T *dalloc(size_t count, int fill = 0) {
     void *p = nullptr;
@@ -720,8 +735,42 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   }
   rt->sync();
 }
+void B2Mpm_t::Io::ensure() {
+  if (ready) return;
+  B2_CUDA(cudaStreamCreateWithFlags(&h2d, cudaStreamNonBlocking));
+  B2_CUDA(cudaStreamCreateWithFlags(&d2h, cudaStreamNonBlocking));
+  for (int b = 0; b < 2; b++)
+    for (cudaEvent_t *e : {&up_done[b], &stage_free[b], &out_ready[b], &out_free[b]}) B2_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  ready = true;
+}
+void *B2Mpm_t::Io::reserve(void **buf, size_t *cap, size_t need) {
+  if (*cap < need) {  // grows on first use only; everything in flight on the old buffer is drained first
+    B2_CUDA(cudaDeviceSynchronize());
+    if (*buf) B2_CUDA(cudaFree(*buf));
+    *buf = nullptr, *cap = 0;
+    B2_CUDA(cudaMalloc(buf, need));
+    *cap = need;
+  }
+  return *buf;
+}
+void B2Mpm_t::Io::wait() {
+  if (!ready) return;
+  B2_CUDA(cudaStreamSynchronize(h2d));
+  B2_CUDA(cudaStreamSynchronize(d2h));
+}
+void B2Mpm_t::Io::destroy() {
+  if (!ready) return;
+  cudaStreamSynchronize(h2d), cudaStreamSynchronize(d2h);
+  for (int b = 0; b < 2; b++) {
+    cudaFree(stage[b]), cudaFree(out[b]);
+    cudaEventDestroy(up_done[b]), cudaEventDestroy(stage_free[b]), cudaEventDestroy(out_ready[b]), cudaEventDestroy(out_free[b]);
+  }
+  cudaStreamDestroy(h2d), cudaStreamDestroy(d2h);
+  ready = false;
+}
 B2Mpm_t::~B2Mpm_t() {
   cudaStreamSynchronize(rt->stream());
+  io.destroy();
   for (void *p : allocs) cudaFree(p);
   for (auto &e : prof_events) cudaEventDestroy(e);
   delete tree;
@@ -860,6 +909,31 @@ int32_t b2_mpm_add_particles(B2Mpm m, int64_t n, const float *x, const float *v,
   require(x != nullptr, TI_ERROR_ARGUMENT_NULL, "x");
   require(m->n_particles + n <= m->prm.max_particles, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "more particles than max_particles");
   cudaStream_t st = m->rt->stream();
+  auto on_host = [](const void *p) { return p == nullptr || !b2_is_device_pointer(p); };
+  if (!b2_is_device_pointer(x) && on_host(v) && on_host(C) && on_host(J) && on_host(ids)) {
+    // host arrays: upload on the copy stream into the staging buffer whose last insert has finished
+    B2Mpm_t::Io &io = m->io;
+    io.ensure();
+    const int b = (int)(io.up_i++ & 1u);
+    char *base = (char *)io.reserve(&io.stage[b], &io.stage_cap[b], (size_t)n * 68);
+    B2_CUDA(cudaStreamWaitEvent(io.h2d, io.stage_free[b], 0));
+    float *dx = (float *)base, *dv = (float *)(base + (size_t)n * 12), *dC = (float *)(base + (size_t)n * 24), *dJ = (float *)(base + (size_t)n * 60);
+    int *di = (int *)(base + (size_t)n * 64);
+    B2_CUDA(cudaMemcpyAsync(dx, x, (size_t)n * 12, cudaMemcpyHostToDevice, io.h2d));
+    if (v) B2_CUDA(cudaMemcpyAsync(dv, v, (size_t)n * 12, cudaMemcpyHostToDevice, io.h2d));
+    if (C) B2_CUDA(cudaMemcpyAsync(dC, C, (size_t)n * 36, cudaMemcpyHostToDevice, io.h2d));
+    if (J) B2_CUDA(cudaMemcpyAsync(dJ, J, (size_t)n * 4, cudaMemcpyHostToDevice, io.h2d));
+    if (ids) B2_CUDA(cudaMemcpyAsync(di, ids, (size_t)n * 4, cudaMemcpyHostToDevice, io.h2d));
+    B2_CUDA(cudaEventRecord(io.up_done[b], io.h2d));
+    B2_CUDA(cudaStreamWaitEvent(st, io.up_done[b], 0));
+    k_mpm_insert<<<m->rt->grid_for(n, 256, 8), 256, 0, st>>>(m->M, m->gen, dx, v ? dv : nullptr, C ? dC : nullptr, J ? dJ : nullptr, ids ? di : nullptr, n, m->n_particles);
+    m->rt->count_launch();
+    B2_CUDA(cudaGetLastError());
+    B2_CUDA(cudaEventRecord(io.stage_free[b], st));
+    m->n_particles += n;
+    m->order_valid = false;
+    return 0;
+  }
   B2Staged sx, sv, sc, sj, si;
   sx.init(x, (size_t)n * 12, true, false, st);
   if (v) sv.init(v, (size_t)n * 12, true, false, st);
@@ -883,12 +957,38 @@ int32_t b2_mpm_set_particles(B2Mpm m, int64_t n, const float *x, const float *v,
   return b2_mpm_add_particles(m, n, x, v, C, J, nullptr);
 }
 int64_t b2_mpm_num_particles(B2Mpm m) { return m ? m->n_particles : -1; }
-int32_t b2_mpm_get_particles(B2Mpm m, float *x, float *v, float *C, float *J) {
+static int32_t mpm_get_particles(B2Mpm m, float *x, float *v, float *C, float *J, bool wait) {
   B2_API_BEGIN
   require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
   const int64_t n = m->n_particles;
   if (n == 0) return 0;
   cudaStream_t st = m->rt->stream();
+  auto on_host = [](const void *p) { return p == nullptr || !b2_is_device_pointer(p); };
+  if (on_host(x) && on_host(v) && on_host(C) && on_host(J)) {
+    // host arrays: extract into the staging buffer whose last download has finished, download on the copy stream
+    B2Mpm_t::Io &io = m->io;
+    io.ensure();
+    const int b = (int)(io.out_i++ & 1u);
+    const size_t ox = 0, ov = ox + (x ? (size_t)n * 12 : 0), oc = ov + (v ? (size_t)n * 12 : 0), oj = oc + (C ? (size_t)n * 36 : 0);
+    const size_t need = oj + (J ? (size_t)n * 4 : 0);
+    if (need == 0) return 0;
+    char *base = (char *)io.reserve(&io.out[b], &io.out_cap[b], need);
+    B2_CUDA(cudaStreamWaitEvent(st, io.out_free[b], 0));
+    B2_CUDA(cudaMemsetAsync(base, 0, need, st));
+    k_mpm_extract<<<m->rt->num_sms * 8, 256, 0, st>>>(m->M, m->gen, x ? (float *)(base + ox) : nullptr, v ? (float *)(base + ov) : nullptr,
+                                                      C ? (float *)(base + oc) : nullptr, J ? (float *)(base + oj) : nullptr, n);
+    m->rt->count_launch();
+    B2_CUDA(cudaGetLastError());
+    B2_CUDA(cudaEventRecord(io.out_ready[b], st));
+    B2_CUDA(cudaStreamWaitEvent(io.d2h, io.out_ready[b], 0));
+    if (x) B2_CUDA(cudaMemcpyAsync(x, base + ox, (size_t)n * 12, cudaMemcpyDeviceToHost, io.d2h));
+    if (v) B2_CUDA(cudaMemcpyAsync(v, base + ov, (size_t)n * 12, cudaMemcpyDeviceToHost, io.d2h));
+    if (C) B2_CUDA(cudaMemcpyAsync(C, base + oc, (size_t)n * 36, cudaMemcpyDeviceToHost, io.d2h));
+    if (J) B2_CUDA(cudaMemcpyAsync(J, base + oj, (size_t)n * 4, cudaMemcpyDeviceToHost, io.d2h));
+    B2_CUDA(cudaEventRecord(io.out_free[b], io.d2h));
+    if (wait) B2_CUDA(cudaStreamSynchronize(io.d2h));
+    return 0;
+  }
   B2Staged sx, sv, sc, sj;
   if (x) sx.init(x, (size_t)n * 12, false, true, st);
   if (v) sv.init(v, (size_t)n * 12, false, true, st);
@@ -898,6 +998,15 @@ int32_t b2_mpm_get_particles(B2Mpm m, float *x, float *v, float *C, float *J) {
   m->rt->count_launch();
   B2_CUDA(cudaGetLastError());
   sx.finish(), sv.finish(), sc.finish(), sj.finish();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_get_particles(B2Mpm m, float *x, float *v, float *C, float *J) { return mpm_get_particles(m, x, v, C, J, true); }
+int32_t b2_mpm_get_particles_async(B2Mpm m, float *x, float *v, float *C, float *J) { return mpm_get_particles(m, x, v, C, J, false); }
+int32_t b2_mpm_wait_io(B2Mpm m) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  m->io.wait();
   return 0;
   B2_API_END(-1)
 }

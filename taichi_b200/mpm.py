@@ -185,14 +185,21 @@ class Mpm3D:
     def num_particles(self):
         return int(lib.b2_mpm_num_particles(self.handle))
 
-    def get_particles(self, x=None, v=None, Cm=None, J=None):
-        """Fills the given arrays (numpy or torch, any may be None); allocates numpy ones if none given."""
+    def get_particles(self, x=None, v=None, Cm=None, J=None, wait=True):
+        """Fills the given arrays (numpy or torch, any may be None); allocates numpy ones if none given.
+        wait=False: host arrays (page-locked) are filled by a copy stream after return -- call wait_io()
+        before reading them; the download then overlaps whatever is enqueued next."""
         if x is None and v is None and Cm is None and J is None:
             n = self.num_particles
             x, v = np.empty((n, 3), np.float32), np.empty((n, 3), np.float32)
             Cm, J = np.empty((n, 3, 3), np.float32), np.empty(n, np.float32)
-        self._ok(lib.b2_mpm_get_particles(self.handle, _ptr(x), _ptr(v), _ptr(Cm), _ptr(J)))
+        fn = lib.b2_mpm_get_particles if wait else lib.b2_mpm_get_particles_async
+        self._ok(fn(self.handle, _ptr(x), _ptr(v), _ptr(Cm), _ptr(J)))
         return x, v, Cm, J
+
+    def wait_io(self):
+        """Blocks until every particle upload / download issued through this solver has finished."""
+        self._ok(lib.b2_mpm_wait_io(self.handle))
 
     def substep(self, n=1):
         self._ok(lib.b2_mpm_substep(self.handle, n))
