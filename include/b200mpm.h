@@ -392,6 +392,9 @@ TI_DLL_EXPORT int32_t b2_mpm_extract_migrants(B2Mpm mpm, int32_t side, void *buf
 TI_DLL_EXPORT int32_t b2_mpm_insert_records(B2Mpm mpm, const void *buf_dev, int64_t cap_records);
 /* compact copy of the live particles + their ids; returns how many (synchronises) */
 TI_DLL_EXPORT int64_t b2_mpm_export(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *J_any, int32_t *ids_any, int64_t cap);
+/* Same records into HOST arrays of `cap` entries each, filled by the solver's copy stream after return; *count
+ * (host) receives the number of records (entries past it are unspecified). Valid after b2_mpm_wait_io(). */
+TI_DLL_EXPORT int32_t b2_mpm_export_async(B2Mpm mpm, float *x, float *v, float *C, float *J, int32_t *ids, int64_t cap, int64_t *count);
 
 /* Native slab driver: the whole decomposed substep (kernels + ncclSend/ncclRecv over NVLink) is
    enqueued from C++ on the runtime's stream; no host synchronisation.  NCCL is bound at run time

@@ -182,6 +182,7 @@ SIGNATURES = {
     "b2_slab_substep": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b2_slab_tune": (C.c_int32, [C.c_void_p]),
     "b2_mpm_export": (C.c_int64, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
+    "b2_mpm_export_async": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
 }
 
 

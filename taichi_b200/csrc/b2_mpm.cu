@@ -1146,6 +1146,40 @@ int32_t b2_mpm_insert_records(B2Mpm m, const void *buf, int64_t cap) {
   return 0;
   B2_API_END(-1)
 }
+int32_t b2_mpm_export_async(B2Mpm m, float *x, float *v, float *C, float *J, int32_t *ids, int64_t cap, int64_t *count) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  require(count != nullptr, TI_ERROR_ARGUMENT_NULL, "count");
+  require(cap > 0, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "cap");
+  auto on_host = [](const void *p) { return p == nullptr || !b2_is_device_pointer(p); };
+  require(on_host(x) && on_host(v) && on_host(C) && on_host(J) && on_host(ids) && !b2_is_device_pointer(count), TI_ERROR_INVALID_ARGUMENT,
+          "export_async fills host arrays");
+  cudaStream_t st = m->rt->stream();
+  B2Mpm_t::Io &io = m->io;
+  io.ensure();
+  const int b = (int)(io.out_i++ & 1u);
+  const size_t ox = 16, ov = ox + (x ? (size_t)cap * 12 : 0), oc = ov + (v ? (size_t)cap * 12 : 0), oj = oc + (C ? (size_t)cap * 36 : 0);
+  const size_t oi = oj + (J ? (size_t)cap * 4 : 0), need = oi + (ids ? (size_t)cap * 4 : 0);
+  char *base = (char *)io.reserve(&io.out[b], &io.out_cap[b], need);
+  B2_CUDA(cudaStreamWaitEvent(st, io.out_free[b], 0));
+  B2_CUDA(cudaMemsetAsync(base, 0, 16, st));  // the record counter lives in front of the arrays
+  k_mpm_export<<<m->rt->num_sms * 8, 256, 0, st>>>(m->M, m->gen, x ? (float *)(base + ox) : nullptr, v ? (float *)(base + ov) : nullptr,
+                                                   C ? (float *)(base + oc) : nullptr, J ? (float *)(base + oj) : nullptr,
+                                                   ids ? (int *)(base + oi) : nullptr, cap, (unsigned long long *)base);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  B2_CUDA(cudaEventRecord(io.out_ready[b], st));
+  B2_CUDA(cudaStreamWaitEvent(io.d2h, io.out_ready[b], 0));
+  B2_CUDA(cudaMemcpyAsync(count, base, 8, cudaMemcpyDeviceToHost, io.d2h));
+  if (x) B2_CUDA(cudaMemcpyAsync(x, base + ox, (size_t)cap * 12, cudaMemcpyDeviceToHost, io.d2h));
+  if (v) B2_CUDA(cudaMemcpyAsync(v, base + ov, (size_t)cap * 12, cudaMemcpyDeviceToHost, io.d2h));
+  if (C) B2_CUDA(cudaMemcpyAsync(C, base + oc, (size_t)cap * 36, cudaMemcpyDeviceToHost, io.d2h));
+  if (J) B2_CUDA(cudaMemcpyAsync(J, base + oj, (size_t)cap * 4, cudaMemcpyDeviceToHost, io.d2h));
+  if (ids) B2_CUDA(cudaMemcpyAsync(ids, base + oi, (size_t)cap * 4, cudaMemcpyDeviceToHost, io.d2h));
+  B2_CUDA(cudaEventRecord(io.out_free[b], io.d2h));
+  return 0;
+  B2_API_END(-1)
+}
 int64_t b2_mpm_export(B2Mpm m, float *x, float *v, float *C, float *J, int32_t *ids, int64_t cap) {
   B2_API_BEGIN
   require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");

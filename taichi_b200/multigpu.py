@@ -65,6 +65,15 @@ class CudaSlab:
         if len(x):
             self._ok(self.lib.b2_mpm_add_particles(self.handle, len(x), _ptr(x), _ptr(v), _ptr(Cm), _ptr(J), _ptr(ids)))
 
+    def export_async(self, cap, count, x=None, v=None, Cm=None, J=None, ids=None):
+        """Compacted live records into page-locked host arrays of `cap` entries, filled by the solver's copy
+        stream after return; `count` (pinned int64[1]) receives the record count. Valid after wait_io()."""
+        from .mpm import _ptr
+        self._ok(self.lib.b2_mpm_export_async(self.handle, _ptr(x), _ptr(v), _ptr(Cm), _ptr(J), _ptr(ids), cap, _ptr(count)))
+
+    def wait_io(self):
+        self._ok(self.lib.b2_mpm_wait_io(self.handle))
+
     def export(self, cap):
         from .mpm import _ptr
         x, v = np.empty((cap, 3), np.float32), np.empty((cap, 3), np.float32)

@@ -97,6 +97,34 @@ def test_native_driver_world1_equals_plain_substep():
     s.destroy()
 
 
+def test_export_async_equals_blocking_export():
+    """The pipelined form of the compact export (device staging + copy stream, pinned host arrays) returns the
+    same record set and count as the blocking one."""
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    import torch
+    from taichi_b200 import multigpu as mg
+    rt = get_rt()
+    x, v, Cm, J, ids = cloud()
+    s = mg.CudaSlab(rt, N_GRID, 2 * N, DT, 0, N_GRID // 4)
+    s.set_particles(x, v, Cm, J, ids)
+    d = mg.NativeSlabDriver(s, 0, 1)
+    d.substep(4)
+    ref = s.export(2 * N)
+    cap = N + N // 4
+    hx, hv = torch.empty(cap, 3).pin_memory(), torch.empty(cap, 3).pin_memory()
+    hi, cnt = torch.empty(cap, dtype=torch.int32).pin_memory(), torch.zeros(1, dtype=torch.int64).pin_memory()
+    s.export_async(cap, cnt, x=hx, v=hv, ids=hi)
+    s.wait_io()
+    n = int(cnt.item())
+    assert n == len(ref[4]) == N
+    o, r = np.argsort(hi.numpy()[:n]), np.argsort(ref[4])
+    assert np.array_equal(hi.numpy()[:n][o], ref[4][r])
+    assert np.array_equal(hx.numpy()[:n][o], ref[0][r]) and np.array_equal(hv.numpy()[:n][o], ref[1][r])
+    d.destroy()
+    s.destroy()
+
+
 def _nccl_worker(rank, world, port, out, native):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
