@@ -271,6 +271,7 @@ typedef struct B2SNodeDesc {
 
 typedef struct B2Tree_t *B2Tree;
 typedef struct B2Mpm_t *B2Mpm;
+typedef struct B2JitKernel_t *B2JitKernel;
 typedef struct B2Comm_t *B2Comm; /* NCCL communicator of the slab layer */
 typedef struct B2Slab_t *B2Slab; /* one rank's slab driver */
 
@@ -409,6 +410,25 @@ TI_DLL_EXPORT B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_
 TI_DLL_EXPORT void b2_slab_destroy(B2Slab slab);
 TI_DLL_EXPORT int32_t b2_slab_substep(B2Slab slab, int32_t nsteps);
 TI_DLL_EXPORT int32_t b2_slab_tune(B2Slab slab); /* message sizes := 2x last counts (synchronises) */
+
+/* ---- struct-for with a run-time compiled body -------------------------------------------
+ * Stands in for the reference's per-kernel codegen + CUDA JIT of a struct-for task (codegen_llvm.cpp:2089-2317,
+ * runtime/cuda/jit_cuda.cpp:8-240, kernel_launcher.cpp:15-213): `source` is CUDA C++ holding one
+ *     B2_BODY(c) { ... }                       // runs once per ACTIVE cell of the loop SNode
+ * with c.I[12] = loop index, c.read<T>(f, J) / c.write<T>(f, J, v) / c.ref<T>(f, J) (writes activate, reads of
+ * inactive cells see the ambient zero, as in lower_access.cpp:254-279), c.is_active(f, J), c.offset(J, axis, d),
+ * c.arg<T>(k); contract in taichi_b200/csrc/b2_jit.cuh.  Compiled once with NVRTC to an sm_100a cubin.
+ * A source that does not compile returns NULL with TI_ERROR_INVALID_ARGUMENT and the compiler log as message;
+ * a missing libnvrtc.so.12 returns NULL with TI_ERROR_NOT_SUPPORTED. */
+TI_DLL_EXPORT B2JitKernel b2_jit_compile(TiRuntime runtime, const char *source, const char *name);
+/* compile only, no device needed: cubin size, or -1 with the compiler log as last error */
+TI_DLL_EXPORT int64_t b2_jit_check(const char *source, const char *name);
+TI_DLL_EXPORT void b2_jit_destroy(B2JitKernel kernel);
+TI_DLL_EXPORT int64_t b2_jit_log(B2JitKernel kernel, char *out, int64_t cap); /* diagnostics; returns size needed */
+/* listgen of loop_snode (offload.cpp:174-264), then the body over its element list. field_places: <= 8 place
+ * SNode ids (field f of the body); args: <= 16 64-bit slots (scalars bit-cast, DEVICE pointers). Asynchronous. */
+TI_DLL_EXPORT int32_t b2_jit_launch(B2JitKernel kernel, B2Tree tree, int32_t loop_snode, const int32_t *field_places,
+                                    int32_t n_fields, const uint64_t *args, int32_t n_args);
 
 #ifdef __cplusplus
 }

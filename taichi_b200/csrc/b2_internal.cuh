@@ -13,8 +13,10 @@
 // recycle needs no ptr2index scan, cf. runtime.cpp:502-512); node sizes are rounded to 128 B
 // so that zero-fill and block loads are 128-bit and aligned.
 #pragma once
+#ifndef __CUDACC_RTC__  // run-time compiled struct-for bodies (b2_jit.cuh) see this header through NVRTC: no host headers there
 #include <cuda_runtime.h>
 #include <stdint.h>
+#endif
 
 #define B2_MAX_AXES 12
 #define B2_MAX_SNODES 64

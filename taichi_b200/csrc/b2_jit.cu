@@ -1,0 +1,195 @@
+// b2_jit.cu -- run-time compiled struct-for bodies: host side.
+//
+// What it stands in for in the reference: the per-kernel LLVM codegen of a struct-for task
+// (codegen_llvm.cpp:2089-2317), the CUDA JIT session (runtime/cuda/jit_cuda.cpp:8-240: PTX -> module ->
+// function) and the launcher's per-task launch (runtime/cuda/kernel_launcher.cpp:15-213).  Here the body is
+// CUDA C++ text (contract in b2_jit.cuh); it is compiled ONCE per source with NVRTC straight to an sm_100a
+// cubin (no PTX JIT in the driver), loaded through the runtime API (cudaLibraryLoadData) and launched over
+// the element list of the loop SNode, which is regenerated before the launch like the reference does
+// (offload.cpp:174-264).  libnvrtc is bound at run time: the library loads without it, and the first
+// b2_jit_compile fails loudly if it cannot be found.
+#include <dlfcn.h>
+
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "b2_host.h"
+#include "b2_jit.cuh"
+#include "build/b2_embed.h"  // b2_src_internal / b2_src_jit: the two device headers as text
+
+namespace {
+typedef struct _nvrtcProgram *nvrtcProgram;
+struct Nvrtc {
+  void *h = nullptr;
+  int (*CreateProgram)(nvrtcProgram *, const char *, const char *, int, const char *const *, const char *const *) = nullptr;
+  int (*CompileProgram)(nvrtcProgram, int, const char *const *) = nullptr;
+  int (*GetProgramLogSize)(nvrtcProgram, size_t *) = nullptr;
+  int (*GetProgramLog)(nvrtcProgram, char *) = nullptr;
+  int (*GetCUBINSize)(nvrtcProgram, size_t *) = nullptr;
+  int (*GetCUBIN)(nvrtcProgram, char *) = nullptr;
+  int (*DestroyProgram)(nvrtcProgram *) = nullptr;
+  const char *(*GetErrorString)(int) = nullptr;
+};
+Nvrtc &nvrtc() {
+  static Nvrtc n;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    const char *env = getenv("B2_NVRTC_LIB");
+    const char *cands[] = {env, "libnvrtc.so.12", "/usr/local/cuda/lib64/libnvrtc.so.12", "libnvrtc.so"};
+    for (const char *c : cands) {
+      if (!c || !*c) continue;
+      n.h = dlopen(c, RTLD_NOW | RTLD_LOCAL);
+      if (n.h) break;
+    }
+    if (!n.h) return;
+#define B2_SYM(name) n.name = (decltype(n.name))dlsym(n.h, "nvrtc" #name)
+    B2_SYM(CreateProgram), B2_SYM(CompileProgram), B2_SYM(GetProgramLogSize), B2_SYM(GetProgramLog);
+    B2_SYM(GetCUBINSize), B2_SYM(GetCUBIN), B2_SYM(DestroyProgram), B2_SYM(GetErrorString);
+#undef B2_SYM
+    if (!n.CreateProgram || !n.CompileProgram || !n.GetCUBINSize || !n.GetCUBIN || !n.DestroyProgram) n.h = nullptr;
+  });
+  return n;
+}
+}  // namespace
+
+struct B2JitKernel_t {
+  TiRuntime_t *rt = nullptr;
+  cudaLibrary_t lib = nullptr;
+  cudaKernel_t fn = nullptr;
+  B2JitTable *tab_dev = nullptr;  // launch table (fields + args), rewritten in stream order before every launch
+  std::string log;
+  size_t cubin_bytes = 0;
+};
+
+static void jit_require(bool ok, TiError code, const char *msg) {
+  if (!ok) throw B2Error(code, msg);
+}
+
+// source -> sm_100a cubin (throws with the compiler log on errors); needs no GPU
+static void jit_build(const char *source, const char *name, std::vector<char> *cubin, std::string *log) {
+  jit_require(source != nullptr, TI_ERROR_ARGUMENT_NULL, "source");
+  Nvrtc &N = nvrtc();
+  jit_require(N.h != nullptr, TI_ERROR_NOT_SUPPORTED, "libnvrtc.so.12 not found (set B2_NVRTC_LIB): struct-for bodies cannot be compiled");
+  std::string src = "#include \"b2_internal.cuh\"\n#include \"b2_jit.cuh\"\n#line 1 \"";
+  src += (name && *name) ? name : "b2_body";
+  src += "\"\n";
+  src += source;
+  src += "\n";
+  const char *headers[2] = {b2_src_internal, b2_src_jit};
+  const char *hnames[2] = {"b2_internal.cuh", "b2_jit.cuh"};
+  nvrtcProgram prog = nullptr;
+  int rc = N.CreateProgram(&prog, src.c_str(), "b2_jit_kernel.cu", 2, headers, hnames);
+  jit_require(rc == 0 && prog != nullptr, TI_ERROR_INVALID_STATE, "nvrtcCreateProgram failed");
+  const char *opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "-lineinfo"};
+  rc = N.CompileProgram(prog, 3, opts);
+  size_t ln = 0;
+  log->clear();
+  if (N.GetProgramLogSize && N.GetProgramLog && N.GetProgramLogSize(prog, &ln) == 0 && ln > 1) {
+    log->resize(ln);
+    N.GetProgramLog(prog, &(*log)[0]);
+    while (!log->empty() && (log->back() == 0 || log->back() == '\n')) log->pop_back();
+  }
+  if (rc != 0) {
+    N.DestroyProgram(&prog);
+    throw B2Error(TI_ERROR_INVALID_ARGUMENT, "struct-for body does not compile:\n" + *log);
+  }
+  size_t nb = 0;
+  rc = N.GetCUBINSize(prog, &nb);
+  cubin->resize(nb);
+  if (rc == 0 && nb) rc = N.GetCUBIN(prog, cubin->data());
+  N.DestroyProgram(&prog);
+  jit_require(rc == 0 && nb > 0, TI_ERROR_INVALID_STATE, "nvrtcGetCUBIN failed");
+}
+
+extern "C" {
+// Compile only (no device needed): size of the sm_100a cubin, or -1 with the compiler log as last error.
+int64_t b2_jit_check(const char *source, const char *name) {
+  B2_API_BEGIN
+  std::vector<char> cubin;
+  std::string log;
+  jit_build(source, name, &cubin, &log);
+  return (int64_t)cubin.size();
+  B2_API_END(-1)
+}
+B2JitKernel b2_jit_compile(TiRuntime rt, const char *source, const char *name) {
+  B2_API_BEGIN
+  jit_require(rt != nullptr, TI_ERROR_ARGUMENT_NULL, "runtime");
+  std::vector<char> cubin;
+  std::string log;
+  jit_build(source, name, &cubin, &log);
+  const size_t nb = cubin.size();
+  B2_CUDA(cudaSetDevice(rt->device));
+  std::unique_ptr<B2JitKernel_t> k(new B2JitKernel_t);
+  k->rt = rt;
+  k->log = log;
+  k->cubin_bytes = nb;
+  B2_CUDA(cudaLibraryLoadData(&k->lib, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0));
+  B2_CUDA(cudaLibraryGetKernel(&k->fn, k->lib, "b2_jit_struct_for"));
+  B2_CUDA(cudaMalloc((void **)&k->tab_dev, sizeof(B2JitTable)));
+  return k.release();
+  B2_API_END(nullptr)
+}
+
+void b2_jit_destroy(B2JitKernel k) {
+  if (!k) return;
+  cudaStreamSynchronize(k->rt->stream());
+  if (k->tab_dev) cudaFree(k->tab_dev);
+  if (k->lib) cudaLibraryUnload(k->lib);
+  delete k;
+}
+
+// Compiler diagnostics (warnings) of a successful compile; size query like ti_get_last_error.
+int64_t b2_jit_log(B2JitKernel k, char *out, int64_t cap) {
+  if (!k) return -1;
+  if (out && cap > 0) {
+    const size_t n = std::min<size_t>((size_t)cap - 1, k->log.size());
+    memcpy(out, k->log.data(), n);
+    out[n] = 0;
+  }
+  return (int64_t)k->log.size() + 1;
+}
+
+int32_t b2_jit_launch(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t *field_places, int32_t n_fields, const uint64_t *args, int32_t n_args) {
+  B2_API_BEGIN
+  jit_require(k != nullptr && t != nullptr, TI_ERROR_ARGUMENT_NULL, "kernel/tree");
+  jit_require(k->rt == t->rt, TI_ERROR_INVALID_ARGUMENT, "kernel and tree belong to different runtimes");
+  jit_require(n_fields >= 0 && n_fields <= B2_JIT_MAX_FIELDS, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "at most 8 fields per body");
+  jit_require(n_args >= 0 && n_args <= B2_JIT_MAX_ARGS, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "at most 16 arguments per body");
+  jit_require(n_fields == 0 || field_places != nullptr, TI_ERROR_ARGUMENT_NULL, "field_places");
+  jit_require(n_args == 0 || args != nullptr, TI_ERROR_ARGUMENT_NULL, "args");
+  t->check_snode(loop_snode, "jit_launch");
+  jit_require(t->s[loop_snode].type != B2T_PLACE && loop_snode != 0, TI_ERROR_INVALID_ARGUMENT, "loop SNode must be a non-root container SNode");
+  static thread_local B2JitTable tab;  // 10 KB: not on the stack
+  memset(&tab, 0, sizeof(tab));
+  tab.n_fields = n_fields, tab.n_args = n_args;
+  for (int i = 0; i < n_args; i++) tab.args[i] = args[i];
+  for (int i = 0; i < n_fields; i++) {
+    const int pid = field_places[i];
+    t->check_snode(pid, "jit_launch field");
+    const B2SNodeHost &p = t->s[pid];
+    jit_require(p.type == B2T_PLACE, TI_ERROR_INVALID_ARGUMENT, "fields are place SNodes");
+    jit_require(t->s[p.parent].type != B2T_DYNAMIC, TI_ERROR_NOT_SUPPORTED, "fields under a dynamic SNode use b2_dynamic_*");
+    tab.f[i].path = t->path_to(p.parent);
+    tab.f[i].off = p.offset_in_parent_cell;
+    tab.f[i].bytes = p.dtype_bytes;
+    tab.f[i].holder = p.parent;
+  }
+  cudaStream_t st = t->rt->stream();
+  B2_CUDA(cudaSetDevice(t->rt->device));
+  B2_CUDA(cudaMemcpyAsync(k->tab_dev, &tab, sizeof(tab), cudaMemcpyHostToDevice, st));  // pageable source: staged before return
+  t->listgen_async(loop_snode);
+  B2TreeDev *dev = t->dev;
+  int sid = loop_snode;
+  const B2JitTable *tp = k->tab_dev;
+  void *params[3] = {&dev, &sid, &tp};
+  const int64_t nc = std::min<int64_t>(t->s[loop_snode].num_cells, 1024);
+  const int block = (int)std::min<int64_t>(256, std::max<int64_t>(32, (nc + 31) / 32 * 32));
+  B2_CUDA(cudaLaunchKernel((const void *)k->fn, dim3(t->rt->num_sms * 8), dim3(block), params, 0, st));
+  t->rt->count_launch();
+  return 0;
+  B2_API_END(-1)
+}
+}  // extern "C"

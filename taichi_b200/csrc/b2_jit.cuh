@@ -1,0 +1,112 @@
+// b2_jit.cuh -- device side of run-time compiled struct-for bodies.
+//
+// Stands in for what the reference generates per kernel: the struct-for task body
+// (codegen_llvm.cpp:2089-2317), its loop-index / global-pointer lowering (lower_access.cpp:42-281,
+// scalar_pointer_lowerer.cpp:32-86) and the JIT session (runtime/cuda/jit_cuda.cpp:8-240).  The user
+// writes the body as CUDA C++:
+//
+//     B2_BODY(c) {                                   // for I in ti.grouped(loop_snode):
+//       float v = c.read<float>(0, c.I);             //   v = x[I]
+//       int J[B2_MAX_AXES]; c.offset(J, 0, +1);      //   J = I + (1, 0, ..)
+//       c.write<float>(1, J, 2.0f * v);              //   y[J] = 2 v        (activates, like the reference)
+//       atomicAdd(c.arg<float *>(0), v);             //   s[None] += v
+//     }
+//
+// The library wraps it with this header (and b2_internal.cuh), compiles it for sm_100a with NVRTC
+// and launches b2_jit_struct_for over the element list of the loop SNode.  Field f = f-th entry of the
+// place list given at launch; arg k = k-th 64-bit launch argument (scalars bit-cast, device pointers).
+#pragma once
+#define B2_JIT_MAX_FIELDS 8
+#define B2_JIT_MAX_ARGS 16
+
+struct B2JitField {
+  B2Path path;     // root .. the SNode that holds the place
+  long long off;   // byte offset of the place inside that SNode's cell
+  int bytes, holder;
+};
+struct B2JitTable {
+  int n_fields, n_args;
+  unsigned long long args[B2_JIT_MAX_ARGS];
+  B2JitField f[B2_JIT_MAX_FIELDS];
+};
+
+#ifdef __CUDACC_RTC__  // everything below exists only in the run-time compiled translation unit
+struct B2Ctx {
+  B2TreeDev *T;
+  const B2JitTable *tab;
+  const B2SNodeDev *ts;  // the loop SNode
+  const B2Element *E;    // the work item this cell belongs to
+  int sid, j;            // loop SNode id, linear cell index inside E->node
+  int I[B2_MAX_AXES];    // loop index (refine_coordinates, struct_llvm.cpp:171-188)
+
+  template <typename V>
+  __device__ __forceinline__ V arg(int k) const {
+    static_assert(sizeof(V) <= 8, "launch arguments are 64-bit slots");
+    union {
+      unsigned long long u;
+      V v;
+    } x;
+    x.u = tab->args[k];
+    return x.v;
+  }
+  // Address of field f at index J.  ACT: activate every level on the way like a write access in the
+  // reference (lower_access.cpp:254-279); otherwise inactive cells resolve to the ambient zero element.
+  template <typename V, bool ACT>
+  __device__ __forceinline__ V *ptr(int f, const int *J) const {
+    const B2JitField &F = tab->f[f];
+    const int hid = F.holder;
+    if (!ACT && hid == sid) {  // the loop's own cell, at the loop index: no walk (the path a struct-for never re-activates)
+      bool same = true;
+#pragma unroll
+      for (int a = 0; a < B2_MAX_AXES; a++) same = same && J[a] == I[a];
+      if (same) return (V *)(b2_lookup(T, sid, E->node, j) + F.off);
+    }
+    int cell;
+    u8 *node = b2_walk<ACT>(T, F.path, J, &cell, nullptr);
+    if (ACT) b2_activate_cell(T, hid, node, cell);
+    return (V *)(b2_lookup(T, hid, node, cell) + F.off);
+  }
+  template <typename V>
+  __device__ __forceinline__ V read(int f, const int *J) const { return *ptr<V, false>(f, J); }
+  template <typename V>
+  __device__ __forceinline__ void write(int f, const int *J, V v) const { *ptr<V, true>(f, J) = v; }
+  template <typename V>
+  __device__ __forceinline__ V *ref(int f, const int *J) const { return ptr<V, true>(f, J); }  // for atomics / +=
+  // ti.is_active(holder of field f, J)
+  __device__ __forceinline__ bool is_active(int f, const int *J) const {
+    const B2JitField &F = tab->f[f];
+    int cell;
+    bool dead;
+    u8 *node = b2_walk<false>(T, F.path, J, &cell, &dead);
+    return !dead && b2_is_active(T->s[F.holder], node, cell);
+  }
+  // J = I with axis a shifted by d
+  __device__ __forceinline__ void offset(int *J, int a, int d) const {
+#pragma unroll
+    for (int q = 0; q < B2_MAX_AXES; q++) J[q] = I[q];
+    J[a] += d;
+  }
+};
+
+#define B2_BODY(c) __device__ __forceinline__ void b2_body(B2Ctx &c)
+__device__ __forceinline__ void b2_body(B2Ctx &c);
+
+// parallel_struct_for (runtime.cpp:1422-1464): CTA <-> Element, thread <-> cell
+extern "C" __global__ void __launch_bounds__(256) b2_jit_struct_for(B2TreeDev *T, int sid, const B2JitTable *tab) {
+  const B2SNodeDev &ts = T->s[sid];
+  B2CList *L = T->lists[sid];
+  const u32 ne = L->count;
+  for (u32 e = blockIdx.x; e < ne; e += gridDim.x) {
+    const B2Element E = *(const B2Element *)b2_list_get(L, e);
+    for (int j0 = E.lo; j0 < E.hi; j0 += blockDim.x) {
+      const int j = j0 + threadIdx.x;
+      if (j < E.hi && b2_is_active(ts, E.node, j)) {
+        B2Ctx c;
+        c.T = T, c.tab = tab, c.ts = &ts, c.E = &E, c.sid = sid, c.j = j;
+        b2_refine(ts, E.pcoord, c.I, j);
+        b2_body(c);
+      }
+    }
+  }
+}
+#endif  // __CUDACC_RTC__

@@ -334,3 +334,69 @@ def no_activate(*_snodes):
 
 def loop_config(**_kw):
     pass
+
+
+# ---------------------------------------------------------------------------------------------
+# struct-for with a run-time compiled body (the part of @ti.kernel this library offers):
+# codegen_llvm.cpp:2089-2317 + jit_cuda.cpp in the reference, NVRTC -> sm_100a cubin here.
+# ---------------------------------------------------------------------------------------------
+def _arg_bits(a):
+    """One 64-bit launch slot: device pointers (torch CUDA tensors / objects with data_ptr), numpy scalars by their
+    dtype, python int -> i64, python float -> f32 (default_fp, compile_config.cpp:30)."""
+    if hasattr(a, "data_ptr"):
+        if hasattr(a, "is_cuda") and not a.is_cuda:
+            raise TypeError("struct-for arguments are device pointers or scalars (got a CPU tensor)")
+        return int(a.data_ptr())
+    if isinstance(a, (bool, int, np.integer)) and not isinstance(a, (np.int32, np.uint32)):
+        return int(np.array(a, np.int64).view(np.uint64))
+    if isinstance(a, (np.int32, np.uint32)):
+        return int(np.array([a, 0], np.int32).view(np.uint64)[0])
+    if isinstance(a, np.float64):
+        return int(np.array(a, np.float64).view(np.uint64))
+    if isinstance(a, (float, np.floating)):
+        return int(np.array([a, 0], np.float32).view(np.uint64)[0])
+    raise TypeError(f"unsupported struct-for argument {type(a)}")
+
+
+class StructFor:
+    """`for I in ti.grouped(snode): <body>` with the body given as CUDA C++ (contract: csrc/b2_jit.cuh).
+
+        scale = ti.struct_for('''B2_BODY(c) {
+            float v = c.read<float>(0, c.I);            // x[I]
+            c.write<float>(1, c.I, c.arg<float>(0) * v); // y[I] = a * x[I]   (activates y's cell)
+        }''')
+        scale(block, fields=[x, y], args=[2.0])
+
+    Compiled once (NVRTC, sm_100a) at construction; a body that does not compile raises with the compiler log."""
+
+    def __init__(self, source, name="b2_body"):
+        if _prog.rt is None:
+            raise RuntimeError("ti.init() first")
+        self.name = name
+        self.handle = lib.b2_jit_compile(_prog.rt, source.encode(), name.encode())
+        L.check()
+        self._rt = _prog.rt
+
+    def __call__(self, snode, fields=(), args=()):
+        if self.handle is None or self._rt != _prog.rt:
+            raise RuntimeError("struct-for kernel belongs to a runtime that was reset")
+        t = _materialize()
+        places = (C.c_int32 * max(1, len(fields)))(*[f.place_id for f in fields])
+        slots = (C.c_uint64 * max(1, len(args)))(*[_arg_bits(a) for a in args])
+        lib.b2_jit_launch(self.handle, t, snode.id, places, len(fields), slots, len(args))
+        L.check()
+
+    def log(self):
+        n = lib.b2_jit_log(self.handle, None, 0)
+        buf = C.create_string_buffer(int(n))
+        lib.b2_jit_log(self.handle, buf, n)
+        return buf.value.decode()
+
+    def destroy(self):
+        if self.handle is not None and self._rt == _prog.rt:
+            lib.b2_jit_destroy(self.handle)
+        self.handle = None
+
+
+def struct_for(source, name="b2_body"):
+    return StructFor(source, name)

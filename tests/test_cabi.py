@@ -81,3 +81,19 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 txt = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "liboracle" not in txt and "oracle/" not in txt.replace("oracle/_ref", "oracle/").replace("# oracle/", "") or f == "nope", f
+
+
+def test_jit_body_compiles_without_a_device():
+    """b2_jit_check: NVRTC turns a B2_BODY source (+ the embedded b2_internal.cuh / b2_jit.cuh) into an sm_100a
+    cubin on the host alone; a broken body reports the compiler log through the last-error channel."""
+    from taichi_b200 import _lib as L
+    ok = L.lib.b2_jit_check(b"B2_BODY(c) { c.write<float>(0, c.I, 2.0f * c.read<float>(0, c.I) + c.arg<float>(0)); }", b"k")
+    if ok < 0 and L.last_error()[0] == -1:
+        import pytest
+        L.lib.ti_set_last_error(0, None)
+        pytest.skip("libnvrtc not installed on this host")
+    assert ok > 1000, L.last_error()
+    assert L.lib.b2_jit_check(b"B2_BODY(c) { nonsense(); }", b"bad_body") == -1
+    code, msg = L.last_error()
+    L.lib.ti_set_last_error(0, None)
+    assert code == -4 and "nonsense" in msg and "bad_body" in msg

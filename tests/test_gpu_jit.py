@@ -1,0 +1,136 @@
+"""Struct-for with run-time compiled bodies: the reference's sparse kernels written as
+B2_BODY sources and run through b2_jit_compile / b2_jit_launch (tests/python/test_bitmasked.py:5-31,
+test_sparse_basics.py pointer/activation idioms, test_struct_for_non_pot.py, docs/lang/articles/basic/sparse.md:
+writes activate, reads do not, struct-for visits active cells only)."""
+import numpy as np
+import pytest
+
+from _b2 import have_gpu
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def ti():
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    import taichi_b200 as ti
+    ti.init(arch=ti.cuda, device_memory_GB=0.5)
+    yield ti
+    ti.reset()
+
+
+def test_sum_over_bitmasked(ti):  # test_bitmasked.py:5-31: for i, j in x: s[None] += x[i, j]
+    import torch
+    x = ti.field(ti.i32)
+    bm = ti.root.bitmasked(ti.ij, (3, 6)).bitmasked(ti.i, 8)
+    bm.place(x)
+    x[5, 1] = 2
+    x[9, 4] = 20
+    x[0, 3] = 20
+    k = ti.struct_for("""B2_BODY(c) {
+        atomicAdd(c.arg<int *>(0), c.read<int>(0, c.I));
+        atomicAdd(c.arg<int *>(0) + 1, 1);
+    }""", "sum_x")
+    s = torch.zeros(2, dtype=torch.int32, device="cuda")
+    k(bm, fields=[x], args=[s])
+    assert s.tolist() == [42, 3]
+    k(bm, fields=[x], args=[s])          # a second launch re-generates the list and accumulates
+    assert s.tolist() == [84, 6]
+
+
+def test_write_activates_read_does_not(ti):  # sparse.md: y[i + 1] = 2 x[i] activates; reading x[i - 1] does not
+    import torch
+    x, y = ti.field(ti.f32), ti.field(ti.f32)
+    bx = ti.root.pointer(ti.i, 32).dense(ti.i, 8)
+    by = ti.root.pointer(ti.i, 32).dense(ti.i, 8)
+    bx.place(x)
+    by.place(y)
+    src = [3, 7, 8, 100, 255 - 1]
+    for q in src:
+        x[q] = float(q + 1)
+    k = ti.struct_for("""B2_BODY(c) {
+        int J[B2_MAX_AXES], K[B2_MAX_AXES];
+        c.offset(J, 0, +1);
+        c.offset(K, 0, -1);
+        const float v = c.read<float>(0, c.I);
+        const float left = c.I[0] > 0 ? c.read<float>(0, K) : 0.0f;   // inactive neighbours read as 0
+        if (v != 0.0f) c.write<float>(1, J, c.arg<float>(0) * v + left);
+    }""", "shift")
+    before = ti.active_indices(bx.parent()).copy()
+    k(bx, fields=[x, y], args=[2.0])
+    img_x, img_y = x.to_numpy(), y.to_numpy()
+    want = np.zeros(256, np.float32)
+    for q in src:
+        want[q + 1] = 2.0 * (q + 1) + img_x[q - 1]
+    assert np.array_equal(img_y, want)
+    assert np.array_equal(ti.active_indices(bx.parent()), before)     # reads did not activate x's blocks
+    got_blocks = sorted(int(b) for b in ti.active_indices(by.parent())[:, 0])
+    assert got_blocks == sorted({(q + 1) // 8 for q in src})          # writes activated exactly the touched blocks
+
+
+def test_loop_over_pointer_level_and_non_pot(ti):  # struct-for over a non-leaf SNode; non power-of-two shapes
+    import torch
+    x = ti.field(ti.i32)
+    ptr = ti.root.pointer(ti.ij, (3, 5))
+    blk = ptr.dense(ti.ij, (3, 2))
+    blk.place(x)
+    for (a, b) in [(0, 0), (4, 7), (8, 9), (7, 1)]:
+        x[a, b] = 1
+    k = ti.struct_for("""B2_BODY(c) {
+        const unsigned long long n = atomicAdd(c.arg<unsigned long long *>(0), 1ull);
+        int *out = c.arg<int *>(1);
+        out[2 * n] = c.I[0], out[2 * n + 1] = c.I[1];
+    }""", "dump")
+    cnt = torch.zeros(1, dtype=torch.int64, device="cuda")
+    out = torch.full((64, 2), -1, dtype=torch.int32, device="cuda")
+    k(ptr, args=[cnt, out])
+    n = int(cnt.item())
+    cells = sorted(map(tuple, out[:n].tolist()))
+    assert cells == sorted({(a // 3, b // 2) for (a, b) in [(0, 0), (4, 7), (8, 9), (7, 1)]})
+    cnt.zero_()
+    k(blk, args=[cnt, out])                                            # leaf level: every cell of the active blocks
+    n = int(cnt.item())
+    assert n == 4 * 6
+    got = sorted(map(tuple, out[:n].tolist()))
+    assert got == sorted(map(tuple, ti.active_indices(blk).tolist()))
+
+
+def test_sparse_laplacian_3d(ti):  # pointer -> bitmasked -> dense(4^3): 7-point stencil into a second sparse field
+    x, y = ti.field(ti.f32), ti.field(ti.f32)
+    bx = ti.root.pointer(ti.ijk, 4).bitmasked(ti.ijk, 4).dense(ti.ijk, 4)
+    by = ti.root.pointer(ti.ijk, 4).bitmasked(ti.ijk, 4).dense(ti.ijk, 4)
+    bx.place(x)
+    by.place(y)
+    rng = np.random.default_rng(0)
+    pts = rng.integers(8, 40, size=(300, 3))
+    vals = rng.random(300).astype(np.float32)
+    x[pts] = vals
+    k = ti.struct_for("""B2_BODY(c) {
+        float acc = -6.0f * c.read<float>(0, c.I);
+        for (int a = 0; a < 3; a++) {
+            int J[B2_MAX_AXES];
+            c.offset(J, a, +1); acc += c.read<float>(0, J);
+            c.offset(J, a, -1); acc += c.read<float>(0, J);
+        }
+        c.write<float>(1, c.I, acc);
+    }""", "laplace")
+    k(bx, fields=[x, y])
+    X = x.to_numpy().astype(np.float32)
+    act = np.zeros_like(X, bool)
+    idx = ti.active_indices(bx)
+    act[idx[:, 0], idx[:, 1], idx[:, 2]] = True
+    P = np.pad(X, 1)
+    lap = (-6.0 * X + P[2:, 1:-1, 1:-1] + P[:-2, 1:-1, 1:-1] + P[1:-1, 2:, 1:-1] + P[1:-1, :-2, 1:-1]
+           + P[1:-1, 1:-1, 2:] + P[1:-1, 1:-1, :-2]).astype(np.float32)
+    Y = y.to_numpy()
+    assert np.allclose(Y[act], lap[act], rtol=1e-6, atol=1e-6)
+    assert np.array_equal(ti.active_indices(by), idx)                 # y is active exactly where the loop ran
+    assert np.all(Y[~act] == 0)
+
+
+def test_compile_error_surfaces_log(ti):
+    from taichi_b200._lib import B2RuntimeError
+    with pytest.raises(B2RuntimeError) as e:
+        ti.struct_for("B2_BODY(c) { undeclared_symbol = 1; }", "broken")
+    assert "undeclared_symbol" in str(e.value) and "broken" in str(e.value)
