@@ -200,15 +200,18 @@ __device__ __forceinline__ void p2g_count(const MpmDev &M, int gen, u32 nslots, 
   if (U.slot >= nslots) return;
   const int n = p2g_unit_entries(U.total, U.q0);
   const u32 off0 = U.q0 % MPM_CHUNK, cid0 = U.cid[0], cid1 = U.cid[1], cid2 = U.cid[2];
+  // entries in REVERSED thread order: the stage phase gives the ragged third round (entries >= 448) to the first
+  // warps, so the count that follows it without a barrier gives its third round to the last ones
+  const int rt = P2G_NW - 1 - tid;
   float4 p0[3];
 #pragma unroll
   for (int e = 0; e < 3; e++) {
-    const int t = tid + e * P2G_NW;
+    const int t = rt + e * P2G_NW;
     if (t < n) p0[e] = *(const float4 *)p2g_entry_ptr(M, gen, off0, cid0, cid1, cid2, t);
   }
 #pragma unroll
   for (int e = 0; e < 3; e++) {
-    const int t = tid + e * P2G_NW;
+    const int t = rt + e * P2G_NW;
     if (t < n) {
       unsigned short ck = 0xffffu;
       if (p0[e].x != MPM_TOMB) {
