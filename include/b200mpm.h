@@ -364,6 +364,11 @@ TI_DLL_EXPORT int32_t b2_mpm_get_particles(B2Mpm mpm, float *x_any, float *v_any
 TI_DLL_EXPORT int32_t b2_mpm_get_particles_async(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *J_any);
 /* Blocks until every upload and download issued through this solver has finished. */
 TI_DLL_EXPORT int32_t b2_mpm_wait_io(B2Mpm mpm);
+/* 0-D reductions over the particles (make_thread_local.cpp:100-213 + runtime.cpp:1204-1266 in the reference):
+ * out[0] live particles, [1..3] momentum, [4] kinetic energy, [5] sum J, [6] max |v|, [7] max |J - 1|.
+ * _device: enqueue only, 8 doubles of device memory. */
+TI_DLL_EXPORT int32_t b2_mpm_diagnostics(B2Mpm mpm, double *out8_host);
+TI_DLL_EXPORT int32_t b2_mpm_diagnostics_device(B2Mpm mpm, double *out8_dev);
 TI_DLL_EXPORT int32_t b2_mpm_substep(B2Mpm mpm, int32_t nsteps);
 /* individual phases (mpm88_graph_aot.py kernel split) */
 TI_DLL_EXPORT int32_t b2_mpm_clear_grid(B2Mpm mpm);
@@ -410,6 +415,9 @@ TI_DLL_EXPORT B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_
 TI_DLL_EXPORT void b2_slab_destroy(B2Slab slab);
 TI_DLL_EXPORT int32_t b2_slab_substep(B2Slab slab, int32_t nsteps);
 TI_DLL_EXPORT int32_t b2_slab_tune(B2Slab slab); /* message sizes := 2x last counts (synchronises) */
+/* Whole-domain particle diagnostics: out[0] live particles, [1..3] momentum, [4] kinetic energy, [5] sum J,
+ * [6] max |v| (CFL), [7] max |J - 1|; local reduction + ncclAllReduce (SUM / MAX) over the slabs. Synchronises. */
+TI_DLL_EXPORT int32_t b2_slab_diagnostics(B2Slab slab, double *out8_host);
 
 /* ---- struct-for with a run-time compiled body -------------------------------------------
  * Stands in for the reference's per-kernel codegen + CUDA JIT of a struct-for task (codegen_llvm.cpp:2089-2317,

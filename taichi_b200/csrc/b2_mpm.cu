@@ -296,6 +296,45 @@ __global__ void __launch_bounds__(256) k_mpm_stats(MpmDev M, int gen) {
   }
 }
 
+// Particle diagnostics (the 0-D reductions an MPM driver asks for every few steps: the reference lowers
+// `s[None] += ...` / ti.atomic_max to a thread-local accumulator + warp reduce + one atomic per warp,
+// make_thread_local.cpp:100-213, runtime.cpp:1204-1266).  out[0] live particles, [1..3] momentum p_mass sum v,
+// [4] kinetic energy, [5] sum J, [6] max |v| (CFL), [7] max |J - 1|.  Sums in fp64; the two maxima are
+// non-negative, so their IEEE bit patterns order like integers (atomicMax on the bits).
+__global__ void __launch_bounds__(256) k_mpm_diag(MpmDev M, int gen, double *out) {
+  const u32 ns = *M.nslots;
+  double acc[6] = {0, 0, 0, 0, 0, 0};
+  float vmax = 0.f, jmax = 0.f;
+  for (u32 s = blockIdx.x; s < ns; s += gridDim.x) {
+    const u32 c = M.count[gen][s];
+    for (u32 q = threadIdx.x; q < c; q += blockDim.x) {
+      const u8 *ch = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)s * M.maxc + q / MPM_CHUNK]);
+      const float4 p0 = ((const float4 *)ch)[q % MPM_CHUNK];
+      if (p0.x == MPM_TOMB) continue;
+      const float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[q % MPM_CHUNK];
+      const double v2 = (double)p1.x * p1.x + (double)p1.y * p1.y + (double)p1.z * p1.z;
+      acc[0] += 1.0, acc[1] += p1.x, acc[2] += p1.y, acc[3] += p1.z, acc[4] += v2, acc[5] += p0.w;
+      vmax = fmaxf(vmax, sqrtf((float)v2));
+      jmax = fmaxf(jmax, fabsf(p0.w - 1.0f));
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 6; k++)
+    for (int d = 16; d > 0; d >>= 1) acc[k] += __shfl_down_sync(0xffffffffu, acc[k], d);
+  for (int d = 16; d > 0; d >>= 1) {
+    vmax = fmaxf(vmax, __shfl_down_sync(0xffffffffu, vmax, d));
+    jmax = fmaxf(jmax, __shfl_down_sync(0xffffffffu, jmax, d));
+  }
+  if ((threadIdx.x & 31) == 0 && acc[0] > 0.0) {
+    atomicAdd(&out[0], acc[0]);
+    atomicAdd(&out[1], acc[1] * (double)M.p_mass), atomicAdd(&out[2], acc[2] * (double)M.p_mass), atomicAdd(&out[3], acc[3] * (double)M.p_mass);
+    atomicAdd(&out[4], 0.5 * (double)M.p_mass * acc[4]);
+    atomicAdd(&out[5], acc[5]);
+    atomicMax((unsigned long long *)&out[6], (unsigned long long)__double_as_longlong((double)vmax));
+    atomicMax((unsigned long long *)&out[7], (unsigned long long)__double_as_longlong((double)jmax));
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // grid kernels: struct-for over the leaf Element list (one Element = one 4^3 block = 1 KiB)
 // ------------------------------------------------------------------------------------------
@@ -1072,6 +1111,27 @@ int32_t b2_mpm_stats(B2Mpm m, double *out) {
   m->rt->sync();
   m->ensure_lists();
   out[4] = (double)m->tree->list_count(m->M.leaf_sid);
+  return 0;
+  B2_API_END(-1)
+}
+// Enqueues the reduction into 8 doubles of device memory (zeroed first); the slab driver all-reduces them.
+int32_t b2_mpm_diagnostics_device(B2Mpm m, double *out8_dev) {
+  B2_API_BEGIN
+  require(m != nullptr && out8_dev != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm/out");
+  cudaStream_t st = m->rt->stream();
+  B2_CUDA(cudaMemsetAsync(out8_dev, 0, 64, st));
+  k_mpm_diag<<<m->rt->num_sms * 4, 256, 0, st>>>(m->M, m->gen, out8_dev);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_diagnostics(B2Mpm m, double *out8) {
+  B2_API_BEGIN
+  require(m != nullptr && out8 != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm/out");
+  if (b2_mpm_diagnostics_device(m, m->M.stats) != 0) return -1;
+  B2_CUDA(cudaMemcpyAsync(out8, m->M.stats, 64, cudaMemcpyDeviceToHost, m->rt->stream()));
+  m->rt->sync();
   return 0;
   B2_API_END(-1)
 }

@@ -16,7 +16,7 @@ typedef struct ncclComm *ncclComm_t;
 typedef struct {
   char internal[128];
 } ncclUniqueId;
-enum { NCCL_UINT8 = 1 };
+enum { NCCL_UINT8 = 1, NCCL_UINT64 = 5, NCCL_FLOAT64 = 8, NCCL_SUM = 0, NCCL_MAX = 2 };
 
 struct NcclApi {
   int (*GetUniqueId)(ncclUniqueId *);
@@ -24,6 +24,7 @@ struct NcclApi {
   int (*CommDestroy)(ncclComm_t);
   int (*Send)(const void *, size_t, int, int, ncclComm_t, cudaStream_t);
   int (*Recv)(void *, size_t, int, int, ncclComm_t, cudaStream_t);
+  int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t);
   int (*GroupStart)();
   int (*GroupEnd)();
   const char *(*GetErrorString)(int);
@@ -44,6 +45,7 @@ static NcclApi &nccl() {
   B2_SYM(CommDestroy, "ncclCommDestroy");
   B2_SYM(Send, "ncclSend");
   B2_SYM(Recv, "ncclRecv");
+  B2_SYM(AllReduce, "ncclAllReduce");
   B2_SYM(GroupStart, "ncclGroupStart");
   B2_SYM(GroupEnd, "ncclGroupEnd");
   B2_SYM(GetErrorString, "ncclGetErrorString");
@@ -74,6 +76,7 @@ struct B2Slab_t {
   int64_t sendA_bytes, recvA_bytes, sendB_bytes, recvB_bytes, sendL_bytes, recvL_bytes, sendR_bytes, recvR_bytes;
   uint8_t *sendA, *recvA, *sendB, *recvB, *sendL, *sendR, *recvL, *recvR;
   uint32_t *sizes_dev;  // tune: 4 counts out, 4 counts in
+  double *diag_dev;     // diagnostics: 8 doubles, reduced over the slabs in place
   std::vector<void *> allocs;
   uint8_t *buf(int64_t bytes) {
     void *p = nullptr;
@@ -152,6 +155,7 @@ B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_t world, int32
   s->sendA = s->buf(bb), s->recvA = s->buf(bb), s->sendB = s->buf(bb), s->recvB = s->buf(bb);
   s->sendL = s->buf(pb), s->sendR = s->buf(pb), s->recvL = s->buf(pb), s->recvR = s->buf(pb);
   s->sizes_dev = (uint32_t *)s->buf(64);
+  s->diag_dev = (double *)s->buf(64);
   s->sendA_bytes = s->recvA_bytes = s->sendB_bytes = s->recvB_bytes = bb;
   s->sendL_bytes = s->recvL_bytes = s->sendR_bytes = s->recvR_bytes = pb;
   return s;
@@ -210,6 +214,26 @@ int32_t b2_slab_substep(B2Slab s, int32_t nsteps) {
 // Shrinks the bytes put on the wire to 2x the record counts of the last substep (+256 records,
 // never above the capacity); neighbours learn each other's sizes through one tiny exchange.
 // Synchronises.  An overflow after tuning raises the device-side error flag (bin overflow).
+// Whole-domain particle diagnostics: every slab reduces its own particles (k_mpm_diag), then
+// ncclAllReduce over the slabs -- sums for out[0..5], maxima (as ordered bit patterns) for out[6..7] -- on the
+// same stream, one group.  Every rank gets the result.  Synchronises.
+int32_t b2_slab_diagnostics(B2Slab s, double *out8) {
+  B2_API_BEGIN
+  require(s != nullptr && out8 != nullptr, TI_ERROR_ARGUMENT_NULL, "slab/out");
+  cudaStream_t st = s->rt->stream();
+  ok0(b2_mpm_diagnostics_device(s->mpm, s->diag_dev));
+  if (s->world > 1) {
+    NcclApi &n = nccl();
+    B2_NCCL(n.GroupStart());
+    B2_NCCL(n.AllReduce(s->diag_dev, s->diag_dev, 6, NCCL_FLOAT64, NCCL_SUM, s->comm->comm, st));
+    B2_NCCL(n.AllReduce(s->diag_dev + 6, s->diag_dev + 6, 2, NCCL_UINT64, NCCL_MAX, s->comm->comm, st));
+    B2_NCCL(n.GroupEnd());
+  }
+  B2_CUDA(cudaMemcpyAsync(out8, s->diag_dev, 64, cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  return 0;
+  B2_API_END(-1)
+}
 int32_t b2_slab_tune(B2Slab s) {
   B2_API_BEGIN
   require(s != nullptr, TI_ERROR_ARGUMENT_NULL, "slab");

@@ -237,6 +237,14 @@ class Mpm3D:
         return dict(particles=int(out[0]), slots=int(out[1]), occupied_slots=int(out[2]), chunks=int(out[3]),
                     active_blocks=int(out[4]))
 
+    DIAG_KEYS = ("particles", "px", "py", "pz", "kinetic_energy", "sum_J", "max_speed", "max_dJ")
+
+    def diagnostics(self):
+        """0-D reductions over the particles (momentum, kinetic energy, max |v| for the CFL check, ...)."""
+        out = (C.c_double * 8)()
+        self._ok(lib.b2_mpm_diagnostics(self.handle, out))
+        return dict(zip(self.DIAG_KEYS, list(out)))
+
     def set_profiling(self, on):
         lib.b2_mpm_set_profiling(self.handle, int(on))
 

@@ -74,6 +74,12 @@ class CudaSlab:
     def wait_io(self):
         self._ok(self.lib.b2_mpm_wait_io(self.handle))
 
+    def diagnostics(self):
+        """Local (this slab's particles) 8-vector: count, momentum xyz, kinetic energy, sum J, max |v|, max |J-1|."""
+        out = (C.c_double * 8)()
+        self._ok(self.lib.b2_mpm_diagnostics(self.handle, out))
+        return np.array(list(out), np.float64)
+
     def export(self, cap):
         from .mpm import _ptr
         x, v = np.empty((cap, 3), np.float32), np.empty((cap, 3), np.float32)
@@ -142,6 +148,15 @@ class NativeSlabDriver:
         rc = self.lib.b2_slab_substep(self.handle, n)
         self.L.check()
         assert rc == 0
+
+    def diagnostics(self):
+        """Whole-domain diagnostics: local reduction + ncclAllReduce (SUM / MAX) enqueued from C++; every rank
+        gets the same 8-vector (count, momentum xyz, kinetic energy, sum J, max |v|, max |J-1|)."""
+        out = (C.c_double * 8)()
+        rc = self.lib.b2_slab_diagnostics(self.handle, out)
+        self.L.check()
+        assert rc == 0
+        return np.array(list(out), np.float64)
 
     def tune(self):
         rc = self.lib.b2_slab_tune(self.handle)
@@ -228,6 +243,20 @@ def substep_distributed(driver, nsteps=1, group=None):
     for _ in range(nsteps):
         for ph in SlabDriver.PHASES:
             exchange_distributed(getattr(driver, ph)(), group)
+
+
+def diagnostics_distributed(backend, group=None):
+    """Whole-domain diagnostics through a torch.distributed communicator (gloo on CPU, nccl on GPUs): the slab's
+    local 8-vector, then all_reduce SUM of [0..5] and MAX of [6..7]."""
+    import torch
+    import torch.distributed as dist
+    d = torch.from_numpy(np.asarray(backend.diagnostics(), np.float64).copy())
+    if dist.get_backend(group) == "nccl":
+        d = d.cuda()
+    sums, maxs = d[:6].clone(), d[6:].clone()
+    dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    dist.all_reduce(maxs, op=dist.ReduceOp.MAX, group=group)
+    return torch.cat([sums, maxs]).cpu().numpy()
 
 
 def substep_local(drivers, nsteps=1):

@@ -35,6 +35,13 @@ class NumpySlab:
     def export(self, cap):
         return self.x, self.v, self.C, self.J, self.ids
 
+    def diagnostics(self):
+        v = self.v.astype(np.float64)
+        v2 = (v * v).sum(1)
+        m = float(self.p_mass)
+        return np.array([len(self.x), *(m * v.sum(0)), 0.5 * m * v2.sum(), self.J.astype(np.float64).sum(),
+                         np.sqrt(v2).max() if len(v) else 0.0, np.abs(self.J - 1).max() if len(v) else 0.0], np.float64)
+
     def _stencil(self):
         X = self.x / self.dx
         base = (X - np.float32(0.5)).astype(np.int32)

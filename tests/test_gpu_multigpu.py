@@ -125,6 +125,32 @@ def test_export_async_equals_blocking_export():
     s.destroy()
 
 
+def test_diagnostics_vs_numpy():
+    """k_mpm_diag (fp64 sums from thread-local accumulators + warp shuffles, maxima as ordered bit patterns)
+    against NumPy on the exported particles; world = 1 slab driver returns the same vector."""
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    from taichi_b200 import multigpu as mg
+    rt = get_rt()
+    x, v, Cm, J, ids = cloud()
+    s = mg.CudaSlab(rt, N_GRID, N, DT, 0, N_GRID // 4)
+    s.set_particles(x, v, Cm, J, ids)
+    d = mg.NativeSlabDriver(s, 0, 1)
+    d.substep(5)
+    xe, ve, Ce, Je, ie = s.export(N)
+    m = (1.0 / N_GRID * 0.5) ** 2
+    v64 = ve.astype(np.float64)
+    want = np.array([len(ie), *(np.float32(m) * v64.sum(0)), 0.5 * np.float32(m) * (v64 * v64).sum(), Je.astype(np.float64).sum(),
+                     np.sqrt((v64 * v64).sum(1)).max(), np.abs(Je - np.float32(1)).max()])
+    got = s.diagnostics()
+    assert got[0] == N
+    assert np.allclose(got[:6], want[:6], rtol=1e-9, atol=1e-12)
+    assert np.allclose(got[6:], want[6:], rtol=1e-6)
+    assert np.array_equal(d.diagnostics(), got)
+    d.destroy()
+    s.destroy()
+
+
 def _nccl_worker(rank, world, port, out, native):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
@@ -152,8 +178,10 @@ def _nccl_worker(rank, world, port, out, native):
     torch.cuda.synchronize()
     buf = C.create_string_buffer(256)
     assert tb._lib.lib.b2_check_runtime_error(rt.handle, buf, 256) == 0, buf.value
+    # whole-domain diagnostics: ncclAllReduce from C++ (native) / torch.distributed all_reduce (python driver)
+    diag = d.diagnostics() if native else mg.diagnostics_distributed(s)
     gathered = [None] * world
-    dist.all_gather_object(gathered, s.export(N))
+    dist.all_gather_object(gathered, tuple(s.export(N)) + (diag, s.diagnostics()))
     if rank == 0:
         torch.save(gathered, out)
     dist.barrier()
@@ -170,4 +198,11 @@ def test_nccl_two_gpus(tmp_path, native):
     mp.spawn(_nccl_worker, args=(2, 29700 + os.getpid() % 1000 + int(native), out, native), nprocs=2, join=True)
     x, v, Cm, J, ids = cloud()
     xs, vs, Cs, Js, *_ = oracle_mpm3d(N_GRID, x, v, Cm, J, DT, STEPS)
-    compare(torch.load(out, weights_only=False), (xs, vs, Cs, Js))
+    parts = torch.load(out, weights_only=False)
+    compare([p[:5] for p in parts], (xs, vs, Cs, Js))
+    # every rank got the same reduced vector = SUM / MAX of the slabs' local vectors
+    assert np.array_equal(parts[0][5], parts[1][5])
+    local = np.stack([p[6] for p in parts])
+    assert np.allclose(parts[0][5][:6], local[:, :6].sum(0), rtol=1e-14, atol=0)
+    assert np.array_equal(parts[0][5][6:], local[:, 6:].max(0))
+    assert parts[0][5][0] == N

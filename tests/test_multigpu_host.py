@@ -86,8 +86,9 @@ def _gloo_worker(rank, world, port, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     s, d = make_rank(rank, world)
     mg.substep_distributed(d, STEPS)
+    diag = mg.diagnostics_distributed(s)        # SUM / MAX all-reduce of the slabs' 0-D reductions
     gathered = [None] * world
-    dist.all_gather_object(gathered, (s.x, s.v, s.J, s.ids))
+    dist.all_gather_object(gathered, (s.x, s.v, s.J, s.ids, diag))
     if rank == 0:
         torch.save(gathered, out)
     dist.barrier()
@@ -98,4 +99,13 @@ def test_gloo_world2_matches_single_domain(tmp_path):
     out = str(tmp_path / "g.pt")
     port = 29500 + os.getpid() % 2000
     mp.spawn(_gloo_worker, args=(2, port, out), nprocs=2, join=True)
-    check_against_single(torch.load(out, weights_only=False))
+    parts = torch.load(out, weights_only=False)
+    check_against_single([p[:4] for p in parts])
+    # whole-domain diagnostics: every rank holds the same vector, equal to the reduction over all particles
+    assert np.array_equal(parts[0][4], parts[1][4])
+    v = np.concatenate([p[1] for p in parts]).astype(np.float64)
+    J = np.concatenate([p[2] for p in parts])
+    m = float(NumpySlab(N_GRID, DT, 0, 1).p_mass)
+    want = np.array([N, *(m * v.sum(0)), 0.5 * m * (v * v).sum(), J.astype(np.float64).sum(),
+                     np.sqrt((v * v).sum(1)).max(), np.abs(J - 1).max()])
+    assert np.allclose(parts[0][4], want, rtol=1e-12, atol=1e-15)
