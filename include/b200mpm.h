@@ -437,6 +437,11 @@ TI_DLL_EXPORT int64_t b2_jit_log(B2JitKernel kernel, char *out, int64_t cap); /*
  * SNode ids (field f of the body); args: <= 16 64-bit slots (scalars bit-cast, DEVICE pointers). Asynchronous. */
 TI_DLL_EXPORT int32_t b2_jit_launch(B2JitKernel kernel, B2Tree tree, int32_t loop_snode, const int32_t *field_places,
                                     int32_t n_fields, const uint64_t *args, int32_t n_args);
+/* Range-for (`for i in range(begin, end)`, gpu_parallel_range_for runtime.cpp:1541-1565) over a source holding
+ *     B2_RANGE_BODY(c) { ... }                 // c.i = loop index; same field access and arguments
+ * e.g. a particle loop scattering into a sparse grid with c.ref<float>(f, J) + atomicAdd (activates). */
+TI_DLL_EXPORT int32_t b2_jit_launch_range(B2JitKernel kernel, B2Tree tree, int64_t begin, int64_t end, const int32_t *field_places,
+                                          int32_t n_fields, const uint64_t *args, int32_t n_args);
 
 #ifdef __cplusplus
 }

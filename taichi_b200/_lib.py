@@ -175,6 +175,7 @@ SIGNATURES = {
     "b2_jit_destroy": (None, [C.c_void_p]),
     "b2_jit_log": (C.c_int64, [C.c_void_p, C.c_char_p, C.c_int64]),
     "b2_jit_launch": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_uint64), C.c_int32]),
+    "b2_jit_launch_range": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_uint64), C.c_int32]),
     "b2_mpm_set_profiling": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b2_mpm_phase_ms": (C.c_int32, [C.c_void_p, f32p]),
     "b2_mpm_pack_blocks": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]),

@@ -58,7 +58,8 @@ Nvrtc &nvrtc() {
 struct B2JitKernel_t {
   TiRuntime_t *rt = nullptr;
   cudaLibrary_t lib = nullptr;
-  cudaKernel_t fn = nullptr;
+  cudaKernel_t fn = nullptr;        // b2_jit_struct_for (B2_BODY), if the source has one
+  cudaKernel_t fn_range = nullptr;  // b2_jit_range_for (B2_RANGE_BODY), if the source has one
   B2JitTable *tab_dev = nullptr;  // launch table (fields + args), rewritten in stream order before every launch
   std::string log;
   size_t cubin_bytes = 0;
@@ -73,7 +74,10 @@ static void jit_build(const char *source, const char *name, std::vector<char> *c
   jit_require(source != nullptr, TI_ERROR_ARGUMENT_NULL, "source");
   Nvrtc &N = nvrtc();
   jit_require(N.h != nullptr, TI_ERROR_NOT_SUPPORTED, "libnvrtc.so.12 not found (set B2_NVRTC_LIB): struct-for bodies cannot be compiled");
-  std::string src = "#include \"b2_internal.cuh\"\n#include \"b2_jit.cuh\"\n#line 1 \"";
+  std::string src;
+  if (strstr(source, "B2_RANGE_BODY")) src += "#define B2_JIT_HAS_RANGE 1\n";
+  if (strstr(source, "B2_BODY")) src += "#define B2_JIT_HAS_BODY 1\n";  // ("B2_RANGE_BODY" does not contain it)
+  src += "#include \"b2_internal.cuh\"\n#include \"b2_jit.cuh\"\n#line 1 \"";
   src += (name && *name) ? name : "b2_body";
   src += "\"\n";
   src += source;
@@ -127,7 +131,10 @@ B2JitKernel b2_jit_compile(TiRuntime rt, const char *source, const char *name) {
   k->log = log;
   k->cubin_bytes = nb;
   B2_CUDA(cudaLibraryLoadData(&k->lib, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0));
-  B2_CUDA(cudaLibraryGetKernel(&k->fn, k->lib, "b2_jit_struct_for"));
+  if (cudaLibraryGetKernel(&k->fn, k->lib, "b2_jit_struct_for") != cudaSuccess) k->fn = nullptr;
+  if (cudaLibraryGetKernel(&k->fn_range, k->lib, "b2_jit_range_for") != cudaSuccess) k->fn_range = nullptr;
+  cudaGetLastError();
+  jit_require(k->fn != nullptr || k->fn_range != nullptr, TI_ERROR_INVALID_ARGUMENT, "source defines neither B2_BODY(c) nor B2_RANGE_BODY(c)");
   B2_CUDA(cudaMalloc((void **)&k->tab_dev, sizeof(B2JitTable)));
   return k.release();
   B2_API_END(nullptr)
@@ -152,16 +159,14 @@ int64_t b2_jit_log(B2JitKernel k, char *out, int64_t cap) {
   return (int64_t)k->log.size() + 1;
 }
 
-int32_t b2_jit_launch(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t *field_places, int32_t n_fields, const uint64_t *args, int32_t n_args) {
-  B2_API_BEGIN
+// fields + args -> the kernel's launch table, uploaded in stream order
+static void jit_upload_table(B2JitKernel k, B2Tree t, const int32_t *field_places, int32_t n_fields, const uint64_t *args, int32_t n_args) {
   jit_require(k != nullptr && t != nullptr, TI_ERROR_ARGUMENT_NULL, "kernel/tree");
   jit_require(k->rt == t->rt, TI_ERROR_INVALID_ARGUMENT, "kernel and tree belong to different runtimes");
   jit_require(n_fields >= 0 && n_fields <= B2_JIT_MAX_FIELDS, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "at most 8 fields per body");
   jit_require(n_args >= 0 && n_args <= B2_JIT_MAX_ARGS, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "at most 16 arguments per body");
   jit_require(n_fields == 0 || field_places != nullptr, TI_ERROR_ARGUMENT_NULL, "field_places");
   jit_require(n_args == 0 || args != nullptr, TI_ERROR_ARGUMENT_NULL, "args");
-  t->check_snode(loop_snode, "jit_launch");
-  jit_require(t->s[loop_snode].type != B2T_PLACE && loop_snode != 0, TI_ERROR_INVALID_ARGUMENT, "loop SNode must be a non-root container SNode");
   static thread_local B2JitTable tab;  // 10 KB: not on the stack
   memset(&tab, 0, sizeof(tab));
   tab.n_fields = n_fields, tab.n_args = n_args;
@@ -177,9 +182,17 @@ int32_t b2_jit_launch(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t
     tab.f[i].bytes = p.dtype_bytes;
     tab.f[i].holder = p.parent;
   }
-  cudaStream_t st = t->rt->stream();
   B2_CUDA(cudaSetDevice(t->rt->device));
-  B2_CUDA(cudaMemcpyAsync(k->tab_dev, &tab, sizeof(tab), cudaMemcpyHostToDevice, st));  // pageable source: staged before return
+  B2_CUDA(cudaMemcpyAsync(k->tab_dev, &tab, sizeof(tab), cudaMemcpyHostToDevice, t->rt->stream()));  // pageable source: staged before return
+}
+
+int32_t b2_jit_launch(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t *field_places, int32_t n_fields, const uint64_t *args, int32_t n_args) {
+  B2_API_BEGIN
+  jit_upload_table(k, t, field_places, n_fields, args, n_args);
+  jit_require(k->fn != nullptr, TI_ERROR_INVALID_ARGUMENT, "this kernel has no B2_BODY (struct-for) entry");
+  t->check_snode(loop_snode, "jit_launch");
+  jit_require(t->s[loop_snode].type != B2T_PLACE && loop_snode != 0, TI_ERROR_INVALID_ARGUMENT, "loop SNode must be a non-root container SNode");
+  cudaStream_t st = t->rt->stream();
   t->listgen_async(loop_snode);
   B2TreeDev *dev = t->dev;
   int sid = loop_snode;
@@ -188,6 +201,25 @@ int32_t b2_jit_launch(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t
   const int64_t nc = std::min<int64_t>(t->s[loop_snode].num_cells, 1024);
   const int block = (int)std::min<int64_t>(256, std::max<int64_t>(32, (nc + 31) / 32 * 32));
   B2_CUDA(cudaLaunchKernel((const void *)k->fn, dim3(t->rt->num_sms * 8), dim3(block), params, 0, st));
+  t->rt->count_launch();
+  return 0;
+  B2_API_END(-1)
+}
+
+// `for i in range(begin, end)`: grid-stride loop, block 128 (the reference's default block_dim), grid capped at a
+// few waves (gpu_parallel_range_for, runtime.cpp:1541-1565; launch shape codegen_cuda.cpp:606-705)
+int32_t b2_jit_launch_range(B2JitKernel k, B2Tree t, int64_t begin, int64_t end, const int32_t *field_places, int32_t n_fields, const uint64_t *args, int32_t n_args) {
+  B2_API_BEGIN
+  jit_upload_table(k, t, field_places, n_fields, args, n_args);
+  jit_require(k->fn_range != nullptr, TI_ERROR_INVALID_ARGUMENT, "this kernel has no B2_RANGE_BODY (range-for) entry");
+  if (end <= begin) return 0;
+  B2TreeDev *dev = t->dev;
+  long long b = begin, e = end;
+  const B2JitTable *tp = k->tab_dev;
+  void *params[4] = {&dev, &b, &e, &tp};
+  const int block = 128;
+  const int grid = (int)std::min<int64_t>((end - begin + block - 1) / block, (int64_t)t->rt->num_sms * 16);
+  B2_CUDA(cudaLaunchKernel((const void *)k->fn_range, dim3(grid), dim3(block), params, 0, t->rt->stream()));
   t->rt->count_launch();
   return 0;
   B2_API_END(-1)

@@ -12,8 +12,16 @@
 //       atomicAdd(c.arg<float *>(0), v);             //   s[None] += v
 //     }
 //
+// and / or a particle loop (`for i in range(n)`, the reference's range-for task):
+//
+//     B2_RANGE_BODY(c) {                             // for p in range(n):
+//       const float3 xp = c.arg<const float3 *>(0)[c.i];
+//       int J[B2_MAX_AXES] = {int(xp.x * 64), int(xp.y * 64), int(xp.z * 64)};
+//       atomicAdd(c.ref<float>(0, J), 1.0f);         //   m[J] += 1   (activates the cell)
+//     }
+//
 // The library wraps it with this header (and b2_internal.cuh), compiles it for sm_100a with NVRTC
-// and launches b2_jit_struct_for over the element list of the loop SNode.  Field f = f-th entry of the
+// and launches b2_jit_struct_for over the element list of the loop SNode / b2_jit_range_for grid-strided.  Field f = f-th entry of the
 // place list given at launch; arg k = k-th 64-bit launch argument (scalars bit-cast, device pointers).
 #pragma once
 #define B2_JIT_MAX_FIELDS 8
@@ -31,13 +39,10 @@ struct B2JitTable {
 };
 
 #ifdef __CUDACC_RTC__  // everything below exists only in the run-time compiled translation unit
-struct B2Ctx {
+// Field access shared by both loop kinds (global pointer lowering, lower_access.cpp:42-281).
+struct B2Access {
   B2TreeDev *T;
   const B2JitTable *tab;
-  const B2SNodeDev *ts;  // the loop SNode
-  const B2Element *E;    // the work item this cell belongs to
-  int sid, j;            // loop SNode id, linear cell index inside E->node
-  int I[B2_MAX_AXES];    // loop index (refine_coordinates, struct_llvm.cpp:171-188)
 
   template <typename V>
   __device__ __forceinline__ V arg(int k) const {
@@ -52,26 +57,13 @@ struct B2Ctx {
   // Address of field f at index J.  ACT: activate every level on the way like a write access in the
   // reference (lower_access.cpp:254-279); otherwise inactive cells resolve to the ambient zero element.
   template <typename V, bool ACT>
-  __device__ __forceinline__ V *ptr(int f, const int *J) const {
+  __device__ __forceinline__ V *walk(int f, const int *J) const {
     const B2JitField &F = tab->f[f];
-    const int hid = F.holder;
-    if (!ACT && hid == sid) {  // the loop's own cell, at the loop index: no walk (the path a struct-for never re-activates)
-      bool same = true;
-#pragma unroll
-      for (int a = 0; a < B2_MAX_AXES; a++) same = same && J[a] == I[a];
-      if (same) return (V *)(b2_lookup(T, sid, E->node, j) + F.off);
-    }
     int cell;
     u8 *node = b2_walk<ACT>(T, F.path, J, &cell, nullptr);
-    if (ACT) b2_activate_cell(T, hid, node, cell);
-    return (V *)(b2_lookup(T, hid, node, cell) + F.off);
+    if (ACT) b2_activate_cell(T, F.holder, node, cell);
+    return (V *)(b2_lookup(T, F.holder, node, cell) + F.off);
   }
-  template <typename V>
-  __device__ __forceinline__ V read(int f, const int *J) const { return *ptr<V, false>(f, J); }
-  template <typename V>
-  __device__ __forceinline__ void write(int f, const int *J, V v) const { *ptr<V, true>(f, J) = v; }
-  template <typename V>
-  __device__ __forceinline__ V *ref(int f, const int *J) const { return ptr<V, true>(f, J); }  // for atomics / +=
   // ti.is_active(holder of field f, J)
   __device__ __forceinline__ bool is_active(int f, const int *J) const {
     const B2JitField &F = tab->f[f];
@@ -80,6 +72,32 @@ struct B2Ctx {
     u8 *node = b2_walk<false>(T, F.path, J, &cell, &dead);
     return !dead && b2_is_active(T->s[F.holder], node, cell);
   }
+};
+
+// struct-for: `for I in ti.grouped(loop_snode)`
+struct B2Ctx : B2Access {
+  const B2SNodeDev *ts;  // the loop SNode
+  const B2Element *E;    // the work item this cell belongs to
+  int sid, j;            // loop SNode id, linear cell index inside E->node
+  int I[B2_MAX_AXES];    // loop index (refine_coordinates, struct_llvm.cpp:171-188)
+
+  template <typename V, bool ACT>
+  __device__ __forceinline__ V *ptr(int f, const int *J) const {
+    const B2JitField &F = tab->f[f];
+    if (!ACT && F.holder == sid) {  // the loop's own cell at the loop index: no walk (a struct-for never re-activates its own path)
+      bool same = true;
+#pragma unroll
+      for (int a = 0; a < B2_MAX_AXES; a++) same = same && J[a] == I[a];
+      if (same) return (V *)(b2_lookup(T, sid, E->node, j) + F.off);
+    }
+    return walk<V, ACT>(f, J);
+  }
+  template <typename V>
+  __device__ __forceinline__ V read(int f, const int *J) const { return *ptr<V, false>(f, J); }
+  template <typename V>
+  __device__ __forceinline__ void write(int f, const int *J, V v) const { *ptr<V, true>(f, J) = v; }
+  template <typename V>
+  __device__ __forceinline__ V *ref(int f, const int *J) const { return ptr<V, true>(f, J); }  // for atomics / +=
   // J = I with axis a shifted by d
   __device__ __forceinline__ void offset(int *J, int a, int d) const {
 #pragma unroll
@@ -88,9 +106,22 @@ struct B2Ctx {
   }
 };
 
-#define B2_BODY(c) __device__ __forceinline__ void b2_body(B2Ctx &c)
-__device__ __forceinline__ void b2_body(B2Ctx &c);
+// range-for: `for i in range(begin, end)` (particle loops; gpu_parallel_range_for, runtime.cpp:1541-1565)
+struct B2RangeCtx : B2Access {
+  long long i;
+  template <typename V>
+  __device__ __forceinline__ V read(int f, const int *J) const { return *walk<V, false>(f, J); }
+  template <typename V>
+  __device__ __forceinline__ void write(int f, const int *J, V v) const { *walk<V, true>(f, J) = v; }
+  template <typename V>
+  __device__ __forceinline__ V *ref(int f, const int *J) const { return walk<V, true>(f, J); }
+};
 
+#define B2_BODY(c) __device__ __forceinline__ void b2_body(B2Ctx &c)
+#define B2_RANGE_BODY(c) __device__ __forceinline__ void b2_range_body(B2RangeCtx &c)
+
+#ifdef B2_JIT_HAS_BODY
+__device__ __forceinline__ void b2_body(B2Ctx &c);
 // parallel_struct_for (runtime.cpp:1422-1464): CTA <-> Element, thread <-> cell
 extern "C" __global__ void __launch_bounds__(256) b2_jit_struct_for(B2TreeDev *T, int sid, const B2JitTable *tab) {
   const B2SNodeDev &ts = T->s[sid];
@@ -109,4 +140,15 @@ extern "C" __global__ void __launch_bounds__(256) b2_jit_struct_for(B2TreeDev *T
     }
   }
 }
+#endif
+#ifdef B2_JIT_HAS_RANGE
+__device__ __forceinline__ void b2_range_body(B2RangeCtx &c);
+extern "C" __global__ void __launch_bounds__(256) b2_jit_range_for(B2TreeDev *T, long long begin, long long end, const B2JitTable *tab) {
+  for (long long i = begin + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < end; i += (long long)gridDim.x * blockDim.x) {
+    B2RangeCtx c;
+    c.T = T, c.tab = tab, c.i = i;
+    b2_range_body(c);
+  }
+}
+#endif
 #endif  // __CUDACC_RTC__

@@ -386,6 +386,16 @@ class StructFor:
         lib.b2_jit_launch(self.handle, t, snode.id, places, len(fields), slots, len(args))
         L.check()
 
+    def range(self, begin, end, fields=(), args=()):
+        """`for i in range(begin, end)` over the source's B2_RANGE_BODY (particle loops; c.i = index)."""
+        if self.handle is None or self._rt != _prog.rt:
+            raise RuntimeError("kernel belongs to a runtime that was reset")
+        t = _materialize()
+        places = (C.c_int32 * max(1, len(fields)))(*[f.place_id for f in fields])
+        slots = (C.c_uint64 * max(1, len(args)))(*[_arg_bits(a) for a in args])
+        lib.b2_jit_launch_range(self.handle, t, int(begin), int(end), places, len(fields), slots, len(args))
+        L.check()
+
     def log(self):
         n = lib.b2_jit_log(self.handle, None, 0)
         buf = C.create_string_buffer(int(n))

@@ -134,3 +134,69 @@ def test_compile_error_surfaces_log(ti):
     with pytest.raises(B2RuntimeError) as e:
         ti.struct_for("B2_BODY(c) { undeclared_symbol = 1; }", "broken")
     assert "undeclared_symbol" in str(e.value) and "broken" in str(e.value)
+
+
+def test_user_p2g_range_for_then_grid_struct_for(ti):
+    """The reference's plain (non-BLS) MPM idiom written by the user: a particle range-for that scatters with
+    quadratic B-spline weights into a SPARSE grid through activating atomic adds (mpm3d.py:40-55), followed by a
+    struct-for over the active grid cells (mpm3d.py:56-61).  Grid mass / momentum against NumPy, active blocks
+    against the touched-block set (x64 semantics)."""
+    import torch
+    from test_gpu_mpm import expected_blocks
+    n_grid, N = 64, 20000
+    gm, gv = ti.field(ti.f32), ti.field(ti.f32)
+    blk = ti.root.pointer(ti.ijk, 4).bitmasked(ti.ijk, 4).dense(ti.ijk, 4)
+    blk.place(gm, gv)
+    rng = np.random.default_rng(7)
+    x = (rng.random((N, 3)) * 0.3 + 0.3).astype(np.float32)
+    vy = (rng.random(N) - 0.5).astype(np.float32)
+    k = ti.struct_for("""
+    B2_RANGE_BODY(c) {
+      const float *x = c.arg<const float *>(0) + 3 * c.i;
+      const float vy = c.arg<const float *>(1)[c.i];
+      const float inv_dx = c.arg<float>(2);
+      int base[3]; float w[3][3];
+      for (int d = 0; d < 3; d++) {
+        const float X = x[d] * inv_dx;
+        base[d] = (int)(X - 0.5f);
+        const float fx = X - (float)base[d];
+        w[0][d] = 0.5f * (1.5f - fx) * (1.5f - fx);
+        w[1][d] = 0.75f - (fx - 1.0f) * (fx - 1.0f);
+        w[2][d] = 0.5f * (fx - 0.5f) * (fx - 0.5f);
+      }
+      for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) for (int kk = 0; kk < 3; kk++) {
+        int J[B2_MAX_AXES] = {base[0] + i, base[1] + j, base[2] + kk};
+        const float wt = w[i][0] * w[j][1] * w[kk][2];
+        atomicAdd(c.ref<float>(0, J), wt);          // grid_m[base + offset] += weight * p_mass (p_mass = 1)
+        atomicAdd(c.ref<float>(1, J), wt * vy);     // grid_v.y
+      }
+    }
+    B2_BODY(c) {                                    // for I in ti.grouped(grid_m): if m > 0: v /= m
+      const float m = c.read<float>(0, c.I);
+      if (m > 0.0f) *c.ref<float>(1, c.I) = c.read<float>(1, c.I) / m;
+    }""", "user_mpm")
+    dx, dvy = torch.from_numpy(x).cuda(), torch.from_numpy(vy).cuda()
+    k.range(0, N, fields=[gm, gv], args=[dx, dvy, float(n_grid)])
+    M = gm.to_numpy()
+    Xg = x * np.float32(n_grid)
+    base = (Xg - np.float32(0.5)).astype(np.int32)
+    fx = Xg - base.astype(np.float32)
+    w = np.stack([np.float32(0.5) * (np.float32(1.5) - fx) ** 2, np.float32(0.75) - (fx - np.float32(1.0)) ** 2,
+                  np.float32(0.5) * (fx - np.float32(0.5)) ** 2])           # (3, N, 3)
+    want_m = np.zeros((n_grid,) * 3, np.float64)
+    want_p = np.zeros((n_grid,) * 3, np.float64)
+    for i in range(3):
+        for j in range(3):
+            for kk in range(3):
+                wt = (w[i, :, 0] * w[j, :, 1] * w[kk, :, 2]).astype(np.float64)
+                np.add.at(want_m, (base[:, 0] + i, base[:, 1] + j, base[:, 2] + kk), wt)
+                np.add.at(want_p, (base[:, 0] + i, base[:, 1] + j, base[:, 2] + kk), wt * vy)
+    assert np.allclose(M, want_m, rtol=2e-5, atol=1e-6)
+    assert abs(M.sum() - N) < 1e-3 * N * 1e-2                             # partition of unity
+    got_blocks = ti.active_indices(blk.parent())                          # bitmasked cells = 4^3 blocks
+    assert np.array_equal(got_blocks, expected_blocks(x, n_grid, halo=False))
+    k(blk, fields=[gm, gv])                                                # struct-for over active cells
+    V = gv.to_numpy()
+    nz = want_m > 0
+    assert np.allclose(V[nz], (want_p[nz] / want_m[nz]), rtol=1e-3, atol=1e-5)
+    assert np.array_equal(ti.active_indices(blk.parent()), got_blocks)     # the struct-for activated nothing new
