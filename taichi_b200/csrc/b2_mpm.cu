@@ -338,7 +338,13 @@ __global__ void __launch_bounds__(256) k_mpm_diag(MpmDev M, int gen, double *out
 // ------------------------------------------------------------------------------------------
 // grid kernels: struct-for over the leaf Element list (one Element = one 4^3 block = 1 KiB)
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_mpm_clear(B2TreeDev *T, int leaf) {
+// zero_a / zero_b (optional): the substep's work counters and the chunk-arena cursor of the generation G2P will
+// write -- reset here, by the first kernel of the substep, instead of by three memset nodes between the kernels
+__global__ void __launch_bounds__(256) k_mpm_clear(B2TreeDev *T, int leaf, u32 *zero_a, u32 *zero_b) {
+  if (blockIdx.x == 0 && threadIdx.x < 8) {
+    if (zero_a) zero_a[threadIdx.x] = 0;
+    if (zero_b && threadIdx.x < 4) zero_b[threadIdx.x] = 0;
+  }
   B2CList *L = T->lists[leaf];
   const u32 ne = L->count;
   const int sub = threadIdx.x >> 6, t = threadIdx.x & 63;
@@ -609,6 +615,7 @@ struct B2Mpm_t {
   bool order_valid = false;  // P2G has left the cell order of the current generation in the chunks (G2P skips its sort)
   bool sparse = false;
   bool profiling = false;
+  bool in_substep = false;  // inside substep(): k_mpm_clear resets the work counters / arena cursor for the phases that follow
   std::vector<cudaEvent_t> prof_events;
   double phase_sum[6] = {0, 0, 0, 0, 0, 0};
   long long phase_count = 0;
@@ -840,12 +847,13 @@ void B2Mpm_t::ensure_lists() {
 }
 void B2Mpm_t::clear_grid() {
   ensure_lists();
-  k_mpm_clear<<<rt->num_sms * 8, 256, 0, rt->stream()>>>(tree->dev, M.leaf_sid);
+  k_mpm_clear<<<rt->num_sms * 8, 256, 0, rt->stream()>>>(tree->dev, M.leaf_sid, in_substep ? M.work_counter : nullptr,
+                                                        in_substep ? M.arena_next[gen ^ 1] : nullptr);
   rt->count_launch();
 }
 void B2Mpm_t::p2g() {
   cudaStream_t st = rt->stream();
-  B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
+  if (!in_substep) B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));  // (P2G takes slots from counter 0, G2P from counter 1)
   if (prm.block_local)
   {
     k_mpm_p2g<<<rt->num_sms * 3, P2G_NT, sizeof(P2GShared), st>>>(M, gen);
@@ -864,8 +872,10 @@ void B2Mpm_t::grid_op() {
 void B2Mpm_t::g2p() {
   cudaStream_t st = rt->stream();
   // the generation being written starts with an empty chunk arena
-  B2_CUDA(cudaMemsetAsync(M.arena_next[gen ^ 1], 0, 16, st));
-  B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
+  if (!in_substep) {
+    B2_CUDA(cudaMemsetAsync(M.arena_next[gen ^ 1], 0, 16, st));
+    B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
+  }
   if (prm.block_local)
   {
     static const bool no_order = getenv("B2_G2P_SORT") != nullptr;  // experiment switch: always sort
@@ -896,6 +906,11 @@ void B2Mpm_t::substep(int n) {
       prof_events.push_back(e);
     }
   }
+  in_substep = true;  // clear resets the counters of the whole substep: no memset nodes between the kernels
+  struct Leave {
+    bool &f;
+    ~Leave() { f = false; }
+  } leave{in_substep};
   for (int s = 0; s < n; s++) {
     cudaEvent_t *e = profiling ? &prof_events[6 * s] : nullptr;
     if (e) B2_CUDA(cudaEventRecord(e[0], st));
