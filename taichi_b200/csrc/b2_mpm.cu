@@ -856,7 +856,7 @@ void B2Mpm_t::p2g() {
   if (!in_substep) B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));  // (P2G takes slots from counter 0, G2P from counter 1)
   if (prm.block_local)
   {
-    k_mpm_p2g<<<rt->num_sms * 3, P2G_NT, sizeof(P2GShared), st>>>(M, gen);
+    k_mpm_p2g<<<rt->num_sms * P2G_CTAS, P2G_NT, sizeof(P2GShared), st>>>(M, gen);
     order_valid = true;
   }
   else

@@ -27,10 +27,21 @@
 //            activate_halo reproduces the CUDA-BLS epilogue).
 #pragma once
 
+#ifdef P2G_WIDE                    /* experiment (make EXTRA=-DP2G_WIDE): 2 CTAs of 384 threads per SM; 0.618 ms vs 0.489 ms on C3 */
+#define P2G_NT 384
+#define P2G_NW 352
+#define P2G_UNITS 117
+#define P2G_CTAS 2
+#else
 #define P2G_NT 256
-#define P2G_NW 224                 /* worker threads (7 warps); warp 7 is the helper             */
-#define P2G_PASS MPM_PASS          /* bin entries per work unit                                  */
+#define P2G_NW 224                 /* worker threads (7 warps); the last warp is the helper      */
 #define P2G_UNITS 74               /* worker thread triples                                      */
+#define P2G_CTAS 3
+#endif
+#define P2G_STR2(x) #x
+#define P2G_STR(x) P2G_STR2(x)
+#define P2G_PASS MPM_PASS          /* bin entries per work unit                                  */
+#define P2G_ROUNDS ((P2G_PASS + P2G_NW - 1) / P2G_NW) /* entries per worker thread */
 #define P2G_XUNITS (P2G_UNITS - 64)/* units beyond one per cell                                  */
 #define P2G_CAP (P2G_PASS + 32)    /* staging slots: the first 32 rows are padded to odd lengths */
 #define P2G_TASKS 280              /* flush tasks: pad nodes, the heavy ones split in groups of <= 9 sources */
@@ -71,9 +82,9 @@ __device__ __forceinline__ u32 p2g_touch_mask(int c) {
   const int h = ((c >> 5) & 1) << 2 | ((c >> 3) & 1) << 1 | ((c >> 1) & 1);
   return (u32)((0xff553311'0f050301ull >> (h * 8)) & 0xffu);
 }
-__device__ __forceinline__ void bar_workers() { asm volatile("bar.sync 1, 224;" ::: "memory"); }
-__device__ __forceinline__ void bar_count_arrive() { asm volatile("bar.arrive 2, 256;" ::: "memory"); }
-__device__ __forceinline__ void bar_count_wait() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
+__device__ __forceinline__ void bar_workers() { asm volatile("bar.sync 1, " P2G_STR(P2G_NW) ";" ::: "memory"); }
+__device__ __forceinline__ void bar_count_arrive() { asm volatile("bar.arrive 2, " P2G_STR(P2G_NT) ";" ::: "memory"); }
+__device__ __forceinline__ void bar_count_wait() { asm volatile("bar.sync 2, " P2G_STR(P2G_NT) ";" ::: "memory"); }
 
 
 // ---- helper warp -----------------------------------------------------------------------------------
@@ -203,14 +214,14 @@ __device__ __forceinline__ void p2g_count(const MpmDev &M, int gen, u32 nslots, 
   // entries in REVERSED thread order: the stage phase gives the ragged third round (entries >= 448) to the first
   // warps, so the count that follows it without a barrier gives its third round to the last ones
   const int rt = P2G_NW - 1 - tid;
-  float4 p0[3];
+  float4 p0[P2G_ROUNDS];
 #pragma unroll
-  for (int e = 0; e < 3; e++) {
+  for (int e = 0; e < P2G_ROUNDS; e++) {
     const int t = rt + e * P2G_NW;
     if (t < n) p0[e] = *(const float4 *)p2g_entry_ptr(M, gen, off0, cid0, cid1, cid2, t);
   }
 #pragma unroll
-  for (int e = 0; e < 3; e++) {
+  for (int e = 0; e < P2G_ROUNDS; e++) {
     const int t = rt + e * P2G_NW;
     if (t < n) {
       unsigned short ck = 0xffffu;
@@ -248,7 +259,7 @@ __device__ __forceinline__ void p2g_flush_task(const MpmDev &M, const P2GShared 
 #define TCK(i) do { } while (0)
 #endif
 static_assert(sizeof(P2GShared) <= 55 * 1024, "4 CTAs per SM");
-__global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
+__global__ void __launch_bounds__(P2G_NT, P2G_CTAS) k_mpm_p2g(MpmDev M, int gen) {
 #ifdef P2G_TIMING
   long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
   int nun = 0;
@@ -381,9 +392,9 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
         S.nb[nbh] = mpm_block_ptr<false>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
       }
       stage(0, Ea);
-      load(2, Ea);
+      if (P2G_ROUNDS > 2) load(2, Ea);
       stage(1, Eb);
-      stage(2, Ea);
+      if (P2G_ROUNDS > 2) stage(2, Ea);
     }
     TCK(1);
     // ---- count the NEXT unit; the helper orders it while this unit is scattered and flushed -----------
@@ -459,8 +470,8 @@ __global__ void __launch_bounds__(P2G_NT, 3) k_mpm_p2g(MpmDev M, int gen) {
     bar_workers();
     TCK(7);
     // ---- flush: every task sums <= 9 partials of one pad node and issues one vector red -----------------
-    p2g_flush_task(M, S, (const ulonglong2 *)P, tid);
-    if (tid >= 2 * P2G_NW - P2G_TASKS) p2g_flush_task(M, S, (const ulonglong2 *)P, P2G_NW + (P2G_NW - 1 - tid));
+    if (tid < P2G_TASKS) p2g_flush_task(M, S, (const ulonglong2 *)P, tid);
+    if (P2G_TASKS > P2G_NW && tid >= 2 * P2G_NW - P2G_TASKS) p2g_flush_task(M, S, (const ulonglong2 *)P, P2G_NW + (P2G_NW - 1 - tid));
     TCK(8);
 #ifdef P2G_TIMING
     nun++;
