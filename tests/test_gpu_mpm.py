@@ -379,3 +379,86 @@ def test_pipelined_host_io_matches_blocking(rt):
     xr = s.get_particles()[0]
     assert np.allclose(xr, blocking[0][0], rtol=0, atol=1e-6)
     s.destroy()
+
+
+def test_full_size_c3_properties(rt):
+    """config[2] at full size (512^3 pointer -> bitmasked -> dense(4^3), 8M particles): the size-independent
+    properties -- partition of unity (grid mass = N p_mass), momentum conservation of P2G, exact active-block set,
+    particle count and finiteness after 10 substeps.  The grid sums run as a run-time compiled struct-for over the
+    solver's own SNode tree (b2_jit_*), in fp64."""
+    import sys
+    import os
+    import torch
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    import taichi_b200 as tb
+    from taichi_b200 import _lib as L
+    lib = L.lib
+    n_grid, N, dt, layout, _ = bench.WORKLOADS["c3"]
+    x0, v0, C0, J0 = bench.make_cloud("c3", N, seed=3)
+    s = tb.Mpm3D(rt, n_grid, N, dt, layout=layout)
+    s.set_particles(x0, v0, C0, J0)
+    s.clear_grid()
+    s.p2g()
+    k = lib.b2_jit_compile(rt.handle, b"""B2_BODY(c) {
+        double *acc = c.arg<double *>(0);
+        const float m = c.read<float>(3, c.I);
+        if (m != 0.0f) {
+            atomicAdd(acc + 0, (double)m);
+            atomicAdd(acc + 1, (double)c.read<float>(0, c.I));
+            atomicAdd(acc + 2, (double)c.read<float>(1, c.I));
+            atomicAdd(acc + 3, (double)c.read<float>(2, c.I));
+            atomicAdd(acc + 4, 1.0);
+        }
+    }""", b"grid_sums")
+    L.check()
+    tree, leaf = lib.b2_mpm_tree(s.handle), lib.b2_mpm_leaf_snode(s.handle)
+    places = (C.c_int32 * 4)(leaf + 1, leaf + 2, leaf + 3, leaf + 4)
+
+    def grid_sums():
+        acc = torch.zeros(5, dtype=torch.float64, device="cuda")
+        args = (C.c_uint64 * 1)(acc.data_ptr())
+        assert lib.b2_jit_launch(k, tree, leaf, places, 4, args, 1) == 0, L.last_error()
+        torch.cuda.synchronize()
+        return acc.cpu().numpy()
+
+    def touched_blocks(x):  # expected_blocks(halo=False) on integer keys (8M particles: seconds instead of a minute)
+        base = (x.astype(np.float32) * np.float32(n_grid) - np.float32(0.5)).astype(np.int32)
+        nb = n_grid // 4
+        keys = []
+        for d in np.ndindex(2, 2, 2):
+            b = (base + 2 * np.array(d, np.int32)) >> 2
+            ok = (b < nb).all(1)
+            keys.append(np.unique((b[ok, 0].astype(np.int64) * nb + b[ok, 1]) * nb + b[ok, 2]))
+        return np.unique(np.concatenate(keys))
+
+    def keys_of(blocks):
+        nb = n_grid // 4
+        return np.sort((blocks[:, 0].astype(np.int64) * nb + blocks[:, 1]) * nb + blocks[:, 2])
+
+    p_mass = float(np.float32((1.0 / n_grid * 0.5) ** 2))
+    g = grid_sums()
+    assert abs(g[0] - N * p_mass) < 2e-6 * N * p_mass
+    want_p = p_mass * v0.astype(np.float64).sum(0)            # C = 0, J = 1: the stress / affine terms cancel
+    assert np.allclose(g[1:4], want_p, rtol=1e-5, atol=1e-7 * N * p_mass)
+    blocks = s.active_blocks()
+    assert np.array_equal(keys_of(blocks), touched_blocks(x0))
+    assert g[4] <= len(blocks) * 64
+    d0 = s.diagnostics()
+    assert d0["particles"] == N and abs(d0["py"] - want_p[1]) < 1e-6 * abs(want_p[1]) and abs(d0["sum_J"] - N) < 1e-3
+    s.grid_op()
+    s.g2p()
+    s.substep(9)
+    st = s.stats()
+    assert st["particles"] == N
+    d1 = s.diagnostics()
+    assert d1["particles"] == N and np.isfinite(list(d1.values())).all() and d1["max_speed"] < 10.0 and d1["max_dJ"] < 0.5
+    s.clear_grid()
+    s.p2g()
+    g = grid_sums()
+    assert abs(g[0] - N * p_mass) < 2e-6 * N * p_mass          # mass is still all on the grid after 10 substeps
+    xr = s.get_particles()[0]
+    assert np.isfinite(xr).all() and xr.min() > 0.0 and xr.max() < 1.0
+    assert np.isin(touched_blocks(xr), keys_of(s.active_blocks())).all()
+    lib.b2_jit_destroy(k)
+    s.destroy()
