@@ -146,7 +146,8 @@ def test_diagnostics_vs_numpy():
     assert got[0] == N
     assert np.allclose(got[:6], want[:6], rtol=1e-9, atol=1e-12)
     assert np.allclose(got[6:], want[6:], rtol=1e-6)
-    assert np.array_equal(d.diagnostics(), got)
+    again = d.diagnostics()                    # fp64 atomics: the order of the adds differs from launch to launch
+    assert np.allclose(again[:6], got[:6], rtol=1e-12, atol=0) and np.array_equal(again[6:], got[6:])
     d.destroy()
     s.destroy()
 
@@ -203,6 +204,6 @@ def test_nccl_two_gpus(tmp_path, native):
     # every rank got the same reduced vector = SUM / MAX of the slabs' local vectors
     assert np.array_equal(parts[0][5], parts[1][5])
     local = np.stack([p[6] for p in parts])
-    assert np.allclose(parts[0][5][:6], local[:, :6].sum(0), rtol=1e-14, atol=0)
+    assert np.allclose(parts[0][5][:6], local[:, :6].sum(0), rtol=1e-12, atol=1e-18)
     assert np.array_equal(parts[0][5][6:], local[:, 6:].max(0))
     assert parts[0][5][0] == N
