@@ -64,6 +64,20 @@ struct B2Access {
     if (ACT) b2_activate_cell(T, F.holder, node, cell);
     return (V *)(b2_lookup(T, F.holder, node, cell) + F.off);
   }
+  // ti.is_active(ancestor, ti.rescale_index(field, ancestor, J)): `up` levels above the SNode that holds field f
+  // (up = 0: the holder itself, 1: its parent SNode, ...), J at the field's own resolution
+  __device__ __forceinline__ bool is_active_up(int f, const int *J, int up) const {
+    const B2Path &P = tab->f[f].path;
+    const int q = P.n - 1 - up;  // level of the queried SNode on the path (level 0 = root)
+    if (q < 1) return true;
+    u8 *node = T->root;
+    for (int l = 0; l < q; l++) {
+      const int sid = P.id[l], i = b2_level_index(T, P, l, J);
+      if (!b2_is_active(T->s[sid], node, i)) return false;
+      node = b2_lookup(T, sid, node, i) + T->s[P.id[l + 1]].offset_in_parent_cell;
+    }
+    return b2_is_active(T->s[P.id[q]], node, b2_level_index(T, P, q, J));
+  }
   // ti.is_active(holder of field f, J)
   __device__ __forceinline__ bool is_active(int f, const int *J) const {
     const B2JitField &F = tab->f[f];

@@ -200,3 +200,97 @@ def test_user_p2g_range_for_then_grid_struct_for(ti):
     nz = want_m > 0
     assert np.allclose(V[nz], (want_p[nz] / want_m[nz]), rtol=1e-3, atol=1e-5)
     assert np.array_equal(ti.active_indices(blk.parent()), got_blocks)     # the struct-for activated nothing new
+
+
+def test_taichi_sparse_capi_example(ti):
+    """c_api/tests/taichi_sparse_test.cpp + tests/cpp/aot/python_scripts/taichi_sparse_test_.py: three pointer levels
+    over a dense(4^2) leaf, fill_img / block1_deactivate_all / activate(t) / paint / check_img_value, the kernels
+    written as JIT bodies.  Known answer of the reference's own check: sum_{i<20} img[i, i] == 15.25; on top of it the
+    whole image against a NumPy restatement of the same pipeline (taichi_logo: examples/patterns.py:5-36)."""
+    n = 512
+    res = n + n // 4 + n // 16 + n // 64
+    x = ti.field(ti.i32)
+    img = ti.field(ti.f32, shape=(res, res))
+    block1 = ti.root.pointer(ti.ij, n // 64)
+    block2 = block1.pointer(ti.ij, 4)
+    block3 = block2.pointer(ti.ij, 4)
+    leaf = block3.dense(ti.ij, 4)
+    leaf.place(x)
+    k = ti.struct_for("""
+    __device__ int taichi_logo(float px, float py) {          // examples/patterns.py:5-36, scale = 1 / 1.11
+      const float scale = 1.0f / 1.11f;
+      const float x = (px - 0.5f) / scale + 0.5f, y = (py - 0.5f) / scale + 0.5f;
+      auto d2 = [&](float cx, float cy) { return (x - cx) * (x - cx) + (y - cy) * (y - cy); };
+      int ret = -1;
+      if (!(d2(0.5f, 0.5f) <= 0.52f * 0.52f)) { if (ret == -1) ret = 0; }
+      if (!(d2(0.5f, 0.5f) <= 0.495f * 0.495f)) { if (ret == -1) ret = 1; }
+      if (d2(0.5f, 0.25f) <= 0.08f * 0.08f) { if (ret == -1) ret = 1; }
+      if (d2(0.5f, 0.75f) <= 0.08f * 0.08f) { if (ret == -1) ret = 0; }
+      if (d2(0.5f, 0.25f) <= 0.25f * 0.25f) { if (ret == -1) ret = 0; }
+      if (d2(0.5f, 0.75f) <= 0.25f * 0.25f) { if (ret == -1) ret = 1; }
+      if (x < 0.5f) { if (ret == -1) ret = 1; } else { if (ret == -1) ret = 0; }
+      return 1 - ret;
+    }
+    __device__ int scatter(int i) { return i + i / 4 + i / 16 + i / 64 + 2; }
+    B2_BODY(c) { c.write<float>(0, c.I, c.arg<float>(0)); }                 // fill_img: img.fill(0.05)
+    B2_RANGE_BODY(c) {                                                     // for i, j in ti.ndrange(n, n)
+      const int n = c.arg<int>(1), mode = c.arg<int>(2);
+      const int i = (int)(c.i / n), j = (int)(c.i % n);
+      int I[B2_MAX_AXES] = {i, j};
+      if (mode == 0) {                                                     // activate(t)
+        const float t = c.arg<float>(0);
+        float px = (float)i / (float)n - 0.5f, py = (float)j / (float)n - 0.5f;
+        const float cs = cosf(sinf(t)), sn = sinf(sinf(t));               // rotation2d(sin(t)) @ (p - 0.5) + 0.5
+        const float qx = cs * px - sn * py + 0.5f, qy = sn * px + cs * py + 0.5f;
+        if (taichi_logo(qx, qy) == 0) c.write<int>(1, I, 1);              // x[i, j] = 1 (activates 3 pointer levels)
+      } else {                                                             // paint()
+        int t = c.read<int>(1, I);
+        t += c.is_active_up(1, I, 3) + c.is_active_up(1, I, 2) + c.is_active_up(1, I, 1);   // block1, block2, block3
+        int P[B2_MAX_AXES] = {scatter(i), scatter(j)};
+        c.write<float>(0, P, 1.0f - (float)t / 4.0f);
+      }
+    }""", "taichi_sparse")
+    k(img.parent_snode, fields=[img], args=[np.float32(0.05)])
+    x[100, 100] = 1                                   # something to deactivate
+    assert len(ti.active_indices(block1)) == 1
+    block1.deactivate_all()                           # block1_deactivate_all (children first, GC)
+    assert len(ti.active_indices(block1)) == 0
+    val = np.float32(0.05)
+    k.range(0, n * n, fields=[img, x], args=[val, np.int32(n), np.int32(0)])
+    k.range(0, n * n, fields=[img, x], args=[val, np.int32(n), np.int32(1)])
+    im = img.to_numpy()
+    acc = np.float32(0)
+    for i in range(20):                                                    # check_img_value: s: ti.f32, s += img[i, i]
+        acc = np.float32(acc + im[i, i])
+    assert acc == np.float32(15.25)
+    # NumPy restatement of the whole pipeline (fp32 like the kernels)
+    f = np.float32
+    ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    px, py = (ii.astype(f) / f(n) - f(0.5)), (jj.astype(f) / f(n) - f(0.5))
+    cs, sn = np.cos(np.sin(val, dtype=f), dtype=f), np.sin(np.sin(val, dtype=f), dtype=f)
+    qx, qy = cs * px - sn * py + f(0.5), sn * px + cs * py + f(0.5)
+    sc = f(1.0) / f(1.11)
+    X, Y = (qx - f(0.5)) / sc + f(0.5), (qy - f(0.5)) / sc + f(0.5)
+    d2 = lambda cx, cy: (X - f(cx)) ** 2 + (Y - f(cy)) ** 2
+    ret = np.full((n, n), -1)
+    for cond, v in [(~(d2(0.5, 0.5) <= f(0.52) * f(0.52)), 0), (~(d2(0.5, 0.5) <= f(0.495) * f(0.495)), 1),
+                    (d2(0.5, 0.25) <= f(0.08) * f(0.08), 1), (d2(0.5, 0.75) <= f(0.08) * f(0.08), 0),
+                    (d2(0.5, 0.25) <= f(0.25) * f(0.25), 0), (d2(0.5, 0.75) <= f(0.25) * f(0.25), 1),
+                    (X < f(0.5), 1), (np.ones((n, n), bool), 0)]:
+        ret = np.where((ret == -1) & cond, v, ret)
+    on = (1 - ret) == 0
+    xs = x.to_numpy()
+    mism = (xs == 1) != on
+    assert mism.mean() < 2e-4, mism.sum()            # fp32 rounding on a handful of boundary pixels (libdevice vs NumPy sin/cos)
+    act = lambda blk: blk.repeat(n // blk.shape[0], 0).repeat(n // blk.shape[1], 1)
+    def level(cells):
+        m = np.zeros((cells, cells), bool)
+        s_ = n // cells
+        np.logical_or.at(m, (ii[xs == 1] // s_, jj[xs == 1] // s_), True)
+        return act(m)
+    t = xs + level(n // 64).astype(int) + level(n // 16).astype(int) + level(n // 4).astype(int)
+    want = np.full((res, res), f(0.05))
+    s_idx = np.arange(n) + np.arange(n) // 4 + np.arange(n) // 16 + np.arange(n) // 64 + 2
+    want[np.ix_(s_idx, s_idx)] = f(1.0) - t.astype(f) / f(4.0)
+    assert np.array_equal(im, want)                  # given the same x, paint is exact
+    assert np.array_equal(ti.active_indices(block3), np.argwhere(level(n // 4)[::4, ::4]))
