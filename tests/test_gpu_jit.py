@@ -294,3 +294,58 @@ def test_taichi_sparse_capi_example(ti):
     want[np.ix_(s_idx, s_idx)] = f(1.0) - t.astype(f) / f(4.0)
     assert np.array_equal(im, want)                  # given the same x, paint is exact
     assert np.array_equal(ti.active_indices(block3), np.argwhere(level(n // 4)[::4, ::4]))
+
+
+COUNT_CELLS = "B2_BODY(c) { atomicAdd(c.arg<int *>(0), 1); }"
+
+
+def _count(ti, snode, fields):
+    import torch
+    s = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ti.struct_for(COUNT_CELLS, "count")(snode, fields=fields, args=[s])
+    return int(s.item())
+
+
+def test_sparse_basics_known_answers(ti):
+    """tests/python/test_sparse_basics.py:8-113 with the kernels as JIT bodies: the reference's own expected counts."""
+    import torch
+    n = 128
+    # test_pointer (:8-28): for i in x: s += 1  -> 256
+    x = ti.field(ti.f32)
+    ptr = ti.root.pointer(ti.i, n)
+    leaf = ptr.dense(ti.i, n)
+    leaf.place(x)
+    # test_pointer2 (:74-100): pointer -> pointer -> dense, 7 writes into 5 distinct leaf containers -> 5 n
+    y = ti.field(ti.f32)
+    leaf2 = ti.root.pointer(ti.i, n).pointer(ti.i, n).dense(ti.i, n)
+    leaf2.place(y)
+    # test_pointer_is_active_2 (:52-71): root.dense(i).pointer(j).place -> 3 active cells
+    z = ti.field(ti.f32)
+    pz = ti.root.dense(ti.i, n).pointer(ti.j, n)
+    pz.place(z)
+    for q in (0, 127, 256):
+        x[q] = 1
+    assert _count(ti, leaf, [x]) == 256
+    # test_pointer_is_active (:31-49): for i in range(n * n): s += is_active(ptr, rescale_index(x, ptr, [i])) -> 256
+    k = ti.struct_for("""B2_RANGE_BODY(c) {
+        int I[B2_MAX_AXES] = {(int)c.i};
+        atomicAdd(c.arg<int *>(0), (int)c.is_active_up(0, I, 1));
+    }""", "is_active_ptr")
+    s = torch.zeros(1, dtype=torch.int32, device="cuda")
+    k.range(0, n * n, fields=[x], args=[s])
+    assert int(s.item()) == 256
+    for q in (0, 127, 254, 256 + n * n, 257 + n * n, 257 + n * n * 2, 257 + n * n * 5):
+        y[q] = 1
+    assert _count(ti, leaf2, [y]) == 5 * n
+    assert y[257 + n * n * 7] == 0                      # the read of an inactive cell (:99) ...
+    assert _count(ti, leaf2, [y]) == 5 * n              # ... activates nothing (:100)
+    for (a, b) in ((0, 0), (0, 127), (127, 127)):
+        z[a, b] = 1
+    k2 = ti.struct_for("""B2_RANGE_BODY(c) {
+        const int n = c.arg<int>(1);
+        int I[B2_MAX_AXES] = {(int)(c.i / n), (int)(c.i % n)};
+        atomicAdd(c.arg<int *>(0), (int)c.is_active_up(0, I, 0));
+    }""", "is_active_2")
+    s.zero_()
+    k2.range(0, n * n, fields=[z], args=[s, np.int32(n)])
+    assert int(s.item()) == 3
