@@ -78,6 +78,21 @@ struct B2Access {
     }
     return b2_is_active(T->s[P.id[q]], node, b2_level_index(T, P, q, J));
   }
+  // ti.deactivate(ancestor, ti.rescale_index(field, ancestor, J)): non-recursive, like the reference (sparse.md:345-351).
+  // Pointer cells hand their node to the recycle list; the caller runs the SNode's GC after the kernel, which is
+  // what the reference's offloader inserts behind every task that deactivates (offload.cpp:671-695).
+  __device__ __forceinline__ void deactivate_up(int f, const int *J, int up) const {
+    const B2Path &P = tab->f[f].path;
+    const int q = P.n - 1 - up;
+    if (q < 1) return;
+    u8 *node = T->root;
+    for (int l = 0; l < q; l++) {
+      const int sid = P.id[l], i = b2_level_index(T, P, l, J);
+      if (!b2_is_active(T->s[sid], node, i)) return;  // nothing below an inactive cell
+      node = b2_lookup(T, sid, node, i) + T->s[P.id[l + 1]].offset_in_parent_cell;
+    }
+    b2_deactivate_cell(T, P.id[q], node, b2_level_index(T, P, q, J));
+  }
   // ti.is_active(holder of field f, J)
   __device__ __forceinline__ bool is_active(int f, const int *J) const {
     const B2JitField &F = tab->f[f];

@@ -377,7 +377,9 @@ class StructFor:
         L.check()
         self._rt = _prog.rt
 
-    def __call__(self, snode, fields=(), args=()):
+    def __call__(self, snode, fields=(), args=(), gc=()):
+        """gc: pointer / dynamic SNodes whose cells the body deactivates -- their GC runs right after the launch,
+        which is where the reference's offloader puts it (offload.cpp:671-695)."""
         if self.handle is None or self._rt != _prog.rt:
             raise RuntimeError("struct-for kernel belongs to a runtime that was reset")
         t = _materialize()
@@ -385,8 +387,11 @@ class StructFor:
         slots = (C.c_uint64 * max(1, len(args)))(*[_arg_bits(a) for a in args])
         lib.b2_jit_launch(self.handle, t, snode.id, places, len(fields), slots, len(args))
         L.check()
+        for sn in gc:
+            lib.b2_gc(t, sn.id)
+            L.check()
 
-    def range(self, begin, end, fields=(), args=()):
+    def range(self, begin, end, fields=(), args=(), gc=()):
         """`for i in range(begin, end)` over the source's B2_RANGE_BODY (particle loops; c.i = index)."""
         if self.handle is None or self._rt != _prog.rt:
             raise RuntimeError("kernel belongs to a runtime that was reset")
@@ -395,6 +400,9 @@ class StructFor:
         slots = (C.c_uint64 * max(1, len(args)))(*[_arg_bits(a) for a in args])
         lib.b2_jit_launch_range(self.handle, t, int(begin), int(end), places, len(fields), slots, len(args))
         L.check()
+        for sn in gc:
+            lib.b2_gc(t, sn.id)
+            L.check()
 
     def log(self):
         n = lib.b2_jit_log(self.handle, None, 0)

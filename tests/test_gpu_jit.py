@@ -349,3 +349,54 @@ def test_sparse_basics_known_answers(ti):
     s.zero_()
     k2.range(0, n * n, fields=[z], args=[s, np.int32(n)])
     assert int(s.item()) == 3
+
+
+def test_sparse_parallel_activation_and_gc(ti):
+    """tests/python/test_sparse_parallel.py:5-78: activation from inside kernels by many threads at once (the lock-free
+    pointer activation under contention), the reference's expected sums, and its fill / clear cycle x10 on a
+    512 x 512 pointer grid of dense 8 x 8 blocks with in-kernel ti.deactivate + GC after the task."""
+    import torch
+    n = 128
+    x = ti.field(ti.f32)
+    ptr = ti.root.pointer(ti.i, n)
+    leaf = ptr.dense(ti.i, n)
+    leaf.place(x)
+    a = ti.field(ti.f32)
+    N = 512
+    pa = ti.root.pointer(ti.ij, [N, N])
+    la = pa.dense(ti.ij, [8, 8])
+    la.place(a)
+    k = ti.struct_for("""
+    B2_RANGE_BODY(c) {
+      const int mode = c.arg<int>(1), n = c.arg<int>(2);
+      if (mode == 0) { int I[B2_MAX_AXES] = {(int)c.i * n}; c.write<float>(0, I, 0.0f); }           // x[i * n] = 0
+      else if (mode == 1) { int I[B2_MAX_AXES] = {(int)c.i}; c.write<float>(0, I, (float)c.i); }    // x[i] = i
+      else { int I[B2_MAX_AXES] = {(int)(c.i / n), (int)(c.i % n)}; c.write<float>(0, I, 2.0f); }   // a[i, j] = 2.0
+    }
+    B2_BODY(c) {
+      const int mode = c.arg<int>(1);
+      if (mode == 0) atomicAdd(c.arg<int *>(0), 1);                                                  // s += 1
+      else if (mode == 1) atomicAdd(c.arg<int *>(0), c.I[0]);                                        // s += i
+      else c.deactivate_up(0, c.I, 1);                        // ti.deactivate(ptr, rescale_index(a, ptr, [i, j]))
+    }""", "sparse_parallel")
+    s = torch.zeros(1, dtype=torch.int32, device="cuda")
+    k.range(0, n, fields=[x], args=[s, np.int32(0), np.int32(n)])
+    k(leaf, fields=[x], args=[s, np.int32(0)])
+    assert int(s.item()) == n * n                                                                    # :27
+    s.zero_()
+    k.range(0, n * n, fields=[x], args=[s, np.int32(1), np.int32(n)])
+    k(leaf, fields=[x], args=[s, np.int32(1)])
+    NN = n * n
+    assert int(s.item()) == NN * (NN - 1) // 2                                                       # :52
+    assert np.array_equal(x.to_numpy(), np.arange(NN, dtype=np.float32))
+    for it in range(10):                                                                             # :55-78
+        k.range(0, (N * 8) * (N * 8), fields=[a], args=[s, np.int32(2), np.int32(N * 8)])
+        if it == 0:
+            assert len(ti.active_indices(pa)) == N * N and pa._num_dynamically_allocated == N * N
+        k(la, fields=[a], args=[s, np.int32(2)], gc=[pa])
+        ti.sync()
+        assert len(ti.active_indices(pa)) == 0
+    assert pa._num_dynamically_allocated == N * N      # ten cycles re-used the same N*N nodes through the GC (test_gc.py:40-52) ...
+    k.range(0, 64, fields=[a], args=[s, np.int32(2), np.int32(N * 8)])
+    assert a[0, 5] == 2.0 and a[0, 70] == 0.0           # ... zero-filled: a recycled block reads 0 outside the new writes
+    assert a.to_numpy().sum() == 2.0 * 64
