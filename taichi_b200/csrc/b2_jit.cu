@@ -176,7 +176,6 @@ static void jit_upload_table(B2JitKernel k, B2Tree t, const int32_t *field_place
     t->check_snode(pid, "jit_launch field");
     const B2SNodeHost &p = t->s[pid];
     jit_require(p.type == B2T_PLACE, TI_ERROR_INVALID_ARGUMENT, "fields are place SNodes");
-    jit_require(t->s[p.parent].type != B2T_DYNAMIC, TI_ERROR_NOT_SUPPORTED, "fields under a dynamic SNode use b2_dynamic_*");
     tab.f[i].path = t->path_to(p.parent);
     tab.f[i].off = p.offset_in_parent_cell;
     tab.f[i].bytes = p.dtype_bytes;

@@ -93,6 +93,25 @@ struct B2Access {
     }
     b2_deactivate_cell(T, P.id[q], node, b2_level_index(T, P, q, J));
   }
+  // ti.append(holder of field f, J, v) for a field under a dynamic SNode (node_dynamic.h:61-88): J addresses the parent
+  // cell (the dynamic axis is ignored), ancestors are activated, returns the index the value landed at.
+  template <typename V>
+  __device__ __forceinline__ int append(int f, const int *J, V v) const {
+    const B2JitField &F = tab->f[f];
+    const B2SNodeDev &s = T->s[F.holder];
+    int cell;
+    B2DynNode *d = (B2DynNode *)b2_walk<true>(T, F.path, J, &cell, nullptr);
+    const u32 i = atomicAdd(&d->n, 1u);
+    B2DynChunk *ch = b2_dynamic_chunk(T, F.holder, d, (int)(i / (u32)s.chunk_size));
+    if (ch) *(V *)((u8 *)ch + 16 + (long long)(i % (u32)s.chunk_size) * s.cell_size + F.off) = v;
+    return (int)i;
+  }
+  // ti.length(holder of field f, J)
+  __device__ __forceinline__ int length(int f, const int *J) const {
+    int cell;
+    const B2DynNode *d = (const B2DynNode *)b2_walk<false>(T, tab->f[f].path, J, &cell, nullptr);
+    return (int)*(const volatile u32 *)&d->n;
+  }
   // ti.is_active(holder of field f, J)
   __device__ __forceinline__ bool is_active(int f, const int *J) const {
     const B2JitField &F = tab->f[f];

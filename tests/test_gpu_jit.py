@@ -400,3 +400,65 @@ def test_sparse_parallel_activation_and_gc(ti):
     k.range(0, 64, fields=[a], args=[s, np.int32(2), np.int32(N * 8)])
     assert a[0, 5] == 2.0 and a[0, 70] == 0.0           # ... zero-filled: a recycled block reads 0 outside the new writes
     assert a.to_numpy().sum() == 2.0 * 64
+
+
+def test_particle_id_lists_per_block(ti):
+    """The reference's sparse-MPM idiom (tests/python/test_mpm_particle_list.py:9-53, bls_test_template.py:148-201):
+    pointer -> pointer -> {dense voxels, dynamic particle-id list}; a particle loop appends every particle to the list of
+    its block (ti.append from thousands of threads), a struct-for over the dynamic SNode visits the ids, and
+    `grid.deactivate_all(); build_pid()` repeated must not leak (the whole pool would be gone after ~110 rounds)."""
+    import torch
+    N, inv_dx = 10000, 128.0
+    pid, grid_m = ti.field(ti.i32), ti.field(ti.f32)
+    grid = ti.root.pointer(ti.ij, 32)
+    block = grid.pointer(ti.ij, 16)
+    voxel = block.dense(ti.ij, 8)
+    voxel.place(grid_m)
+    lists = block.dynamic(ti.k, 1024 * 1024, chunk_size=4096)
+    lists.place(pid)
+    g = torch.Generator().manual_seed(5)
+    x = (torch.rand(N, 2, generator=g) * 0.5).cuda()
+    k = ti.struct_for("""
+    __device__ void base_of(const float *x, float inv_dx, int *b) {       // floor(x * inv_dx - 0.5) + 1
+      b[0] = (int)floorf(x[0] * inv_dx - 0.5f) + 1;
+      b[1] = (int)floorf(x[1] * inv_dx - 0.5f) + 1;
+    }
+    B2_RANGE_BODY(c) {                                                     // build_pid
+      int b[2];
+      base_of(c.arg<const float *>(0) + 2 * c.i, c.arg<float>(1), b);
+      int J[B2_MAX_AXES] = {b[0] >> 3, b[1] >> 3};                         // rescale to the block
+      c.append<int>(0, J, (int)c.i);
+    }
+    B2_BODY(c) {                                                           // for I in ti.grouped(pid): p = pid[I]
+      const int p = c.read<int>(0, c.I);
+      int b[2];
+      base_of(c.arg<const float *>(0) + 2 * p, c.arg<float>(1), b);
+      unsigned long long *acc = c.arg<unsigned long long *>(2);
+      atomicAdd(acc + 0, 1ull);
+      atomicAdd(acc + 1, (unsigned long long)p);
+      atomicAdd(acc + 2, (unsigned long long)((b[0] >> 3) != c.I[0] || (b[1] >> 3) != c.I[1]));   // listed under a wrong block
+      atomicAdd(acc + 3, (unsigned long long)(c.I[2] >= c.length(0, c.I)));                       // index beyond the list
+      int V[B2_MAX_AXES] = {b[0], b[1]};
+      atomicAdd(c.ref<float>(1, V), 1.0f);                                 // grid_m[base] += 1 (voxel resolution)
+    }""", "particle_lists")
+    rounds = 150
+    for _ in range(rounds):
+        grid.deactivate_all()
+        k.range(0, N, fields=[pid, grid_m], args=[x, np.float32(inv_dx)])
+    acc = torch.zeros(4, dtype=torch.int64, device="cuda")
+    k(lists, fields=[pid, grid_m], args=[x, np.float32(inv_dx), acc])
+    assert acc.tolist() == [N, N * (N - 1) // 2, 0, 0]
+    base = np.floor(x.cpu().numpy() * np.float32(inv_dx) - np.float32(0.5)).astype(np.int64) + 1
+    blk = base >> 3
+    want_len = np.zeros((512, 512), np.int64)
+    np.add.at(want_len, (blk[:, 0], blk[:, 1]), 1)
+    occupied = np.argwhere(want_len > 0)
+    assert np.array_equal(ti.length(lists, occupied), want_len[occupied[:, 0], occupied[:, 1]])
+    assert np.array_equal(ti.active_indices(block), occupied)
+    M = grid_m.to_numpy()
+    want_m = np.zeros_like(M)
+    np.add.at(want_m, (base[:, 0], base[:, 1]), 1.0)
+    assert np.array_equal(M, want_m)
+    # no leakage: nodes and list chunks were recycled through the GC round after round
+    assert block._num_dynamically_allocated == len(occupied)
+    assert lists._num_dynamically_allocated <= 2 * len(occupied)
