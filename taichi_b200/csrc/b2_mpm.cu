@@ -880,7 +880,9 @@ void B2Mpm_t::g2p() {
   {
     static const bool no_order = getenv("B2_G2P_SORT") != nullptr;  // experiment switch: always sort
     static const int occ = getenv("B2_G2P_OCC") ? atoi(getenv("B2_G2P_OCC")) : 20;
-    if (order_valid && !no_order && occ == 16)
+    if (order_valid && !no_order && occ == 32)
+      k_mpm_g2p_bls<32, 32, true><<<rt->num_sms * 32, 32, 0, st>>>(M, gen);
+    else if (order_valid && !no_order && occ == 16)
       k_mpm_g2p_bls<64, 16, true><<<rt->num_sms * 16, 64, 0, st>>>(M, gen);
     else if (order_valid && !no_order && occ == 20)
       k_mpm_g2p_bls<64, 20, true><<<rt->num_sms * 20, 64, 0, st>>>(M, gen);

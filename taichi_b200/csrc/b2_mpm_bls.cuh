@@ -136,9 +136,10 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
     int bx, by, bz;
     mpm_unkey(M, key, bx, by, bz);
     const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
-    if (tid < (int)nchunks) S.chunk[tid] = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + tid]);
-    if (tid >= 32 && tid < 40) {
-      const int nbh = tid - 32;
+    for (int t = tid; t < (int)nchunks; t += G2P_THREADS) S.chunk[t] = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + t]);
+    constexpr int NB0 = G2P_THREADS >= 64 ? 32 : 0;  // second warp if there is one
+    if (tid >= NB0 && tid < NB0 + 8) {
+      const int nbh = tid - NB0;
       sNb[nbh] = mpm_block_ptr<false>(M, bx + (nbh >> 2), by + ((nbh >> 1) & 1), bz + (nbh & 1));
     }
     __syncthreads();
