@@ -43,6 +43,7 @@ class _Program:
         self.nodes = None
         self.tree = None
         self.fields = []
+        self.kernels = []
 
 
 _prog = _Program()
@@ -66,6 +67,9 @@ def init(arch=cuda, device_memory_GB=None, device_memory_fraction=None, device_i
 
 def reset():
     global root
+    for k in list(_prog.kernels):
+        k.destroy()
+    _prog.kernels = []
     if _prog.tree:
         lib.b2_destroy_tree(_prog.tree)
     if _prog.rt:
@@ -376,6 +380,7 @@ class StructFor:
         self.handle = lib.b2_jit_compile(_prog.rt, source.encode(), name.encode())
         L.check()
         self._rt = _prog.rt
+        _prog.kernels.append(self)  # unloaded with the runtime (ti.reset)
 
     def __call__(self, snode, fields=(), args=(), gc=()):
         """gc: pointer / dynamic SNodes whose cells the body deactivates -- their GC runs right after the launch,
