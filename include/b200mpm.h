@@ -325,6 +325,9 @@ TI_DLL_EXPORT int32_t b2_reduce(TiRuntime runtime, const void *data_dev, int64_t
 TI_DLL_EXPORT void b2_sync(TiRuntime runtime);
 TI_DLL_EXPORT int32_t b2_device_index(TiRuntime runtime);
 TI_DLL_EXPORT int64_t b2_pool_bytes_used(TiRuntime runtime); /* memory-profiler query */
+/* print_memory_profiler_info (llvm_runtime_executor.cpp:314-384) as text: per SNode the element list, the data list and
+ * the allocator counters, then the pool usage. Returns the size needed (incl. NUL); synchronises. */
+TI_DLL_EXPORT int64_t b2_memory_profiler_info(B2Tree tree, char *out, int64_t cap);
 TI_DLL_EXPORT void b2_set_pool_size(uint64_t bytes);         /* ti.init(device_memory_GB=), before ti_create_runtime */
 /* Kernel launch counter (all kernels this library launched since creation). */
 TI_DLL_EXPORT uint64_t b2_launch_count(TiRuntime runtime);

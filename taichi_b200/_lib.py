@@ -167,6 +167,7 @@ SIGNATURES = {
     "b2_mpm_grid_to_dense": (C.c_int32, [C.c_void_p, C.c_void_p]),
     "b2_mpm_stats": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "b2_mpm_invalidate_lists": (C.c_int32, [C.c_void_p]),
+    "b2_memory_profiler_info": (C.c_int64, [C.c_void_p, C.c_char_p, C.c_int64]),
     "b2_mpm_diagnostics": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "b2_mpm_diagnostics_device": (C.c_int32, [C.c_void_p, C.c_void_p]),
     "b2_slab_diagnostics": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),

@@ -1392,6 +1392,49 @@ int64_t b2_pool_bytes_used(TiRuntime rt) {
   return (int64_t)std::min(h.head, h.size);
   B2_API_END(-1)
 }
+// print_memory_profiler_info (llvm_runtime_executor.cpp:314-384): the same walk over the tree, one block of lines per
+// non-place SNode -- its element list, and for SNodes with a NodeManager the data list and the allocator counters --
+// followed by the bytes taken from the pool.  Written into `out` (size query like ti_get_last_error); synchronises.
+int64_t b2_memory_profiler_info(B2Tree t, char *out, int64_t cap) {
+  B2_API_BEGIN
+  require(t, TI_ERROR_ARGUMENT_NULL, "tree");
+  static const char *names[] = {"root", "dense", "pointer", "bitmasked", "dynamic", "place"};
+  cudaStream_t st = t->rt->stream();
+  std::string r = "[Memory Profiler]\n";
+  char line[256];
+  for (int sid = 0; sid < (int)t->s.size(); sid++) {
+    const B2SNodeHost &sn = t->s[sid];
+    if (sn.type == B2T_PLACE) continue;
+    snprintf(line, sizeof(line), "SNode S%d%s\n", sid, names[sn.type]);
+    r += line;
+    if (t->host_copy.lists[sid]) {
+      u32 hdr[4] = {0, 0, 0, 0};  // count, elem_size, log2_epc
+      B2_CUDA(cudaMemcpyAsync(hdr, t->host_copy.lists[sid], 16, cudaMemcpyDeviceToHost, st));
+      B2_CUDA(cudaStreamSynchronize(st));
+      const unsigned long long epc = 1ull << hdr[2];
+      snprintf(line, sizeof(line), "  active element list: num_elements=%u; element_size=%u B; %llu elements per chunk\n", hdr[0], hdr[1], epc);
+      r += line;
+    }
+    if (t->host_copy.mgr[sid]) {
+      int32_t a[4];
+      if (b2_alloc_stats(t, sid, a) != 0) return -1;
+      snprintf(line, sizeof(line), "  data list:           num_elements=%d; element_size=%lld B\n", a[0], (long long)t->s[sid].alloc_size);
+      r += line;
+      snprintf(line, sizeof(line), "  Allocated elements=%d; free list length=%d; recycled list length=%d\n", a[3], a[1], a[2]);
+      r += line;
+    }
+  }
+  const int64_t used = b2_pool_bytes_used(t->rt);
+  snprintf(line, sizeof(line), "Total requested dynamic memory: %lld B of a %llu B pool\n", (long long)used, (unsigned long long)t->rt->pool_size);
+  r += line;
+  if (out && cap > 0) {
+    const size_t n = std::min<size_t>((size_t)cap - 1, r.size());
+    memcpy(out, r.data(), n);
+    out[n] = 0;
+  }
+  return (int64_t)r.size() + 1;
+  B2_API_END(-1)
+}
 uint64_t b2_launch_count(TiRuntime rt) { return rt ? rt->launches : 0; }
 int32_t b2_check_runtime_error(TiRuntime rt, char *msg, uint64_t cap) {
   B2_API_BEGIN

@@ -232,6 +232,17 @@ def active_indices(snode):
     return out[np.lexsort(out.T[::-1])] if n else out
 
 
+def memory_profiler_info():
+    """ti.profiler.print_memory_profiler_info(): the report as a string."""
+    t = _materialize()
+    n = lib.b2_memory_profiler_info(t, None, 0)
+    L.check()
+    buf = C.create_string_buffer(int(n))
+    lib.b2_memory_profiler_info(t, buf, n)
+    L.check()
+    return buf.value.decode()
+
+
 def deactivate_all_snodes():
     for q, nd in enumerate(_prog.nodes):
         if nd["parent"] == 0 and nd["type"] != L.PLACE:

@@ -96,3 +96,19 @@ def test_dynamic_append(ti):  # ti.append / ti.length
     assert len(ti.active_indices(dyn)) == 300
     ptr.deactivate_all()
     assert ti.length(dyn, [3]) == 0
+
+
+def test_memory_profiler_report(ti):  # llvm_runtime_executor.cpp:314-384
+    x = ti.field(ti.f32)
+    ptr = ti.root.pointer(ti.i, 16)
+    ptr.dense(ti.i, 8).place(x)
+    x[3] = 1.0
+    x[100] = 2.0
+    assert len(ti.active_indices(ptr)) == 2          # generates the lists the report reads
+    rep = ti.memory_profiler_info()
+    assert rep.startswith("[Memory Profiler]") and "S1pointer" in rep and "S2dense" in rep
+    assert "num_elements=2" in rep and "Allocated elements=2; free list length=0; recycled list length=0" in rep
+    ptr.deactivate_all()
+    rep = ti.memory_profiler_info()
+    assert "Allocated elements=0; free list length=2; recycled list length=0" in rep
+    assert "Total requested dynamic memory:" in rep
