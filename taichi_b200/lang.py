@@ -300,6 +300,19 @@ class ScalarField:
         lib.b2_field_from_dense(_materialize(), self.place_id, arr.ctypes.data_as(C.c_void_p))
         L.check()
 
+    def to_sparse(self):
+        """Checkpoint form of a sparse field: (coords [n, ndim] of the ACTIVE cells in sorted order, values [n]).
+        Unlike to_numpy (dense image, `_kernels.py:40-60`) it keeps the active set, so `from_sparse` restores the
+        field exactly -- same active cells, same values, nothing else activated."""
+        idx = active_indices(self.parent_snode)
+        vals = self[idx] if len(idx) else np.zeros(0, self.np_dtype)
+        return idx, np.asarray(vals, self.np_dtype)
+
+    def from_sparse(self, coords, values):
+        coords = np.asarray(coords, np.int32)
+        if len(coords):
+            self[coords] = np.asarray(values, self.np_dtype)
+
     def to_torch(self, device="cuda"):
         import torch
         out = torch.zeros(self.shape, dtype=getattr(torch, self.np_dtype.name), device=device)

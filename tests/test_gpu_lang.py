@@ -112,3 +112,22 @@ def test_memory_profiler_report(ti):  # llvm_runtime_executor.cpp:314-384
     rep = ti.memory_profiler_info()
     assert "Allocated elements=0; free list length=2; recycled list length=0" in rep
     assert "Total requested dynamic memory:" in rep
+
+
+def test_sparse_checkpoint_roundtrip(ti):
+    """Sparse-field checkpoint: to_sparse / deactivate_all + GC / from_sparse restores values AND the
+    active set bit-exactly (a dense to_numpy / from_numpy round trip would activate every cell)."""
+    x = ti.field(ti.f32)
+    blk = ti.root.pointer(ti.ijk, 4).bitmasked(ti.ijk, 4).dense(ti.ijk, 2)
+    blk.place(x)
+    rng = np.random.default_rng(1)
+    pts = np.unique(rng.integers(0, 32, size=(500, 3)), axis=0)
+    x[pts] = rng.random(len(pts)).astype(np.float32)
+    img0, act0 = x.to_numpy(), ti.active_indices(blk).copy()
+    coords, vals = x.to_sparse()
+    assert len(coords) == len(act0) and len(coords) % 8 == 0          # whole dense(2^3) cells are active
+    blk.parent().parent().deactivate_all()
+    assert len(ti.active_indices(blk)) == 0 and x.to_numpy().sum() == 0
+    x.from_sparse(coords, vals)
+    assert np.array_equal(ti.active_indices(blk), act0)
+    assert np.array_equal(x.to_numpy(), img0)
