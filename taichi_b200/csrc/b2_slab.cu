@@ -211,9 +211,6 @@ int32_t b2_slab_substep(B2Slab s, int32_t nsteps) {
   B2_API_END(-1)
 }
 
-// Shrinks the bytes put on the wire to 2x the record counts of the last substep (+256 records,
-// never above the capacity); neighbours learn each other's sizes through one tiny exchange.
-// Synchronises.  An overflow after tuning raises the device-side error flag (bin overflow).
 // Whole-domain particle diagnostics: every slab reduces its own particles (k_mpm_diag), then
 // ncclAllReduce over the slabs -- sums for out[0..5], maxima (as ordered bit patterns) for out[6..7] -- on the
 // same stream, one group.  Every rank gets the result.  Synchronises.
@@ -234,6 +231,9 @@ int32_t b2_slab_diagnostics(B2Slab s, double *out8) {
   return 0;
   B2_API_END(-1)
 }
+// Shrinks the bytes put on the wire to 2x the record counts of the last substep (+256 records,
+// never above the capacity); neighbours learn each other's sizes through one tiny exchange.
+// Synchronises.  An overflow after tuning raises the device-side error flag (bin overflow).
 int32_t b2_slab_tune(B2Slab s) {
   B2_API_BEGIN
   require(s != nullptr, TI_ERROR_ARGUMENT_NULL, "slab");
