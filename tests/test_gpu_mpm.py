@@ -462,3 +462,32 @@ def test_full_size_c3_properties(rt):
     assert np.isin(touched_blocks(xr), keys_of(s.active_blocks())).all()
     lib.b2_jit_destroy(k)
     s.destroy()
+
+
+def test_out_of_domain_particles_raise_the_device_error(rt):
+    """The reference asserts in debug mode when an index leaves the field (`taichi_assert_format`, runtime.cpp:727-741);
+    here a particle whose stencil leaves the grid, or a NaN position, sets the device-side error flag (and is clamped
+    into the grid, never written out of bounds).  Reading the flag clears it."""
+    import taichi_b200 as tb
+    lib = tb._lib.lib
+    buf = C.create_string_buffer(256)
+    assert lib.b2_check_runtime_error(rt.handle, buf, 256) == 0, buf.value
+    n_grid, N = 64, 1000
+    x0, v0, C0, J0 = cloud(31, N)
+    for bad in (np.array([1.5, 0.5, 0.5], np.float32), np.array([0.5, -0.2, 0.5], np.float32),
+                np.array([0.5, 0.5, np.nan], np.float32)):
+        s = tb.Mpm3D(rt, n_grid, N, 2e-4, layout="pointer_bitmasked")
+        x = x0.copy()
+        x[17] = bad
+        s.set_particles(x, v0, C0, J0)
+        with pytest.raises(tb._lib.B2RuntimeError, match=r"assertion failed \[arg 17\]"):
+            rt.wait()                                                    # ti_wait surfaces it (llvm_runtime_executor.cpp:272-312)
+        assert lib.b2_check_runtime_error(rt.handle, buf, 256) == 0      # cleared by the read
+        assert s.stats()["particles"] == N                               # clamped into a border block, not dropped
+        s.destroy()
+    s = tb.Mpm3D(rt, n_grid, N, 2e-4, layout="pointer_bitmasked")
+    s.set_particles(x0, v0, C0, J0)
+    s.substep(2)
+    rt.wait()
+    assert lib.b2_check_runtime_error(rt.handle, buf, 256) == 0, buf.value  # a valid cloud raises nothing
+    s.destroy()
