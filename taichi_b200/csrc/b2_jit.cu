@@ -18,7 +18,7 @@
 
 #include "b2_host.h"
 #include "b2_jit.cuh"
-#include "build/b2_embed.h"  // b2_src_internal / b2_src_jit: the two device headers as text
+#include "build/b2_embed.h"  // b2_src_internal / b2_src_jit / b2_src_svd: the device headers as text
 
 namespace {
 typedef struct _nvrtcProgram *nvrtcProgram;
@@ -77,15 +77,15 @@ static void jit_build(const char *source, const char *name, std::vector<char> *c
   std::string src;
   if (strstr(source, "B2_RANGE_BODY")) src += "#define B2_JIT_HAS_RANGE 1\n";
   if (strstr(source, "B2_BODY")) src += "#define B2_JIT_HAS_BODY 1\n";  // ("B2_RANGE_BODY" does not contain it)
-  src += "#include \"b2_internal.cuh\"\n#include \"b2_jit.cuh\"\n#line 1 \"";
+  src += "#include \"b2_internal.cuh\"\n#include \"b2_svd.cuh\"\n#include \"b2_jit.cuh\"\n#line 1 \"";
   src += (name && *name) ? name : "b2_body";
   src += "\"\n";
   src += source;
   src += "\n";
-  const char *headers[2] = {b2_src_internal, b2_src_jit};
-  const char *hnames[2] = {"b2_internal.cuh", "b2_jit.cuh"};
+  const char *headers[3] = {b2_src_internal, b2_src_jit, b2_src_svd};
+  const char *hnames[3] = {"b2_internal.cuh", "b2_jit.cuh", "b2_svd.cuh"};
   nvrtcProgram prog = nullptr;
-  int rc = N.CreateProgram(&prog, src.c_str(), "b2_jit_kernel.cu", 2, headers, hnames);
+  int rc = N.CreateProgram(&prog, src.c_str(), "b2_jit_kernel.cu", 3, headers, hnames);
   jit_require(rc == 0 && prog != nullptr, TI_ERROR_INVALID_STATE, "nvrtcCreateProgram failed");
   const char *opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "-lineinfo"};
   rc = N.CompileProgram(prog, 3, opts);

@@ -462,3 +462,140 @@ def test_particle_id_lists_per_block(ti):
     # no leakage: nodes and list chunks were recycled through the GC round after round
     assert block._num_dynamically_allocated == len(occupied)
     assert lists._num_dynamically_allocated <= 2 * len(occupied)
+
+
+@pytest.mark.gpu
+def test_svd3_and_svd2_in_range_for(ti):
+    """ti.svd inside a kernel body (test_svd.py:27-63) through b2_svd.cuh: U^T U = V^T V = I, U sig V^T = A at the
+    reference's f32 tolerance 1e-5, singular values against numpy.linalg, det U = det V = +1."""
+    import torch
+    N = 50000
+    rng = np.random.default_rng(21)
+    A3 = rng.standard_normal((N, 3, 3)).astype(np.float32)
+    A3[0] = [[1, 1, 3], [9, -3, 2], [-3, 4, 2]]
+    A3[1] = 0
+    A3[2] = np.eye(3)
+    A3[3] = np.outer([1, 2, 3], [3, 2, 1])
+    A2 = rng.standard_normal((N, 2, 2)).astype(np.float32)
+    A2[0] = [[1, 1], [2, 3]]
+    dummy = ti.field(ti.f32)
+    ti.root.dense(ti.i, 4).place(dummy)
+    k = ti.struct_for("""
+    B2_RANGE_BODY(c) {
+      const int dim = c.arg<int>(2);
+      if (dim == 3) {
+        const float *A = c.arg<const float *>(0) + 9 * c.i; float *o = c.arg<float *>(1) + 21 * c.i;
+        float U[9], s[3], V[9];
+        b2_svd3(A, U, s, V);
+        for (int q = 0; q < 9; q++) { o[q] = U[q]; o[12 + q] = V[q]; }
+        for (int q = 0; q < 3; q++) o[9 + q] = s[q];
+      } else {
+        const float *A = c.arg<const float *>(0) + 4 * c.i; float *o = c.arg<float *>(1) + 10 * c.i;
+        float U[4], s[2], V[4];
+        b2_svd2(A, U, s, V);
+        for (int q = 0; q < 4; q++) { o[q] = U[q]; o[6 + q] = V[q]; }
+        for (int q = 0; q < 2; q++) o[4 + q] = s[q];
+      }
+    }""", "svd")
+    for n, A in ((3, A3), (2, A2)):
+        dA = torch.from_numpy(A).cuda()
+        out = torch.zeros(N, n * n * 2 + n, device="cuda")
+        k.range(0, N, fields=[dummy], args=[dA, out, np.int32(n)])
+        o = out.cpu().numpy()
+        U, s, V = o[:, :n * n].reshape(N, n, n), o[:, n * n:n * n + n], o[:, n * n + n:].reshape(N, n, n)
+        sc = np.maximum(1.0, np.abs(A).max(axis=(1, 2)))
+        rec = np.einsum("nij,nj,nkj->nik", U, s, V)
+        assert (np.abs(rec - A).max(axis=(1, 2)) / sc).max() < 1e-5
+        eye = np.eye(n, dtype=np.float32)
+        assert np.abs(np.einsum("nji,njk->nik", U, U) - eye).max() < 1e-5
+        assert np.abs(np.einsum("nji,njk->nik", V, V) - eye).max() < 1e-5
+        assert np.abs(np.linalg.det(U.astype(np.float64)) - 1).max() < 1e-4
+        assert np.abs(np.linalg.det(V.astype(np.float64)) - 1).max() < 1e-4
+        want = np.linalg.svd(A.astype(np.float64), compute_uv=False)
+        assert (np.abs(-np.sort(-np.abs(s), axis=1) - want).max(axis=1) / sc).max() < 1e-5
+        assert np.all(s[:, :-1] >= -1e-5 * sc[:, None])
+
+
+@pytest.mark.gpu
+def test_3d_constitutive_model_range_for(ti):
+    """The F/SVD material update of mpm128.py:36-63 (hardening, snow plasticity clamp, liquid reset, fixed-corotated
+    stress) written for 3-D matrices in a user range-for, Jp in a field; against a float64 NumPy evaluation of the
+    same formulas on numpy.linalg.svd (the update is invariant to the SVD's ordering and sign conventions)."""
+    import torch
+    N = 30000
+    rng = np.random.default_rng(33)
+    dt, E, nu = 1e-4, 1e3, 0.2
+    mu0, la0 = E / (2 * (1 + nu)), E * nu / ((1 + nu) * (1 - 2 * nu))
+    q = np.linalg.qr(rng.standard_normal((N, 3, 3)))[0]
+    q *= np.sign(np.linalg.det(q))[:, None, None]
+    F0 = (q @ (np.eye(3) + 0.04 * rng.standard_normal((N, 3, 3)))).astype(np.float32)
+    C0 = (20.0 * rng.standard_normal((N, 3, 3))).astype(np.float32)
+    Jp0 = (1 + 0.05 * rng.standard_normal(N)).astype(np.float32)
+    mat = rng.integers(0, 3, N).astype(np.int32)
+    Jp = ti.field(ti.f32)
+    ti.root.dense(ti.i, 32768).place(Jp)
+    Jp.from_numpy(np.concatenate([Jp0, np.zeros(32768 - N, np.float32)]))
+    k = ti.struct_for("""
+    B2_RANGE_BODY(c) {
+      const int p = c.i;
+      float *Fp = c.arg<float *>(0) + 9 * p; const float *C = c.arg<const float *>(1) + 9 * p;
+      const int material = c.arg<const int *>(2)[p]; float *out = c.arg<float *>(3) + 9 * p;
+      const float dt = c.arg<float>(4), mu_0 = c.arg<float>(5), lambda_0 = c.arg<float>(6);
+      float F[9];
+      for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {      // F = (I + dt C) F
+        float a = 0.f;
+        for (int m = 0; m < 3; m++) a += ((i == m ? 1.f : 0.f) + dt * C[i * 3 + m]) * Fp[m * 3 + j];
+        F[i * 3 + j] = a;
+      }
+      int I[B2_MAX_AXES] = {p};
+      float jp = c.read<float>(0, I);
+      float h = fmaxf(0.1f, fminf(5.f, expf(10.f * (1.f - jp))));
+      if (material == 1) h = 0.3f;
+      float mu = mu_0 * h; const float la = lambda_0 * h;
+      if (material == 0) mu = 0.f;
+      float U[9], sig[3], V[9];
+      b2_svd3(F, U, sig, V);
+      float J = 1.f;
+      for (int d = 0; d < 3; d++) {
+        float ns = sig[d];
+        if (material == 2) ns = fminf(fmaxf(sig[d], 1.f - 2.5e-2f), 1.f + 4.5e-3f);
+        jp *= sig[d] / ns; sig[d] = ns; J *= ns;
+      }
+      c.write<float>(0, I, jp);
+      float R[9];
+      for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+        R[i * 3 + j] = U[i * 3] * V[j * 3] + U[i * 3 + 1] * V[j * 3 + 1] + U[i * 3 + 2] * V[j * 3 + 2];
+        if (material == 0) F[i * 3 + j] = i == j ? cbrtf(J) : 0.f;
+        else if (material == 2)
+          F[i * 3 + j] = U[i * 3] * sig[0] * V[j * 3] + U[i * 3 + 1] * sig[1] * V[j * 3 + 1] + U[i * 3 + 2] * sig[2] * V[j * 3 + 2];
+      }
+      for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {      // 2 mu (F - U V^T) F^T + la J (J - 1) I
+        float a = 0.f;
+        for (int m = 0; m < 3; m++) a += (F[i * 3 + m] - R[i * 3 + m]) * F[j * 3 + m];
+        out[i * 3 + j] = 2.f * mu * a + (i == j ? la * J * (J - 1.f) : 0.f);
+      }
+      for (int q = 0; q < 9; q++) Fp[q] = F[q];
+    }""", "material3d")
+    dF, dC, dm = torch.from_numpy(F0).cuda(), torch.from_numpy(C0).cuda(), torch.from_numpy(mat).cuda()
+    dS = torch.zeros(N, 9, device="cuda")
+    k.range(0, N, fields=[Jp], args=[dF, dC, dm, dS, np.float32(dt), np.float32(mu0), np.float32(la0)])
+    gotF, gotS, gotJp = dF.cpu().numpy().astype(np.float64), dS.cpu().numpy().reshape(N, 3, 3).astype(np.float64), Jp.to_numpy()[:N]
+    # float64 evaluation of the same formulas
+    F = (np.eye(3) + dt * C0.astype(np.float64)) @ F0.astype(np.float64)
+    h = np.clip(np.exp(10 * (1 - Jp0.astype(np.float64))), 0.1, 5)
+    h[mat == 1] = 0.3
+    mu, la = mu0 * h, la0 * h
+    mu[mat == 0] = 0
+    U, sig, Vt = np.linalg.svd(F)
+    ns = np.where((mat == 2)[:, None], np.clip(sig, 1 - 2.5e-2, 1 + 4.5e-3), sig)
+    wantJp = Jp0 * np.prod(sig / ns, axis=1)
+    J = np.prod(ns, axis=1)
+    R = U @ Vt
+    Fn = F.copy()
+    Fn[mat == 0] = np.eye(3) * np.cbrt(J[mat == 0])[:, None, None]
+    Fn[mat == 2] = (U * ns[:, None, :] @ Vt)[mat == 2]
+    wantS = 2 * mu[:, None, None] * ((Fn - R) @ np.swapaxes(Fn, 1, 2)) + np.eye(3) * (la * J * (J - 1))[:, None, None]
+    assert np.allclose(gotJp, wantJp, rtol=2e-5, atol=1e-6)
+    assert np.abs(gotF - Fn).max() < 5e-6
+    assert np.abs(gotS - wantS).max() < 2e-5 * 2 * mu0 * 5 + 1e-3      # |dS| <= 2 mu |dF| |F| at eps-level |dF|
+    assert (mat == 2).sum() > 0 and np.abs(ns - sig)[mat == 2].max() > 1e-3   # the clamp was exercised
