@@ -599,3 +599,210 @@ def test_3d_constitutive_model_range_for(ti):
     assert np.abs(gotF - Fn).max() < 5e-6
     assert np.abs(gotS - wantS).max() < 2e-5 * 2 * mu0 * 5 + 1e-3      # |dS| <= 2 mu |dF| |F| at eps-level |dF|
     assert (mat == 2).sum() > 0 and np.abs(ns - sig)[mat == 2].max() > 1e-3   # the clamp was exercised
+
+
+MPM3D_MATERIAL_SRC = """
+__device__ void weights(const float *x, float inv_dx, int *base, float (*w)[3], float *fx) {
+  for (int d = 0; d < 3; d++) {
+    const float X = x[d] * inv_dx;
+    base[d] = (int)(X - 0.5f);
+    fx[d] = X - (float)base[d];
+    w[0][d] = 0.5f * (1.5f - fx[d]) * (1.5f - fx[d]);
+    w[1][d] = 0.75f - (fx[d] - 1.0f) * (fx[d] - 1.0f);
+    w[2][d] = 0.5f * (fx[d] - 0.5f) * (fx[d] - 0.5f);
+  }
+}
+struct Par { float dt, inv_dx, p_vol, p_mass, mu_0, lambda_0, gravity; int n_grid, bound, phase; };
+B2_RANGE_BODY(c) {
+  const int p = c.i;
+  float *x = c.arg<float *>(0) + 3 * p, *v = c.arg<float *>(1) + 3 * p, *C = c.arg<float *>(2) + 9 * p;
+  float *Fp = c.arg<float *>(3) + 9 * p, *Jp = c.arg<float *>(4) + p;
+  const int material = c.arg<const int *>(5)[p];
+  const Par P = *c.arg<const Par *>(6);
+  const float dx = 1.0f / P.inv_dx;
+  int base[3]; float w[3][3], fx[3];
+  weights(x, P.inv_dx, base, w, fx);
+  if (P.phase == 0) {                                  // ---- P2G (mpm128.py:31-71 in 3-D)
+    float F[9];
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+      float a = 0.f;
+      for (int m = 0; m < 3; m++) a += ((i == m ? 1.f : 0.f) + P.dt * C[i * 3 + m]) * Fp[m * 3 + j];
+      F[i * 3 + j] = a;
+    }
+    float jp = *Jp;
+    float h = fmaxf(0.1f, fminf(5.f, expf(10.f * (1.f - jp))));
+    if (material == 1) h = 0.3f;
+    float mu = P.mu_0 * h; const float la = P.lambda_0 * h;
+    if (material == 0) mu = 0.f;
+    float U[9], sig[3], V[9];
+    b2_svd3(F, U, sig, V);
+    float J = 1.f;
+    for (int d = 0; d < 3; d++) {
+      float ns = sig[d];
+      if (material == 2) ns = fminf(fmaxf(sig[d], 1.f - 2.5e-2f), 1.f + 4.5e-3f);
+      jp *= sig[d] / ns; sig[d] = ns; J *= ns;
+    }
+    *Jp = jp;
+    float R[9], A[9];
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+      R[i * 3 + j] = U[i * 3] * V[j * 3] + U[i * 3 + 1] * V[j * 3 + 1] + U[i * 3 + 2] * V[j * 3 + 2];
+      if (material == 0) F[i * 3 + j] = i == j ? cbrtf(J) : 0.f;
+      else if (material == 2)
+        F[i * 3 + j] = U[i * 3] * sig[0] * V[j * 3] + U[i * 3 + 1] * sig[1] * V[j * 3 + 1] + U[i * 3 + 2] * sig[2] * V[j * 3 + 2];
+    }
+    const float k = -P.dt * P.p_vol * 4.f * P.inv_dx * P.inv_dx;
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+      float a = 0.f;
+      for (int m = 0; m < 3; m++) a += (F[i * 3 + m] - R[i * 3 + m]) * F[j * 3 + m];
+      A[i * 3 + j] = k * (2.f * mu * a + (i == j ? la * J * (J - 1.f) : 0.f)) + P.p_mass * C[i * 3 + j];
+    }
+    for (int q = 0; q < 9; q++) Fp[q] = F[q];
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) for (int kk = 0; kk < 3; kk++) {
+      const float dpos[3] = {((float)i - fx[0]) * dx, ((float)j - fx[1]) * dx, ((float)kk - fx[2]) * dx};
+      const float wt = w[i][0] * w[j][1] * w[kk][2];
+      int I[B2_MAX_AXES] = {base[0] + i, base[1] + j, base[2] + kk};
+      for (int d = 0; d < 3; d++)
+        atomicAdd(c.ref<float>(d, I), wt * (P.p_mass * v[d] + A[d * 3] * dpos[0] + A[d * 3 + 1] * dpos[1] + A[d * 3 + 2] * dpos[2]));
+      atomicAdd(c.ref<float>(3, I), wt * P.p_mass);
+    }
+  } else {                                             // ---- G2P (mpm128.py:88-102 in 3-D)
+    float nv[3] = {0.f, 0.f, 0.f}, nC[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) for (int kk = 0; kk < 3; kk++) {
+      const float dpos[3] = {(float)i - fx[0], (float)j - fx[1], (float)kk - fx[2]};
+      const float wt = w[i][0] * w[j][1] * w[kk][2];
+      int I[B2_MAX_AXES] = {base[0] + i, base[1] + j, base[2] + kk};
+      for (int d = 0; d < 3; d++) {
+        const float g = c.read<float>(d, I);
+        nv[d] += wt * g;
+        for (int e = 0; e < 3; e++) nC[d * 3 + e] += 4.f * P.inv_dx * wt * g * dpos[e];
+      }
+    }
+    for (int d = 0; d < 3; d++) { v[d] = nv[d]; x[d] += P.dt * nv[d]; }
+    for (int q = 0; q < 9; q++) C[q] = nC[q];
+  }
+}
+B2_BODY(c) {                                           // ---- grid op (mpm128.py:72-87 in 3-D)
+  const Par P = *c.arg<const Par *>(6);
+  const float m = c.read<float>(3, c.I);
+  if (m > 0.f) {
+    float v[3];
+    for (int d = 0; d < 3; d++) v[d] = c.read<float>(d, c.I) / m;
+    v[1] -= P.dt * P.gravity;
+    for (int d = 0; d < 3; d++) {
+      if (c.I[d] < P.bound && v[d] < 0.f) v[d] = 0.f;
+      if (c.I[d] > P.n_grid - P.bound && v[d] > 0.f) v[d] = 0.f;
+      c.write<float>(d, c.I, v[d]);
+    }
+  }
+}
+"""
+
+
+def _np_mpm3d_material_substep(S, par):
+    """float64 restatement of MPM3D_MATERIAL_SRC on numpy.linalg.svd."""
+    x, v, C, F, Jp, mat = S["x"], S["v"], S["C"], S["F"], S["Jp"], S["mat"]
+    n, dt, inv_dx = par["n_grid"], par["dt"], float(par["n_grid"])
+    dx = 1.0 / inv_dx
+    X = x * inv_dx
+    base = (X - 0.5).astype(np.int64)
+    fx = X - base
+    w = [0.5 * (1.5 - fx) ** 2, 0.75 - (fx - 1.0) ** 2, 0.5 * (fx - 0.5) ** 2]
+    F = (np.eye(3) + dt * C) @ F
+    h = np.clip(np.exp(10 * (1 - Jp)), 0.1, 5)
+    h[mat == 1] = 0.3
+    mu, la = par["mu_0"] * h, par["lambda_0"] * h
+    mu[mat == 0] = 0
+    U, sig, Vt = np.linalg.svd(F)
+    ns = np.where((mat == 2)[:, None], np.clip(sig, 1 - 2.5e-2, 1 + 4.5e-3), sig)
+    Jp = Jp * np.prod(sig / ns, axis=1)
+    J = np.prod(ns, axis=1)
+    R = U @ Vt
+    F[mat == 0] = np.eye(3) * np.cbrt(J[mat == 0])[:, None, None]
+    F[mat == 2] = (U * ns[:, None, :] @ Vt)[mat == 2]
+    stress = 2 * mu[:, None, None] * ((F - R) @ np.swapaxes(F, 1, 2)) + np.eye(3) * (la * J * (J - 1))[:, None, None]
+    A = (-dt * par["p_vol"] * 4 * inv_dx * inv_dx) * stress + par["p_mass"] * C
+    gv, gm = np.zeros((n, n, n, 3)), np.zeros((n, n, n))
+    offs = [(i, j, k) for i in range(3) for j in range(3) for k in range(3)]
+    for (i, j, k) in offs:
+        o = np.array([i, j, k], np.float64)
+        wt = w[i][:, 0] * w[j][:, 1] * w[k][:, 2]
+        dpos = (o - fx) * dx
+        idx = (base[:, 0] + i, base[:, 1] + j, base[:, 2] + k)
+        np.add.at(gv, idx, wt[:, None] * (par["p_mass"] * v + np.einsum("nij,nj->ni", A, dpos)))
+        np.add.at(gm, idx, wt * par["p_mass"])
+    act = gm > 0
+    gv[act] /= gm[act][:, None]
+    gv[act, 1] -= dt * par["gravity"]
+    I = np.indices((n, n, n)).transpose(1, 2, 3, 0)
+    gv[act[..., None] & (I < par["bound"]) & (gv < 0)] = 0
+    gv[act[..., None] & (I > n - par["bound"]) & (gv > 0)] = 0
+    nv, nC = np.zeros_like(v), np.zeros_like(C)
+    for (i, j, k) in offs:
+        o = np.array([i, j, k], np.float64)
+        wt = w[i][:, 0] * w[j][:, 1] * w[k][:, 2]
+        g = gv[base[:, 0] + i, base[:, 1] + j, base[:, 2] + k]
+        nv += wt[:, None] * g
+        nC += 4 * inv_dx * wt[:, None, None] * np.einsum("ni,nj->nij", g, o - fx)
+    S.update(x=x + dt * nv, v=nv, C=nC, F=F, Jp=Jp)
+    return gm
+
+
+@pytest.mark.gpu
+def test_3d_mpm_with_materials_on_sparse_grid(ti):
+    """the full mpm128 constitutive model (liquid / jelly / snow, ti.svd) carried to 3-D and written by
+    the USER as run-time bodies over the sparse grid pointer -> bitmasked -> dense(4^3): P2G range-for with activating
+    atomic adds, grid struct-for, G2P range-for, `deactivate_all` between substeps.  State after 6 substeps against the
+    float64 NumPy restatement; grid mass per substep; active blocks = touched blocks."""
+    import ctypes
+    import torch
+    from test_gpu_mpm import expected_blocks
+    n_grid, N, steps = 64, 20000, 6
+    E, nu = 1e3, 0.2
+    dx = 1.0 / n_grid
+    par = dict(dt=1e-4, n_grid=n_grid, p_vol=(dx * 0.5) ** 3, p_mass=(dx * 0.5) ** 3 * 1.0, gravity=9.8, bound=3,
+               mu_0=E / (2 * (1 + nu)), lambda_0=E * nu / ((1 + nu) * (1 - 2 * nu)))
+    rng = np.random.default_rng(17)
+    x0 = (rng.random((N, 3)) * 0.3 + 0.3).astype(np.float32)
+    v0 = (rng.standard_normal((N, 3)) * 0.3).astype(np.float32)
+    C0 = (rng.standard_normal((N, 3, 3)) * 2.0).astype(np.float32)
+    q = np.linalg.qr(rng.standard_normal((N, 3, 3)))[0]
+    q *= np.sign(np.linalg.det(q))[:, None, None]
+    F0 = (q @ (np.eye(3) + 0.02 * rng.standard_normal((N, 3, 3)))).astype(np.float32)
+    Jp0 = (1 + 0.02 * rng.standard_normal(N)).astype(np.float32)
+    mat = rng.integers(0, 3, N).astype(np.int32)
+    g = [ti.field(ti.f32) for _ in range(4)]                               # grid_v.x/y/z, grid_m
+    top = ti.root.pointer(ti.ijk, 4)
+    blk = top.bitmasked(ti.ijk, 4).dense(ti.ijk, 4)
+    blk.place(*g)
+
+    class Par(ctypes.Structure):
+        _fields_ = [(k, ctypes.c_float) for k in ("dt", "inv_dx", "p_vol", "p_mass", "mu_0", "lambda_0", "gravity")] + \
+                   [(k, ctypes.c_int32) for k in ("n_grid", "bound", "phase")]
+
+    def par_dev(phase):
+        pb = Par(par["dt"], float(n_grid), par["p_vol"], par["p_mass"], par["mu_0"], par["lambda_0"], par["gravity"],
+                 n_grid, par["bound"], phase)
+        return torch.frombuffer(bytearray(bytes(pb)), dtype=torch.uint8).cuda()
+    P0, P1 = par_dev(0), par_dev(1)
+    k = ti.struct_for(MPM3D_MATERIAL_SRC, "mpm3d_material")
+    d = [torch.from_numpy(a.copy()).cuda() for a in (x0, v0, C0, F0, Jp0, mat)]
+    S = dict(x=x0.astype(np.float64), v=v0.astype(np.float64), C=C0.astype(np.float64), F=F0.astype(np.float64),
+             Jp=Jp0.astype(np.float64), mat=mat)
+    for s in range(steps):
+        x_before = d[0].cpu().numpy()
+        top.deactivate_all()
+        k.range(0, N, fields=g, args=d + [P0])
+        got_m = g[3].to_numpy()
+        assert np.array_equal(ti.active_indices(blk.parent()), expected_blocks(x_before, n_grid, halo=False))
+        k(blk, fields=g, args=d + [P0])
+        k.range(0, N, fields=g, args=d + [P1])
+        want_m = _np_mpm3d_material_substep(S, par)
+        assert np.allclose(got_m, want_m, rtol=2e-4, atol=par["p_mass"] * 1e-4), s
+        assert abs(got_m.sum() - N * par["p_mass"]) < 1e-5 * N * par["p_mass"]
+    got = [a.cpu().numpy().astype(np.float64) for a in d[:5]]
+    assert np.abs(got[0] - S["x"]).max() < 2e-6
+    assert np.abs(got[1] - S["v"]).max() < 2e-3 * max(1.0, np.abs(S["v"]).max())
+    assert np.abs(got[2].reshape(N, 3, 3) - S["C"]).max() < 2e-3 * np.abs(S["C"]).max()
+    assert np.abs(got[3].reshape(N, 3, 3) - S["F"]).max() < 2e-5
+    assert np.allclose(got[4], S["Jp"], rtol=1e-4)
+    assert np.abs(S["v"] - v0).max() > 0.05                                  # the substeps did something
