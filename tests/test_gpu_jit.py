@@ -806,3 +806,112 @@ def test_3d_mpm_with_materials_on_sparse_grid(ti):
     assert np.abs(got[3].reshape(N, 3, 3) - S["F"]).max() < 2e-5
     assert np.allclose(got[4], S["Jp"], rtol=1e-4)
     assert np.abs(S["v"] - v0).max() > 0.05                                  # the substeps did something
+
+
+STENCIL_SRC = """
+B2_RANGE_BODY(c) {                                     // populate: for I in ti.grouped(ti.ndrange(*ndrange)): x[I] = sum I[i] ** (i + 1)
+  const int dim = c.arg<int>(2), lo0 = c.arg<int>(4), lo1 = c.arg<int>(5), lo2 = c.arg<int>(6);
+  const int n0 = c.arg<int>(7), n1 = c.arg<int>(8), n2 = c.arg<int>(9);
+  int r = (int)c.i;
+  int I[B2_MAX_AXES] = {0};
+  if (dim == 3) { I[2] = lo2 + r % n2; r /= n2; }
+  if (dim >= 2) { I[1] = lo1 + r % n1; r /= n1; }
+  I[0] = lo0 + r;
+  (void)n0;
+  c.write<int>(0, I, I[0] + (dim >= 2 ? I[1] * I[1] : 0) + (dim == 3 ? I[2] * I[2] * I[2] : 0));
+}
+B2_BODY(c) {                                           // apply: for I in ti.grouped(x)
+  const int *st = c.arg<const int *>(0); const int ns = c.arg<int>(1), dim = c.arg<int>(2), scatter = c.arg<int>(3);
+  int s = 0;
+  const int xv = scatter ? c.read<int>(0, c.I) : 0;
+  for (int q = 0; q < ns; q++) {
+    int J[B2_MAX_AXES] = {0};
+    for (int d = 0; d < dim; d++) J[d] = c.I[d] + st[q * 3 + d];
+    if (scatter) atomicAdd(c.ref<int>(1, J), xv);      // y[I + offset] += x[I]   (activates)
+    else s += c.read<int>(0, J);                       // s += x[I + offset]      (never activates)
+  }
+  if (!scatter) c.write<int>(1, c.I, s);
+}
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dim,N,bs,stencil,scatter", [
+    (1, 128, 32, [(0,)], False), (1, 128, 32, [(-1,), (0,)], False),
+    (2, 128, 16, [(0, 0), (0, -1), (0, 1), (1, 0)], False), (2, 128, (4, 16), [(0, 0), (0, -1), (0, 1), (1, 0)], False),
+    (3, 128, (4, 8, 16), [(-1, -1, -1), (2, 0, 1)], False),
+    (1, 128, 32, [(0,)], True), (1, 128, 32, [(1,), (0,)], True),
+    (2, 128, 16, [(0, 0), (0, -1), (0, 1), (1, 0)], True), (3, 128, (4, 8, 16), [(-1, -1, -1), (2, 0, 1)], True)])
+def test_stencil_gather_scatter_over_pointer_blocks(ti, dim, N, bs, stencil, scatter):
+    """The stencil cases of tests/python/test_bls.py:60-121 / bls_test_template.py:8-96 (1-D / 2-D / 3-D, non-square
+    blocks (4, 16) and (4, 8, 16), gather and scatter, int32 => exact) as struct-for bodies over pointer -> dense(bs);
+    where the reference compares block_local against plain, this compares with the NumPy answer.  (3-D runs at N = 128:
+    with the reference's N = 64 the populated range [2 bs, N - 2 bs) is empty along the 16-wide axis.)"""
+    import torch
+    bs = [bs] * dim if isinstance(bs, int) else list(bs)
+    axes = [ti.i, ti.ij, ti.ijk][dim - 1]
+    grid = [N // b for b in bs]
+    x, y = ti.field(ti.i32), ti.field(ti.i32)
+    if scatter:
+        block = ti.root.pointer(axes, grid)
+        xs, ys = block.dense(axes, bs), block.dense(axes, bs)
+    else:
+        xs, ys = ti.root.pointer(axes, grid).dense(axes, bs), ti.root.pointer(axes, grid).dense(axes, bs)
+    xs.place(x)
+    ys.place(y)
+    lo = [2 * b for b in bs] + [0] * (3 - dim)
+    cnt = [N - 4 * b for b in bs] + [1] * (3 - dim)
+    st = np.zeros((len(stencil), 3), np.int32)
+    st[:, :dim] = np.array(stencil, np.int32)
+    dst = torch.from_numpy(st).cuda()
+    args = [dst, np.int32(len(stencil)), np.int32(dim), np.int32(int(scatter))] + [np.int32(v) for v in lo + cnt]
+    k = ti.struct_for(STENCIL_SRC, "stencil")
+    k.range(0, int(np.prod(cnt)), fields=[x, y], args=args)
+    I = np.indices((N,) * dim)
+    inside = np.ones((N,) * dim, bool)
+    for d in range(dim):
+        inside &= (I[d] >= lo[d]) & (I[d] < lo[d] + cnt[d])
+    X = np.where(inside, sum(I[d].astype(np.int64) ** (d + 1) for d in range(dim)), 0).astype(np.int32)
+    assert np.array_equal(x.to_numpy(), X)
+    k(xs, fields=[x, y], args=args)
+    want = np.zeros_like(X)
+    for off in stencil:
+        # gather: y[I] = sum x[I + off];  scatter: y[I + off] += x[I]
+        want += np.roll(X, tuple(-o for o in off) if not scatter else tuple(off), axis=tuple(range(dim)))
+    if not scatter:
+        want = np.where(inside, want, 0)                                  # only cells of x's active blocks are visited
+    assert np.array_equal(y.to_numpy(), want)
+    assert np.array_equal(x.to_numpy(), X)                                # reads activated nothing in x
+    nblk = int(np.prod([c // b for c, b in zip(cnt, bs)]))
+    got_blk = len(ti.active_indices(xs.parent()))
+    assert got_blk >= nblk if scatter else got_blk == nblk                # a scatter may open neighbouring blocks
+
+
+@pytest.mark.gpu
+def test_stencil_multiple_inputs(ti):
+    """test_bls.py:124-157: w[i, j] = x[i, j-2] + y[i+2, j-1] + y[i-1, j] + z[i-1, j] + z[i+1, j] over x's active cells."""
+    N, bs = 128, 8
+    f = [ti.field(ti.i32) for _ in range(4)]
+    blk = ti.root.pointer(ti.ij, N // bs).dense(ti.ij, bs)
+    blk.place(*f)
+    k = ti.struct_for("""
+    B2_RANGE_BODY(c) {
+      const int n = c.arg<int>(0), bs = c.arg<int>(1);
+      const int i = bs + (int)c.i / n, j = bs + (int)c.i % n;
+      int I[B2_MAX_AXES] = {i, j};
+      c.write<int>(0, I, i - j); c.write<int>(1, I, i + j * j); c.write<int>(2, I, i * i - j);
+    }
+    B2_BODY(c) {
+      const int i = c.I[0], j = c.I[1];
+      int a[B2_MAX_AXES] = {i, j - 2}, b[B2_MAX_AXES] = {i + 2, j - 1}, d[B2_MAX_AXES] = {i - 1, j}, e[B2_MAX_AXES] = {i + 1, j};
+      c.write<int>(3, c.I, c.read<int>(0, a) + c.read<int>(1, b) + c.read<int>(1, d) + c.read<int>(2, d) + c.read<int>(2, e));
+    }""", "multi")
+    n = N - 2 * bs
+    k.range(0, n * n, fields=f, args=[np.int32(n), np.int32(bs)])
+    k(blk, fields=f, args=[np.int32(n), np.int32(bs)])
+    i, j = np.indices((N, N))
+    ins = (i >= bs) & (i < N - bs) & (j >= bs) & (j < N - bs)
+    X, Y, Z = [np.where(ins, v, 0).astype(np.int32) for v in (i - j, i + j * j, i * i - j)]
+    sh = lambda A, di, dj: np.roll(A, (-di, -dj), axis=(0, 1))
+    want = np.where(ins, sh(X, 0, -2) + sh(Y, 2, -1) + sh(Y, -1, 0) + sh(Z, -1, 0) + sh(Z, 1, 0), 0)
+    assert np.array_equal(f[3].to_numpy(), want)
