@@ -838,6 +838,11 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
     B2_CUDA(cudaMemcpyAsync(d, &tab, sizeof(tab), cudaMemcpyHostToDevice, rt->stream()));
     M.p2g_tab = d;
     B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(P2GShared)));
+    {  // smallest shared-memory carve-out that holds P2G_CTAS CTAs: what is left of the 256 KB stays L1
+      int pct = (int)((P2G_CTAS * (sizeof(P2GShared) + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+      if (const char *e = getenv("B2_P2G_CARVEOUT")) pct = atoi(e);
+      B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct));
+    }
   }
   rt->sync();
 }

@@ -44,6 +44,10 @@
 #define P2G_ROUNDS ((P2G_PASS + P2G_NW - 1) / P2G_NW) /* entries per worker thread */
 #define P2G_XUNITS (P2G_UNITS - 64)/* units beyond one per cell                                  */
 #define P2G_CAP (P2G_PASS + 32)    /* staging slots: the first 32 rows are padded to odd lengths */
+#ifndef P2G_NPL
+#define P2G_NPL 5                  /* staging planes: 5 = all weights staged; 4 (make EXTRA=-DP2G_NPL=4) = the scatter
+                                      recomputes the y/z weights, 44 KB per CTA, 132 KB carve-out: 0.506 ms vs 0.483 ms on C3 */
+#endif
 #define P2G_TASKS 280              /* flush tasks: pad nodes, the heavy ones split in groups of <= 9 sources */
 #define P2G_ZERO 1728              /* partial slot that is kept zero (padding of short tasks)    */
 
@@ -67,11 +71,11 @@ struct P2GUnit {                   // one work unit; header by the helper, ck by
 };
 
 struct P2GShared {
-  float4 stg[5][P2G_CAP];          // staging planes; the 64 x 27 per-cell partials (+ zero slot) alias them later
+  float4 stg[P2G_NPL][P2G_CAP];        // staging planes; the 64 x 27 per-cell partials (+ zero slot) alias them later
   P2GUnit unit[2];
   int cnt[64];                     // particles per cell (counted by the workers, consumed and zeroed by the helper)
   int hist[64];                    // helper: cells per last-unit length
-  int nk[64];                      // helper: last units longer than k
+  unsigned short nk[64];           // helper: last units longer than k
   float4 *nb[8];
 };
 
@@ -177,7 +181,7 @@ __device__ __forceinline__ void p2g_order(const MpmDev &M, int gen, P2GShared &S
     if (lane + d < 32) sfx += v;
   }
   const int nkB = sfx - hA - hB, nkA = nkB + hB;  // last units longer than 2*lane+1 / 2*lane
-  S.nk[cA] = nkA, S.nk[cB] = nkB;
+  S.nk[cA] = (unsigned short)nkA, S.nk[cB] = (unsigned short)nkB;
   // row k: every full unit + the last units longer than k, padded to an odd length
   const int padr = lane < 16 ? 1 : 0;  // rows 0..31 only: P2G_CAP
   const int lenA = cA < L ? ((F + nkA) | padr) : 0, lenB = cB < L ? ((F + nkB) | padr) : 0;
@@ -259,6 +263,7 @@ __device__ __forceinline__ void p2g_flush_task(const MpmDev &M, const P2GShared 
 #define TCK(i) do { } while (0)
 #endif
 static_assert(sizeof(P2GShared) <= 55 * 1024, "4 CTAs per SM");
+static_assert(P2G_NPL == 5 || sizeof(P2GShared) + 1024 <= 132 * 1024 / 3, "three CTAs inside the 132 KB carve-out");
 __global__ void __launch_bounds__(P2G_NT, P2G_CTAS) k_mpm_p2g(MpmDev M, int gen) {
 #ifdef P2G_TIMING
   long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
@@ -376,11 +381,18 @@ __global__ void __launch_bounds__(P2G_NT, P2G_CTAS) k_mpm_p2g(MpmDev M, int gen)
         const float b0 = m * E.p1.x - (A00 * s.fx[0] + A01 * s.fx[1] + A02 * s.fx[2]);
         const float b1 = m * E.p1.y - (A10 * s.fx[0] + A11 * s.fx[1] + A12 * s.fx[2]);
         const float b2 = m * E.p1.z - (A20 * s.fx[0] + A21 * s.fx[1] + A22 * s.fx[2]);
+#if P2G_NPL == 5
         S.stg[0][pos] = make_float4(s.w[0][1], s.w[1][1], s.w[2][1], s.w[0][2]);
         S.stg[1][pos] = make_float4(s.w[1][2], s.w[2][2], s.fx[0], 0.0f);
         S.stg[2][pos] = make_float4(b0, b1, A00, A10);
         S.stg[3][pos] = make_float4(A01, A11, A02, A12);
         S.stg[4][pos] = make_float4(b2, A20, A21, A22);
+#else
+        S.stg[0][pos] = make_float4(s.fx[0], s.fx[1], s.fx[2], b2);
+        S.stg[1][pos] = make_float4(b0, b1, A00, A10);
+        S.stg[2][pos] = make_float4(A01, A11, A02, A12);
+        S.stg[3][pos] = make_float4(A20, A21, A22, 0.0f);
+#endif
       };
       Ent Ea, Eb;
       load(0, Ea);
@@ -413,12 +425,31 @@ __global__ void __launch_bounds__(P2G_NT, P2G_CTAS) k_mpm_p2g(MpmDev M, int gen)
 #pragma unroll 1
     for (int k = 0; k < np; k++) {
       const int pos = U.rowstart[k] + u;
+#if P2G_NPL == 5
       const float4 h0 = S.stg[0][pos], h1 = S.stg[1][pos], h2 = S.stg[2][pos], h3 = S.stg[3][pos], h4 = S.stg[4][pos];
       const float tx = h1.z - wb;
       const float wx = fmaf(wa * tx, tx, wg);
       const u64 wx2 = f2_pack(wx, wx);
       const u64 wxy2[3] = {f2_mul(wx2, f2_pack(h0.x, h0.x)), f2_mul(wx2, f2_pack(h0.y, h0.y)), f2_mul(wx2, f2_pack(h0.z, h0.z))};
       const u64 wz2[3] = {f2_pack(h0.w, h0.w), f2_pack(h1.x, h1.x), f2_pack(h1.y, h1.y)};
+#else
+      // four planes: the (y, z) weights are recomputed here as one packed pair per offset (same formulas as mpm_stencil)
+      const float4 hf = S.stg[0][pos], h2 = S.stg[1][pos], h3 = S.stg[2][pos], hA = S.stg[3][pos];
+      const float4 h4 = make_float4(hf.w, hA.x, hA.y, hA.z);
+      const float tx = hf.x - wb;
+      const float wx = fmaf(wa * tx, tx, wg);
+      const u64 wx2 = f2_pack(wx, wx);
+      const u64 fyz = f2_pack(hf.y, hf.z), half2 = f2_pack(0.5f, 0.5f);
+      const u64 t0 = f2_fma(fyz, f2_pack(-1.0f, -1.0f), f2_pack(1.5f, 1.5f));
+      const u64 t1 = f2_add(fyz, f2_pack(-1.0f, -1.0f)), t2 = f2_add(fyz, f2_pack(-0.5f, -0.5f));
+      const u64 wyz0 = f2_mul(f2_mul(half2, t0), t0);
+      const u64 wyz1 = f2_fma(f2_mul(t1, f2_pack(-1.0f, -1.0f)), t1, f2_pack(0.75f, 0.75f));
+      const u64 wyz2 = f2_mul(f2_mul(half2, t2), t2);
+      float wy0, wy1, wy2, wz0, wz1, wz2s;
+      f2_unpack(wyz0, wy0, wz0), f2_unpack(wyz1, wy1, wz1), f2_unpack(wyz2, wy2, wz2s);
+      const u64 wxy2[3] = {f2_mul(wx2, f2_pack(wy0, wy0)), f2_mul(wx2, f2_pack(wy1, wy1)), f2_mul(wx2, f2_pack(wy2, wy2))};
+      const u64 wz2[3] = {f2_pack(wz0, wz0), f2_pack(wz1, wz1), f2_pack(wz2s, wz2s)};
+#endif
       // value at node (i = plane, 0, 0) = b + i A'[:,0]; walks along j with A'[:,1], along k with A'[:,2]
       u64 r01 = f2_fma(f2_pack(fpl, fpl), f2_pack(h2.z, h2.w), f2_pack(h2.x, h2.y));
       u64 r2o = f2_pack(fmaf(fpl, h4.y, h4.x), 1.0f);
