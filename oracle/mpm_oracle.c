@@ -225,6 +225,230 @@ int orc_mpm3d_substeps(int n_grid, int64_t N, float *x, float *v, float *C, floa
   return 0;
 }
 
+/* ============== 3-D J model on a SPARSE grid (blocked active set, the reference's ti.cpu cost model) ==============
+ * Same arithmetic as m3_p2g / m3_gridop / m3_g2p above (mpm3d.py:36-81), but the grid is what a
+ * pointer -> bitmasked -> dense(4^3) SNode tree gives the reference: storage exists for ACTIVE 4^3 blocks only;
+ * a write to an inactive block activates it (lower_access.cpp:254-279: claim, zero-filled node, publish), a read
+ * of an inactive block sees zeros (the ambient element, node_pointer.h:90-98); clear / grid-op touch the active
+ * blocks only (struct-for over the leaf list); `deactivate_every` = K > 0 reproduces the reference's sparse-MPM
+ * idiom of deactivating the grid every K-th substep (snode.py:286-304 deactivate_all + GC, test_gc.py:40-52),
+ * after which P2G re-activates exactly the touched blocks.
+ * mode 0: fp64 accumulators (CAS on the bit pattern, any thread count: order-free to fp64 rounding) = the checker;
+ * mode 1: fp32 CAS atomics as the reference's x64 backend (atomic.h:75) = the timed CPU baseline.            */
+typedef struct {
+  int n_grid, nb;
+  int64_t N;
+  float dt, dx, p_vol, p_mass, E, gravity;
+  int bound;
+  float *x, *v, *C, *J;
+  int32_t *blk_of;  /* [nb^3] -> block index, -1 inactive, -2 being activated */
+  int32_t *blk_key; /* [cap]  */
+  int32_t nblk, cap;
+  float *val;  /* [cap][64][4] {vx, vy, vz, m} */
+  double *acc; /* [cap][64][4] (mode 0)        */
+  int mode, overflow;
+} M3S;
+
+static void atomic_add_f64(double *p, double v) {
+  uint64_t *ip = (uint64_t *)p, old, neu;
+  do {
+    old = __atomic_load_n(ip, __ATOMIC_RELAXED);
+    double f;
+    memcpy(&f, &old, 8);
+    f += v;
+    memcpy(&neu, &f, 8);
+  } while (!__atomic_compare_exchange_n(ip, &old, neu, 0, __ATOMIC_SEQ_CST, __ATOMIC_RELAXED));
+}
+/* block index of 4^3 block (bx,by,bz); activate = 1 claims and zero-fills a new block */
+static int32_t m3s_block(M3S *c, int bx, int by, int bz, int activate) {
+  const int64_t key = ((int64_t)bx * c->nb + by) * c->nb + bz;
+  int32_t b = __atomic_load_n(&c->blk_of[key], __ATOMIC_ACQUIRE);
+  if (b >= 0 || !activate) return b;
+  if (b == -1) {
+    int32_t expect = -1;
+    if (__atomic_compare_exchange_n(&c->blk_of[key], &expect, -2, 0, __ATOMIC_ACQ_REL, __ATOMIC_ACQUIRE)) {
+      int32_t idx = __atomic_fetch_add(&c->nblk, 1, __ATOMIC_RELAXED);
+      if (idx >= c->cap) {
+        c->overflow = 1;
+        idx = c->cap - 1;
+      }
+      c->blk_key[idx] = (int32_t)key;
+      memset(c->val + (size_t)idx * 256, 0, 1024);
+      if (c->acc) memset(c->acc + (size_t)idx * 256, 0, 2048);
+      __atomic_store_n(&c->blk_of[key], idx, __ATOMIC_RELEASE);
+      return idx;
+    }
+  }
+  while ((b = __atomic_load_n(&c->blk_of[key], __ATOMIC_ACQUIRE)) < 0) {
+  }
+  return b;
+}
+static void m3s_clear(void *c_, int64_t lo, int64_t hi) {
+  M3S *c = (M3S *)c_;
+  memset(c->val + (size_t)lo * 256, 0, (size_t)(hi - lo) * 1024);
+  if (c->acc) memset(c->acc + (size_t)lo * 256, 0, (size_t)(hi - lo) * 2048);
+}
+static void m3s_deactivate(void *c_, int64_t lo, int64_t hi) {
+  M3S *c = (M3S *)c_;
+  for (int64_t b = lo; b < hi; b++) c->blk_of[c->blk_key[b]] = -1;
+}
+static void m3s_p2g(void *c_, int64_t lo, int64_t hi) {
+  M3S *c = (M3S *)c_;
+  const float dx = c->dx, dt = c->dt;
+  for (int64_t p = lo; p < hi; p++) {
+    float Xp[3], fx[3], w[3][3];
+    int base[3];
+    for (int d = 0; d < 3; d++) {
+      Xp[d] = c->x[p * 3 + d] / dx;
+      base[d] = (int)(Xp[d] - 0.5f);
+      fx[d] = Xp[d] - (float)base[d];
+      w[0][d] = 0.5f * (1.5f - fx[d]) * (1.5f - fx[d]);
+      w[1][d] = 0.75f - (fx[d] - 1.0f) * (fx[d] - 1.0f);
+      w[2][d] = 0.5f * (fx[d] - 0.5f) * (fx[d] - 0.5f);
+    }
+    float stress = -dt * 4.0f * c->E * c->p_vol * (c->J[p] - 1.0f) / (dx * dx);
+    float A[3][3];
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++) A[i][j] = (i == j ? stress : 0.0f) + c->p_mass * c->C[p * 9 + i * 3 + j];
+    int32_t cache_b[8]; /* the stencil reaches <= 2 blocks per axis */
+    for (int q = 0; q < 8; q++) cache_b[q] = -3;
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++)
+        for (int k = 0; k < 3; k++) {
+          float dpos[3] = {((float)i - fx[0]) * dx, ((float)j - fx[1]) * dx, ((float)k - fx[2]) * dx};
+          float weight = 1.0f;
+          weight *= w[i][0];
+          weight *= w[j][1];
+          weight *= w[k][2];
+          const int gx = base[0] + i, gy = base[1] + j, gz = base[2] + k;
+          const int q = ((gx >> 2) - (base[0] >> 2)) * 4 + ((gy >> 2) - (base[1] >> 2)) * 2 + ((gz >> 2) - (base[2] >> 2));
+          if (cache_b[q] == -3) cache_b[q] = m3s_block(c, gx >> 2, gy >> 2, gz >> 2, 1);
+          const size_t g = (size_t)cache_b[q] * 64 + (size_t)(((gx & 3) << 4) | ((gy & 3) << 2) | (gz & 3));
+          float mv[3];
+          for (int d = 0; d < 3; d++)
+            mv[d] = weight * (c->p_mass * c->v[p * 3 + d] + (A[d][0] * dpos[0] + A[d][1] * dpos[1] + A[d][2] * dpos[2]));
+          float m = weight * c->p_mass;
+          if (c->mode == 0) {
+            for (int d = 0; d < 3; d++) atomic_add_f64(&c->acc[g * 4 + d], (double)mv[d]);
+            atomic_add_f64(&c->acc[g * 4 + 3], (double)m);
+          } else {
+            for (int d = 0; d < 3; d++) atomic_add_f32(&c->val[g * 4 + d], mv[d]);
+            atomic_add_f32(&c->val[g * 4 + 3], m);
+          }
+        }
+  }
+}
+static void m3s_finish_acc(void *c_, int64_t lo, int64_t hi) {
+  M3S *c = (M3S *)c_;
+  for (int64_t g = lo * 256; g < hi * 256; g++) c->val[g] = (float)c->acc[g];
+}
+static void m3s_gridop(void *c_, int64_t lo, int64_t hi) {
+  M3S *c = (M3S *)c_;
+  const int n = c->n_grid, nb = c->nb;
+  for (int64_t b = lo; b < hi; b++) {
+    const int32_t key = c->blk_key[b];
+    const int bx = key / (nb * nb), by = (key / nb) % nb, bz = key % nb;
+    for (int t = 0; t < 64; t++) {
+      int I[3] = {bx * 4 + (t >> 4), by * 4 + ((t >> 2) & 3), bz * 4 + (t & 3)};
+      float *v = &c->val[((size_t)b * 64 + t) * 4];
+      float m = v[3];
+      if (m > 0.0f)
+        for (int d = 0; d < 3; d++) v[d] /= m;
+      v[1] -= c->dt * c->gravity;
+      for (int d = 0; d < 3; d++) {
+        int cond = ((I[d] < c->bound) && (v[d] < 0.0f)) || ((I[d] > n - c->bound) && (v[d] > 0.0f));
+        if (cond) v[d] = 0.0f;
+      }
+    }
+  }
+}
+static void m3s_g2p(void *c_, int64_t lo, int64_t hi) {
+  M3S *c = (M3S *)c_;
+  const float dx = c->dx, dt = c->dt;
+  static const float zero4[4] = {0, 0, 0, 0};
+  for (int64_t p = lo; p < hi; p++) {
+    float Xp[3], fx[3], w[3][3];
+    int base[3];
+    for (int d = 0; d < 3; d++) {
+      Xp[d] = c->x[p * 3 + d] / dx;
+      base[d] = (int)(Xp[d] - 0.5f);
+      fx[d] = Xp[d] - (float)base[d];
+      w[0][d] = 0.5f * (1.5f - fx[d]) * (1.5f - fx[d]);
+      w[1][d] = 0.75f - (fx[d] - 1.0f) * (fx[d] - 1.0f);
+      w[2][d] = 0.5f * (fx[d] - 0.5f) * (fx[d] - 0.5f);
+    }
+    float nv[3] = {0, 0, 0}, nC[9] = {0};
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++)
+        for (int k = 0; k < 3; k++) {
+          float dpos[3] = {((float)i - fx[0]) * dx, ((float)j - fx[1]) * dx, ((float)k - fx[2]) * dx};
+          float weight = 1.0f;
+          weight *= w[i][0];
+          weight *= w[j][1];
+          weight *= w[k][2];
+          const int gx = base[0] + i, gy = base[1] + j, gz = base[2] + k;
+          const int32_t b = m3s_block(c, gx >> 2, gy >> 2, gz >> 2, 0);
+          const float *gv = b >= 0 ? &c->val[((size_t)b * 64 + (size_t)(((gx & 3) << 4) | ((gy & 3) << 2) | (gz & 3))) * 4] : zero4;
+          for (int a = 0; a < 3; a++) {
+            nv[a] += weight * gv[a];
+            for (int bb = 0; bb < 3; bb++) nC[a * 3 + bb] += 4.0f * weight * (gv[a] * dpos[bb]) / (dx * dx);
+          }
+        }
+    for (int d = 0; d < 3; d++) {
+      c->v[p * 3 + d] = nv[d];
+      c->x[p * 3 + d] += dt * nv[d];
+    }
+    c->J[p] *= 1.0f + dt * (nC[0] + nC[4] + nC[8]);
+    memcpy(&c->C[p * 9], nC, sizeof(nC));
+  }
+}
+/* nsteps substeps on the sparse grid.  Particles are updated in place.  On return out_keys[0..*out_nblk) are the
+   linear keys ((bx*nb+by)*nb+bz) of the active blocks (activation order: compare as sorted sets), out_grid their
+   post-grid-op {vx,vy,vz,m} cells [64][4] of the LAST substep and out_p2g the raw P2G momentum/mass of the last
+   substep (any of the three may be NULL).  Returns 0, or -1 if more than cap blocks became active. */
+int orc_mpm3d_sparse_substeps(int n_grid, int64_t N, float *x, float *v, float *C, float *J, float dt, float E, float p_rho,
+                              float gravity, int bound, int nsteps, int mode, int nthreads, int deactivate_every, int32_t cap,
+                              int32_t *out_nblk, int32_t *out_keys, float *out_p2g, float *out_grid) {
+  M3S c;
+  memset(&c, 0, sizeof(c));
+  c.n_grid = n_grid, c.nb = n_grid / 4, c.N = N;
+  c.dt = dt;
+  c.dx = 1.0f / (float)n_grid;
+  c.p_vol = (c.dx * 0.5f) * (c.dx * 0.5f);
+  c.p_mass = c.p_vol * p_rho;
+  c.E = E, c.gravity = gravity, c.bound = bound;
+  c.x = x, c.v = v, c.C = C, c.J = J;
+  c.mode = mode, c.cap = cap;
+  const size_t nblocks = (size_t)c.nb * c.nb * c.nb;
+  c.blk_of = (int32_t *)malloc(nblocks * 4);
+  c.blk_key = (int32_t *)malloc((size_t)cap * 4);
+  c.val = (float *)malloc((size_t)cap * 1024);
+  if (mode == 0) c.acc = (double *)malloc((size_t)cap * 2048);
+  memset(c.blk_of, 0xFF, nblocks * 4);
+  for (int s = 0; s < nsteps; s++) {
+    if (deactivate_every > 0 && s % deactivate_every == 0) {
+      parallel_for(c.nblk, nthreads, m3s_deactivate, &c); /* deactivate_all + GC: nodes are zero-filled when reused */
+      c.nblk = 0;
+    } else {
+      parallel_for(c.nblk, c.nblk >= 1024 ? nthreads : 1, m3s_clear, &c);
+    }
+    parallel_for(N, nthreads, m3s_p2g, &c);
+    if (c.overflow) break;
+    if (mode == 0) parallel_for(c.nblk, c.nblk >= 1024 ? nthreads : 1, m3s_finish_acc, &c);
+    if (s == nsteps - 1 && out_p2g) memcpy(out_p2g, c.val, (size_t)c.nblk * 1024);
+    parallel_for(c.nblk, c.nblk >= 1024 ? nthreads : 1, m3s_gridop, &c);
+    parallel_for(N, nthreads, m3s_g2p, &c);
+  }
+  if (out_nblk) *out_nblk = c.nblk;
+  if (!c.overflow) {
+    if (out_keys) memcpy(out_keys, c.blk_key, (size_t)c.nblk * 4);
+    if (out_grid) memcpy(out_grid, c.val, (size_t)c.nblk * 1024);
+  }
+  const int rc = c.overflow ? -1 : 0;
+  free(c.blk_of), free(c.blk_key), free(c.val), free(c.acc);
+  return rc;
+}
+
 /* ============================ 2-D J model (test_mpm88.py) ============================ */
 typedef struct {
   int n_grid;

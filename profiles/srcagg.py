@@ -9,7 +9,22 @@ import sys
 path = sys.argv[1]
 want = sys.argv[2] if len(sys.argv) > 2 else ""
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
-rows = list(csv.reader(open(path, errors="replace")))
+def _rows(path):
+    """ncu does not escape quotes inside the source column (inline asm): split on '","' and keep the fixed-width tail"""
+    width = None
+    for line in open(path, errors="replace"):
+        line = line.rstrip("\n")
+        if not (line.startswith('"') and line.endswith('"')):
+            continue
+        f = line[1:-1].split('","')
+        if f[0] == "Line No":
+            width = len(f)
+        elif width and len(f) > width and f[0].isdigit():
+            f = [f[0], '","'.join(f[1:len(f) - width + 2])] + f[len(f) - width + 2:]
+        yield f
+
+
+rows = list(_rows(path))
 fn = None
 hdr = None
 cur_file = ""

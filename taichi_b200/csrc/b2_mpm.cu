@@ -410,7 +410,7 @@ __global__ void __launch_bounds__(256) k_mpm_mark_listed(MpmDev M) {
 
 #include "b2_f32x2.cuh"
 #include "b2_mpm_bls.cuh"
-#include "b2_mpm_p2g.cuh"
+#include "b2_mpm_p2gw.cuh"
 
 // Plain path (ti.block_local off): every particle walks the SNode tree with activation and issues
 // one vector red per node -- the reference's non-BLS access pattern (K15) on the binned particles.
@@ -618,7 +618,6 @@ struct B2Mpm_t {
   bool order_valid = false;  // P2G has left the cell order of the current generation in the chunks (G2P skips its sort)
   bool sparse = false;
   bool profiling = false;
-  int flush_wavefronts = 0;  // shared-memory wavefronts of one flush pass after the table search (diagnostic)
   bool in_substep = false;  // inside substep(): k_mpm_clear resets the work counters / arena cursor for the phases that follow
   std::vector<cudaEvent_t> prof_events;
   double phase_sum[6] = {0, 0, 0, 0, 0, 0};
@@ -752,98 +751,8 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   M.work_counter = dalloc<u32>(8);
   M.listed = dalloc<u32>((size_t)(nblocks + 31) / 32);
   M.stats = dalloc<double>(8);
-  {  // P2G flush tasks: for every pad node the (cell, offset) partials that reach it, in groups of <= 9,
-     // biggest groups first (equal trip counts inside a warp); short groups are padded with the zero slot
-    static P2GTab tab;
-    static int tab_wavefronts = -1;  // the table depends on nothing but the 4^3 block shape: built once per process
-    if (tab_wavefronts < 0) {
-    std::vector<std::vector<unsigned short>> src(216);
-    for (int c = 0; c < 64; c++)
-      for (int i = 0; i < 3; i++)
-        for (int j = 0; j < 3; j++)
-          for (int k = 0; k < 3; k++) {
-            const int px = (c >> 4) + i, py = ((c >> 2) & 3) + j, pz = (c & 3) + k;
-            src[(px * 6 + py) * 6 + pz].push_back((unsigned short)(c * 27 + i * 9 + j * 3 + k));
-          }
-    struct Task { int node; std::vector<unsigned short> s; };
-    std::vector<Task> tasks;
-    for (int nd = 0; nd < 216; nd++)
-      for (size_t o = 0; o < src[nd].size(); o += 9) {
-        Task t;
-        t.node = nd;
-        t.s.assign(src[nd].begin() + o, src[nd].begin() + std::min(src[nd].size(), o + 9));
-        tasks.push_back(t);
-      }
-    if ((int)tasks.size() != P2G_TASKS) throw B2Error(TI_ERROR_INVALID_STATE, "flush task table");
-    std::stable_sort(tasks.begin(), tasks.end(), [](const Task &a, const Task &b) { return a.s.size() > b.s.size(); });
-    for (int t = 0; t < P2G_TASKS; t++) {
-      for (int q = 0; q < 9; q++) tab.task[t][q] = q < (int)tasks[t].s.size() ? tasks[t].s[q] : (unsigned short)P2G_ZERO;
-      tab.task[t][9] = (unsigned short)tasks[t].node;
-    }
-    // Bank conflicts of the flush: the q-th LDS.128 of 8 consecutive tasks (a quarter warp) is one wavefront only if the
-    // 8 partials lie in 8 different 16-byte bank groups (index mod 8) or at the same address.  Which task sits in which
-    // lane and in which order a task sums its sources is free, so a deterministic local search permutes both until no
-    // swap lowers the wavefront count (ncu before: half of the flush's shared-memory wavefronts were replays).
-    {
-      auto cost_block = [&](int b) {
-        int c = 0;
-        for (int q = 0; q < 9; q++) {
-          int worst = 1;
-          for (int g = 0; g < 8; g++) {
-            unsigned short seen[8];
-            int ns = 0;
-            for (int l = 0; l < 8; l++) {
-              const unsigned short a = tab.task[b * 8 + l][q];
-              if ((a & 7) != g) continue;
-              bool dup = false;
-              for (int k = 0; k < ns; k++) dup = dup || seen[k] == a;
-              if (!dup) seen[ns++] = a;
-            }
-            worst = std::max(worst, ns);
-          }
-          c += worst;
-        }
-        return c;
-      };
-      static_assert(P2G_TASKS % 8 == 0, "quarter warps");
-      const int nblk = P2G_TASKS / 8;
-      uint64_t rng = 0x9E3779B97F4A7C15ull;
-      auto rnd = [&](int n) {
-        rng = rng * 6364136223846793005ull + 1442695040888963407ull;
-        return (int)((rng >> 33) % (uint64_t)n);
-      };
-      for (int iter = 0; iter < 200000; iter++) {
-        if (iter & 1) {  // swap two sources inside one task
-          const int t = rnd(P2G_TASKS), q0 = rnd(9), q1 = rnd(9);
-          if (q0 == q1) continue;
-          const int b = t / 8, before = cost_block(b);
-          std::swap(tab.task[t][q0], tab.task[t][q1]);
-          if (cost_block(b) > before) std::swap(tab.task[t][q0], tab.task[t][q1]);
-        } else {  // swap two whole tasks between lanes
-          const int t0 = rnd(P2G_TASKS), t1 = rnd(P2G_TASKS);
-          if (t0 / 8 == t1 / 8) continue;
-          const int b0 = t0 / 8, b1 = t1 / 8, before = cost_block(b0) + cost_block(b1);
-          for (int q = 0; q < 10; q++) std::swap(tab.task[t0][q], tab.task[t1][q]);
-          if (cost_block(b0) + cost_block(b1) > before)
-            for (int q = 0; q < 10; q++) std::swap(tab.task[t0][q], tab.task[t1][q]);
-        }
-      }
-      int total = 0;
-      for (int b = 0; b < nblk; b++) total += cost_block(b);
-      tab_wavefronts = total;  // 9 * 35 = 315 would be conflict-free (580 before the search, ~435 after)
-    }
-    }
-    flush_wavefronts = tab_wavefronts;
-    void *d = dalloc<unsigned char>(sizeof(P2GTab));
-    B2_CUDA(cudaMemcpyAsync(d, &tab, sizeof(tab), cudaMemcpyHostToDevice, rt->stream()));
-    M.p2g_tab = d;
-    B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(P2GShared)));
-    {  // smallest shared-memory carve-out that holds P2G_CTAS CTAs: what is left of the 256 KB stays L1
-      int pct = (int)((P2G_CTAS * (sizeof(P2GShared) + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
-      if (const char *e = getenv("B2_P2G_CARVEOUT")) pct = atoi(e);
-      B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct));
-    }
-  }
+  B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
+  B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
   rt->sync();
 }
 void B2Mpm_t::Io::ensure() {
@@ -921,7 +830,10 @@ void B2Mpm_t::p2g() {
   if (!in_substep) B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));  // (P2G takes slots from counter 0, G2P from counter 1)
   if (prm.block_local)
   {
-    k_mpm_p2g<<<rt->num_sms * P2G_CTAS, P2G_NT, sizeof(P2GShared), st>>>(M, gen);
+    if (M.pot)
+      k_mpm_p2g<true><<<rt->num_sms * P2W_CTAS, P2W_WARPS * 32, P2W_WARPS * sizeof(P2WWarp), st>>>(M, gen);
+    else
+      k_mpm_p2g<false><<<rt->num_sms * P2W_CTAS, P2W_WARPS * 32, P2W_WARPS * sizeof(P2WWarp), st>>>(M, gen);
     order_valid = true;
   }
   else

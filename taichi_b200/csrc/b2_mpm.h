@@ -6,8 +6,8 @@
 #define MPM_PLANE_BYTES 4096     /* 256 x float4                                 */
 #define MPM_CHUNK_BYTES 17920    /* 4 float4 planes + 256 x u32 particle ids + 256 x u16 cell-sorted order */
 #define MPM_PERM_OFF 17408       /* byte offset of the u16 order plane (written by P2G, read by G2P) */
-#define MPM_PASS 576             /* bin entries per P2G work unit = per G2P pass when it follows P2G   */
-#define MPM_MAXPASS 16           /* passes per bin: maxc * 256 / MPM_PASS rounded up                   */
+#define MPM_PASS 1024            /* bin entries per P2G pass (4 chunks) = per G2P pass when it follows P2G */
+#define MPM_MAXPASS 8            /* passes per bin: maxc * 256 / MPM_PASS                                  */
 #define MPM_SB 2048              /* particles cell-sorted per pass (shared-memory keys) */
 #define MPM_TOMB (-1.0e30f)      /* p0.x of a bin entry whose particle moved to another block */
 
@@ -44,6 +44,5 @@ struct MpmDev {
   u32 *work_counter;  // dynamic slot fetch for the persistent kernels [8]
   u32 *listed;        // [nb^3 / 32] bit per block: the block is in the leaf element list (kept current incrementally)
   int dbg;              // B2_DBG experiment switches (0 in production)
-  const void *p2g_tab;  // P2GTab (b2_mpm_p2g.cuh): flush source table
   double *stats;      // [8]
 };

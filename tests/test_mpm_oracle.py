@@ -73,3 +73,68 @@ def test_mpm3d_conservation_and_modes():
         assert abs(pm.astype(np.float64).sum() - N * p_mass) < 1e-5 * N * p_mass  # partition of unity
     assert np.allclose(outs[0][0], outs[1][0], rtol=1e-4, atol=1e-6)
     assert np.allclose(outs[0][2], outs[1][2], rtol=1e-4, atol=1e-9)
+
+
+def run_sparse(n_grid, x, v, Cm, J, dt, nsteps, mode, nthreads, deactivate_every, cap=4096):
+    xs, vs, Cs, Js = x.copy(), v.copy(), Cm.copy(), J.copy()
+    nblk = C.c_int32(0)
+    keys = np.zeros(cap, np.int32)
+    p2g = np.zeros((cap, 64, 4), np.float32)
+    grid = np.zeros((cap, 64, 4), np.float32)
+    rc = ORC.orc_mpm3d_sparse_substeps(n_grid, C.c_int64(len(x)), fp(xs), fp(vs), fp(Cs), fp(Js), C.c_float(dt), C.c_float(400.0),
+                                       C.c_float(1.0), C.c_float(9.8), 3, nsteps, mode, nthreads, deactivate_every, cap,
+                                       C.byref(nblk), keys.ctypes.data_as(C.POINTER(C.c_int32)), fp(p2g), fp(grid))
+    assert rc == 0
+    n = nblk.value
+    order = np.argsort(keys[:n])
+    return xs, vs, Cs, Js, keys[:n][order], p2g[:n][order], grid[:n][order]
+
+
+def dense_blocks(field, keys, nb):
+    """[n][n][n][k] dense image -> [len(keys)][64][k] blocks in key order"""
+    bx, by, bz = keys // (nb * nb), (keys // nb) % nb, keys % nb
+    out = np.zeros((len(keys), 64, field.shape[-1]), field.dtype)
+    for t in range(64):
+        out[:, t] = field[bx * 4 + (t >> 4), by * 4 + ((t >> 2) & 3), bz * 4 + (t & 3)]
+    return out
+
+
+def test_sparse_port_equals_dense_port():
+    """The blocked active-set variant (the honest ti.cpu cost model, also the full-size checker) runs the same
+    arithmetic as the dense restatement that the mpm88 vector pins indirectly: single-threaded fp64 accumulation
+    is bit-identical; the active set is exactly the set of blocks holding a touched node."""
+    rng = np.random.default_rng(7)
+    n_grid, N, dt, steps = 32, 5000, 4e-4, 6
+    nb = n_grid // 4
+    x = (rng.random((N, 3)) * 0.3 + 0.2).astype(np.float32)
+    v = ((rng.random((N, 3)) - 0.5) * 2).astype(np.float32)
+    Cm = ((rng.random((N, 3, 3)) - 0.5) * 2).astype(np.float32)
+    J = (1 + (rng.random(N) - 0.5) * 0.05).astype(np.float32)
+    xd, vd, Cd, Jd = x.copy(), v.copy(), Cm.copy(), J.copy()
+    gv = np.zeros((n_grid,) * 3 + (3,), np.float32)
+    gm = np.zeros((n_grid,) * 3, np.float32)
+    pv, pm = np.zeros_like(gv), np.zeros_like(gm)
+    ORC.orc_mpm3d_substeps(n_grid, C.c_int64(N), fp(xd), fp(vd), fp(Cd), fp(Jd), C.c_float(dt), C.c_float(400.0), C.c_float(1.0),
+                           C.c_float(9.8), 3, steps, 0, 1, fp(gv), fp(gm), fp(pv), fp(pm))
+    xs, vs, Cs, Js, keys, p2g, grid = run_sparse(n_grid, x, v, Cm, J, dt, steps, 0, 1, 1)
+    assert np.array_equal(xs, xd) and np.array_equal(vs, vd) and np.array_equal(Cs, Cd) and np.array_equal(Js, Jd)
+    dense_p2g = dense_blocks(np.concatenate([pv, pm[..., None]], -1), keys, nb)
+    assert np.array_equal(p2g, dense_p2g)
+    # with deactivate_every = 1 the active set is exactly the blocks the LAST substep's particles touch
+    # (positions BEFORE the last substep: rerun steps - 1 substeps)
+    xb = run_sparse(n_grid, x, v, Cm, J, dt, steps - 1, 0, 1, 1)[0]
+    base = (xb * np.float32(n_grid) - np.float32(0.5)).astype(np.int32)
+    want = set()
+    for d in np.ndindex(2, 2, 2):
+        b = (base + 2 * np.array(d, np.int32)) >> 2
+        want.update(((b[:, 0] * nb + b[:, 1]) * nb + b[:, 2]).tolist())
+    assert sorted(want) == keys.tolist()
+    # never deactivating only grows the set; threaded fp32 CAS mode agrees within the reorder tolerance
+    xk, vk, Ck, Jk, keys_keep, _, _ = run_sparse(n_grid, x, v, Cm, J, dt, steps, 1, 4, 0)
+    assert set(keys.tolist()) <= set(keys_keep.tolist())
+    assert np.allclose(xk, xs, rtol=0, atol=2e-6) and np.allclose(vk, vs, rtol=1e-4, atol=1e-4) and np.allclose(Jk, Js, rtol=1e-5)
+    # block capacity overflow is reported, not written out of bounds
+    nblk = C.c_int32(0)
+    rc = ORC.orc_mpm3d_sparse_substeps(n_grid, C.c_int64(N), fp(x.copy()), fp(v.copy()), fp(Cm.copy()), fp(J.copy()), C.c_float(dt),
+                                       C.c_float(400.0), C.c_float(1.0), C.c_float(9.8), 3, 1, 1, 2, 0, 4, C.byref(nblk), None, None, None)
+    assert rc == -1
