@@ -380,6 +380,9 @@ TI_DLL_EXPORT int32_t b2_mpm_grid_op(B2Mpm mpm);
 TI_DLL_EXPORT int32_t b2_mpm_g2p(B2Mpm mpm);
 /* dense image of the grid, [n][n][n][4] floats {vx,vy,vz,m}; inactive cells 0 */
 TI_DLL_EXPORT int32_t b2_mpm_grid_to_dense(B2Mpm mpm, float *out_any);
+/* compact image: keys[e] = (bx*nb+by)*nb+bz of the e-th active 4^3 block (leaf list order), cells[e][64][4] its
+ * {vx,vy,vz,m} cells.  Returns the number of active blocks (also when keys/cells are NULL); at most cap are written. */
+TI_DLL_EXPORT int64_t b2_mpm_grid_blocks(B2Mpm mpm, int32_t *keys_any, float *cells_any, int64_t cap);
 /* out_host[8]: {n_particles, n_active_blocks, n_bins, n_work_items, sum_m, sum_px, sum_py, sum_pz} (doubles) */
 TI_DLL_EXPORT int32_t b2_mpm_stats(B2Mpm mpm, double *out_host);
 /* per-phase device time of the last b2_mpm_substep call with profiling on, ms:

@@ -260,7 +260,8 @@ static void atomic_add_f64(double *p, double v) {
   } while (!__atomic_compare_exchange_n(ip, &old, neu, 0, __ATOMIC_SEQ_CST, __ATOMIC_RELAXED));
 }
 /* block index of 4^3 block (bx,by,bz); activate = 1 claims and zero-fills a new block */
-static int32_t m3s_block(M3S *c, int bx, int by, int bz, int activate) {
+static inline int32_t m3s_block(M3S *c, int bx, int by, int bz, int activate) {
+  if (bx >= c->nb || by >= c->nb || bz >= c->nb) return -1; /* (only reached by the non-touching corner lookups of G2P) */
   const int64_t key = ((int64_t)bx * c->nb + by) * c->nb + bz;
   int32_t b = __atomic_load_n(&c->blk_of[key], __ATOMIC_ACQUIRE);
   if (b >= 0 || !activate) return b;
@@ -310,8 +311,15 @@ static void m3s_p2g(void *c_, int64_t lo, int64_t hi) {
     float A[3][3];
     for (int i = 0; i < 3; i++)
       for (int j = 0; j < 3; j++) A[i][j] = (i == j ? stress : 0.0f) + c->p_mass * c->C[p * 9 + i * 3 + j];
-    int32_t cache_b[8]; /* the stencil reaches <= 2 blocks per axis */
-    for (int q = 0; q < 8; q++) cache_b[q] = -3;
+    /* the stencil reaches <= 2 blocks per axis: resolve (and activate) the touched ones once per particle */
+    size_t blk[8];
+    const int hi[3] = {((base[0] + 2) >> 2) - (base[0] >> 2), ((base[1] + 2) >> 2) - (base[1] >> 2), ((base[2] + 2) >> 2) - (base[2] >> 2)};
+    for (int q = 0; q < 8; q++) {
+      const int qx = q >> 2, qy = (q >> 1) & 1, qz = q & 1;
+      blk[q] = (qx <= hi[0] && qy <= hi[1] && qz <= hi[2])
+                   ? (size_t)m3s_block(c, (base[0] >> 2) + qx, (base[1] >> 2) + qy, (base[2] >> 2) + qz, 1) * 64
+                   : 0;
+    }
     for (int i = 0; i < 3; i++)
       for (int j = 0; j < 3; j++)
         for (int k = 0; k < 3; k++) {
@@ -322,8 +330,7 @@ static void m3s_p2g(void *c_, int64_t lo, int64_t hi) {
           weight *= w[k][2];
           const int gx = base[0] + i, gy = base[1] + j, gz = base[2] + k;
           const int q = ((gx >> 2) - (base[0] >> 2)) * 4 + ((gy >> 2) - (base[1] >> 2)) * 2 + ((gz >> 2) - (base[2] >> 2));
-          if (cache_b[q] == -3) cache_b[q] = m3s_block(c, gx >> 2, gy >> 2, gz >> 2, 1);
-          const size_t g = (size_t)cache_b[q] * 64 + (size_t)(((gx & 3) << 4) | ((gy & 3) << 2) | (gz & 3));
+          const size_t g = blk[q] + (size_t)(((gx & 3) << 4) | ((gy & 3) << 2) | (gz & 3));
           float mv[3];
           for (int d = 0; d < 3; d++)
             mv[d] = weight * (c->p_mass * c->v[p * 3 + d] + (A[d][0] * dpos[0] + A[d][1] * dpos[1] + A[d][2] * dpos[2]));
@@ -378,6 +385,11 @@ static void m3s_g2p(void *c_, int64_t lo, int64_t hi) {
       w[2][d] = 0.5f * (fx[d] - 0.5f) * (fx[d] - 0.5f);
     }
     float nv[3] = {0, 0, 0}, nC[9] = {0};
+    const float *blk[8]; /* inactive blocks read the ambient zeros */
+    for (int q = 0; q < 8; q++) {
+      const int32_t b = m3s_block(c, (base[0] >> 2) + (q >> 2), (base[1] >> 2) + ((q >> 1) & 1), (base[2] >> 2) + (q & 1), 0);
+      blk[q] = b >= 0 ? &c->val[(size_t)b * 256] : NULL;
+    }
     for (int i = 0; i < 3; i++)
       for (int j = 0; j < 3; j++)
         for (int k = 0; k < 3; k++) {
@@ -387,8 +399,8 @@ static void m3s_g2p(void *c_, int64_t lo, int64_t hi) {
           weight *= w[j][1];
           weight *= w[k][2];
           const int gx = base[0] + i, gy = base[1] + j, gz = base[2] + k;
-          const int32_t b = m3s_block(c, gx >> 2, gy >> 2, gz >> 2, 0);
-          const float *gv = b >= 0 ? &c->val[((size_t)b * 64 + (size_t)(((gx & 3) << 4) | ((gy & 3) << 2) | (gz & 3))) * 4] : zero4;
+          const int q = ((gx >> 2) - (base[0] >> 2)) * 4 + ((gy >> 2) - (base[1] >> 2)) * 2 + ((gz >> 2) - (base[2] >> 2));
+          const float *gv = blk[q] ? blk[q] + (size_t)(((gx & 3) << 4) | ((gy & 3) << 2) | (gz & 3)) * 4 : zero4;
           for (int a = 0; a < 3; a++) {
             nv[a] += weight * gv[a];
             for (int bb = 0; bb < 3; bb++) nC[a * 3 + bb] += 4.0f * weight * (gv[a] * dpos[bb]) / (dx * dx);

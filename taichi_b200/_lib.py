@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200mpm.so")
+LIB_PATH = os.environ.get("B2_LIB") or os.path.join(_HERE, "lib", "libb200mpm.so")  # B2_LIB: experiment builds of the same library
 
 TI_ARCH_CUDA = 3
 TI_ARGUMENT_TYPE_I32, TI_ARGUMENT_TYPE_F32, TI_ARGUMENT_TYPE_NDARRAY = 0, 1, 2
@@ -165,6 +165,7 @@ SIGNATURES = {
     "b2_mpm_grid_op": (C.c_int32, [C.c_void_p]),
     "b2_mpm_g2p": (C.c_int32, [C.c_void_p]),
     "b2_mpm_grid_to_dense": (C.c_int32, [C.c_void_p, C.c_void_p]),
+    "b2_mpm_grid_blocks": (C.c_int64, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_mpm_stats": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "b2_mpm_invalidate_lists": (C.c_int32, [C.c_void_p]),
     "b2_memory_profiler_info": (C.c_int64, [C.c_void_p, C.c_char_p, C.c_int64]),

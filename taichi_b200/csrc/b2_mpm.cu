@@ -397,6 +397,18 @@ __global__ void __launch_bounds__(256) k_mpm_grid_to_dense(MpmDev M, float4 *out
   }
 }
 
+// grid -> compact list of active blocks: key (bx*nb+by)*nb+bz and the 64 cells of each (list order)
+__global__ void __launch_bounds__(256) k_mpm_grid_blocks(MpmDev M, int *keys, float4 *cells, long long cap) {
+  B2CList *L = M.T->lists[M.leaf_sid];
+  const u32 ne = (u32)min((long long)L->count, cap);
+  const int sub = threadIdx.x >> 6, t = threadIdx.x & 63;
+  for (u32 e = blockIdx.x * 4 + sub; e < ne; e += gridDim.x * 4) {
+    const B2Element *E = (const B2Element *)b2_list_get(L, e);
+    if (t == 0) keys[e] = (E->pcoord[0] * M.nb + E->pcoord[1]) * M.nb + E->pcoord[2];
+    cells[(u64)e * 64 + t] = ((const float4 *)E->node)[t];
+  }
+}
+
 // after a full listgen: every listed block gets its bit
 __global__ void __launch_bounds__(256) k_mpm_mark_listed(MpmDev M) {
   B2CList *L = M.T->lists[M.leaf_sid];
@@ -751,8 +763,9 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   M.work_counter = dalloc<u32>(8);
   M.listed = dalloc<u32>((size_t)(nblocks + 31) / 32);
   M.stats = dalloc<double>(8);
-  B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
-  B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
+  B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
+  B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
+  B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<false, P2W_CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
   rt->sync();
 }
 void B2Mpm_t::Io::ensure() {
@@ -830,10 +843,14 @@ void B2Mpm_t::p2g() {
   if (!in_substep) B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));  // (P2G takes slots from counter 0, G2P from counter 1)
   if (prm.block_local)
   {
-    if (M.pot)
-      k_mpm_p2g<true><<<rt->num_sms * P2W_CTAS, P2W_WARPS * 32, P2W_WARPS * sizeof(P2WWarp), st>>>(M, gen);
+    static const int ctas = getenv("B2_P2G_CTAS") ? atoi(getenv("B2_P2G_CTAS")) : P2W_CTAS;  // experiment switch
+    const size_t smem = P2W_WARPS * sizeof(P2WWarp);
+    if (!M.pot)
+      k_mpm_p2g<false, P2W_CTAS><<<rt->num_sms * P2W_CTAS, P2W_WARPS * 32, smem, st>>>(M, gen);
+    else if (ctas == 2)
+      k_mpm_p2g<true, 2><<<rt->num_sms * 2, P2W_WARPS * 32, smem, st>>>(M, gen);
     else
-      k_mpm_p2g<false><<<rt->num_sms * P2W_CTAS, P2W_WARPS * 32, P2W_WARPS * sizeof(P2WWarp), st>>>(M, gen);
+      k_mpm_p2g<true, 3><<<rt->num_sms * 3, P2W_WARPS * 32, smem, st>>>(M, gen);
     order_valid = true;
   }
   else
@@ -1092,6 +1109,25 @@ int32_t b2_mpm_grid_to_dense(B2Mpm m, float *out) {
   B2_CUDA(cudaGetLastError());
   o.finish();
   return 0;
+  B2_API_END(-1)
+}
+int64_t b2_mpm_grid_blocks(B2Mpm m, int32_t *keys, float *cells, int64_t cap) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  cudaStream_t st = m->rt->stream();
+  m->ensure_lists();
+  m->rt->sync();
+  const int64_t n = (int64_t)m->tree->list_count(m->M.leaf_sid);
+  if (keys == nullptr || cells == nullptr || cap <= 0) return n;
+  const int64_t k = std::min(n, cap);
+  B2Staged sk, sc;
+  sk.init(keys, (size_t)k * 4, false, true, st);
+  sc.init(cells, (size_t)k * 1024, false, true, st);
+  k_mpm_grid_blocks<<<m->rt->num_sms * 8, 256, 0, st>>>(m->M, sk.as<int>(), sc.as<float4>(), k);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  sk.finish(), sc.finish();
+  return n;
   B2_API_END(-1)
 }
 int32_t b2_mpm_stats(B2Mpm m, double *out) {

@@ -14,8 +14,8 @@
 //            the 32 lanes of a round loop over nearly equal trip counts: round r hands unit rank 32 r + lane to lane;
 //   gather   lane = cell: the lane walks its cell's particles through the order.  The four 16-byte planes
 //            of a particle travel global -> shared with cp.async (SASS LDGSTS) into a per-lane ring
-//            P2W_DEPTH particles deep (the bin itself was L2-prefetched with cp.async.bulk.prefetch one bin
-//            ahead), so no load latency is exposed and no register holds data in flight.  All 27 stencil
+//            P2W_DEPTH particles deep, so no register holds data in flight (an L2 bulk prefetch of the next
+//            bin, as r1 had, doubles the DRAM reads here and was measured slower: 0.381 vs 0.367 ms).  All 27 stencil
 //            nodes x {mv, m} are accumulated in 54 packed-fp32x2 REGISTERS: no atomics, no shuffles;
 //   pad      the round's 32 cells are distinct, so for a fixed stencil offset the 32 lanes add into 32
 //            different nodes of the warp's private (4+2)^3 pad: 27 plain LDS/FADD2/STS steps;
@@ -28,21 +28,27 @@
 #define P2W_WARPS 4 /* warps per CTA (the CTA is only a container: warps never synchronise with each other) */
 #endif
 #ifndef P2W_CTAS
-#define P2W_CTAS 2  /* CTAs per SM */
+#define P2W_CTAS 3  /* CTAs per SM: 12 warps at 168 registers (2 x 4 warps at 248: 0.368 ms on C3, 3 x 4: 0.335 ms) */
+#endif
+#ifndef P2W_COUNT_U
+#define P2W_COUNT_U 4 /* position loads in flight per lane in the count phase */
 #endif
 #ifndef P2W_UNIT
 #define P2W_UNIT 32 /* longest run of one cell's particles a lane accumulates before it goes to the pad (< 64) */
 #endif
 #ifndef P2W_DEPTH
-#define P2W_DEPTH 4 /* particles in flight per lane (power of two) */
+#define P2W_DEPTH 2 /* particles in flight per lane (power of two); 4 is not faster and costs 4 KB of L1 per warp */
 #endif
 static_assert(MPM_PASS == 4 * MPM_CHUNK, "a pass is four whole chunks");
+static_assert(P2W_DEPTH * 4 * 32 * 16 >= MPM_PASS * 2, "ck fits the ring");
 
 struct P2WWarp {                      // private state of one warp
-  float4 ring[P2W_DEPTH][4][32];      // [slot][plane][lane]: particles in flight
+  union {
+    float4 ring[P2W_DEPTH][4][32];    // gather: [slot][plane][lane] particles in flight
+    unsigned short ck[MPM_PASS];      // count / order: entry -> cell << 10 | rank inside the cell (live entries)
+  };
   float4 pad[216];                    // (4+2)^3 nodes {sum w mv_x, sum w mv_y, sum w mv_z, sum w}
   unsigned short order[MPM_PASS];     // cell-major position -> entry of the pass
-  unsigned short ck[MPM_PASS];        // entry -> cell << 10 | rank inside the cell (live entries)
   u32 liveb[MPM_PASS / 32];           // entry -> live (not a tombstone)
   int cnt[64];                        // particles per cell
   int hist[64];                       // units per length
@@ -65,24 +71,6 @@ __device__ __forceinline__ void p2w_commit() { asm volatile("cp.async.commit_gro
 template <int N>
 __device__ __forceinline__ void p2w_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
-// L2 prefetch of the four particle planes of pass `pass` of a bin: one bulk prefetch per (chunk, plane),
-// issued by 16 lanes (SASS UBLKPF.L2).
-__device__ __forceinline__ void p2w_prefetch(const MpmDev &M, int gen, u32 nslots, u32 slot, u32 pass) {
-  const int lane = threadIdx.x & 31;
-  if (slot >= nslots || lane >= 16) return;
-  const u32 total = M.count[gen][slot];
-  const u32 q0 = pass * MPM_PASS;
-  if (q0 >= total) return;
-  const int n = (int)min((u32)MPM_PASS, total - q0);
-  const int ch = lane >> 2, pl = lane & 3;
-  const int ne = min(MPM_CHUNK, n - ch * MPM_CHUNK);
-  if (ne <= 0) return;
-  const u32 id1 = M.chunk_of[gen][(u64)slot * M.maxc + min(pass * 4u + (u32)ch, (u32)M.maxc - 1u)];
-  if (id1 == 0) return;
-  const u8 *src = mpm_chunk_ptr(M, gen, id1) + pl * MPM_PLANE_BYTES;
-  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(ne * 16) : "memory");
 }
 
 template <bool POT>
@@ -109,8 +97,8 @@ __device__ __forceinline__ int p2w_cell_of(const MpmDev &M, const float4 p0) {
   return (l[0] << 4) | (l[1] << 2) | l[2];
 }
 
-template <bool POT>
-__global__ void __launch_bounds__(P2W_WARPS * 32, P2W_CTAS) k_mpm_p2g(MpmDev M, int gen) {
+template <bool POT, int CTAS>
+__global__ void __launch_bounds__(P2W_WARPS * 32, CTAS) k_mpm_p2g(MpmDev M, int gen) {
   extern __shared__ __align__(16) unsigned char p2w_smem[];
   P2WWarp &S = ((P2WWarp *)p2w_smem)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
@@ -118,20 +106,28 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, P2W_CTAS) k_mpm_p2g(MpmDev M, 
   const u32 nslots = *M.nslots;
   const int cA = 2 * lane, cB = cA + 1;
 
+  // header of a bin, one word per lane: lane 0 entries, lane 1 block key, lanes 2..5 the first pass's chunk ids.  The
+  // header of the NEXT bin is requested before this bin is processed: the dependent chain work counter -> count /
+  // key -> chunk ids never sits on the critical path (it was 9 % of the warp samples).
+  auto header = [&](u32 sl) -> u32 {
+    if (sl >= nslots || lane >= 6) return 0u;
+    if (lane == 0) return M.count[gen][sl];
+    if (lane == 1) return (u32)M.slot_key[sl];
+    return M.chunk_of[gen][(u64)sl * M.maxc + (u32)(lane - 2)];
+  };
   u32 next = 0;
   if (lane == 0) next = atomicAdd(&M.work_counter[0], 1u);
   next = __shfl_sync(FULL, next, 0);
-  p2w_prefetch(M, gen, nslots, next, 0u);
-
+  u32 hnext = header(next);
   for (;;) {
-    const u32 slot = next;
+    const u32 slot = next, hdr = hnext;
     if (slot >= nslots) break;
     if (lane == 0) next = atomicAdd(&M.work_counter[0], 1u);
     next = __shfl_sync(FULL, next, 0);
-    p2w_prefetch(M, gen, nslots, next, 0u);  // the next bin's planes travel to L2 while this bin is processed
-    const u32 total = M.count[gen][slot];
+    hnext = header(next);
+    const u32 total = __shfl_sync(FULL, hdr, 0);
     if (total == 0) continue;
-    const int key = M.slot_key[slot];
+    const int key = (int)__shfl_sync(FULL, hdr, 1);
     int bx, by, bz;
     mpm_unkey(M, key, bx, by, bz);
     for (int i = lane; i < 216; i += 32) S.pad[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -139,22 +135,25 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, P2W_CTAS) k_mpm_p2g(MpmDev M, 
 
     for (u32 pass = 0; pass * MPM_PASS < total; pass++) {
       const u32 q0 = pass * MPM_PASS;
-      if (q0 + MPM_PASS < total) p2w_prefetch(M, gen, nslots, slot, pass + 1);
       const int n = (int)min((u32)MPM_PASS, total - q0);
       __syncwarp();
-      if (lane < 4) S.ch[lane] = mpm_chunk_ptr(M, gen, max(M.chunk_of[gen][(u64)slot * M.maxc + min(pass * 4u + (u32)lane, (u32)M.maxc - 1u)], 1u));
+      {
+        u32 cid = __shfl_sync(FULL, hdr, (lane & 3) + 2);
+        if (pass > 0 && lane < 4) cid = M.chunk_of[gen][(u64)slot * M.maxc + min(pass * 4u + (u32)lane, (u32)M.maxc - 1u)];
+        if (lane < 4) S.ch[lane] = mpm_chunk_ptr(M, gen, max(cid, 1u));
+      }
       S.cnt[cA] = 0, S.cnt[cB] = 0, S.hist[cA] = 0, S.hist[cB] = 0;
       __syncwarp();
       auto entry = [&](int t) -> const u8 * { return S.ch[t >> 8] + (t & (MPM_CHUNK - 1)) * 16; };
-      // ---- count: cell and rank inside the cell of every entry (eight loads in flight per lane) ----------------
-      for (int tb = 0; tb < n; tb += 256) {
+      // ---- count: cell and rank inside the cell of every entry (P2W_COUNT_U loads in flight per lane) ----------
+      for (int tb = 0; tb < n; tb += 32 * P2W_COUNT_U) {
         const int t0 = tb + lane;
-        float4 pv[8];
+        float4 pv[P2W_COUNT_U];
 #pragma unroll
-        for (int u = 0; u < 8; u++)
+        for (int u = 0; u < P2W_COUNT_U; u++)
           if (t0 + 32 * u < n) pv[u] = *(const float4 *)entry(t0 + 32 * u);
 #pragma unroll
-        for (int u = 0; u < 8; u++) {
+        for (int u = 0; u < P2W_COUNT_U; u++) {
           const int t = t0 + 32 * u;  // t >> 5 is warp-uniform
           if ((t & ~31) < n) {
             const bool live = t < n && pv[u].x != MPM_TOMB;
@@ -261,17 +260,22 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, P2W_CTAS) k_mpm_p2g(MpmDev M, 
             const u64 i01 = f2_pack(A00, A10), i2 = f2_pack(A20, 0.0f);
             const u64 j01 = f2_pack(A01, A11), j2 = f2_pack(A21, 0.0f);
             const u64 k01 = f2_pack(A02, A12), k2 = f2_pack(A22, 0.0f);
+            const u64 wy01 = f2_pack(w[0][1], w[1][1]), wz01 = f2_pack(w[0][2], w[1][2]);
 #pragma unroll
             for (int i = 0; i < 3; i++) {
               u64 q01 = r01, q2o = r2o;
+              float wxy[3];  // the weight products of two nodes come from one packed multiply
+              f2_unpack(f2_mul(f2_pack(w[i][0], w[i][0]), wy01), wxy[0], wxy[1]);
+              wxy[2] = w[i][0] * w[2][1];
 #pragma unroll
               for (int j = 0; j < 3; j++) {
-                const float wxy = w[i][0] * w[j][1];
                 u64 c01 = q01, c2o = q2o;
+                float wn[3];
+                f2_unpack(f2_mul(f2_pack(wxy[j], wxy[j]), wz01), wn[0], wn[1]);
+                wn[2] = wxy[j] * w[2][2];
 #pragma unroll
                 for (int kk = 0; kk < 3; kk++) {
-                  const float wn = wxy * w[kk][2];
-                  const u64 w2 = f2_pack(wn, wn);
+                  const u64 w2 = f2_pack(wn[kk], wn[kk]);
                   a01[(i * 3 + j) * 3 + kk] = f2_fma(w2, c01, a01[(i * 3 + j) * 3 + kk]);
                   a2m[(i * 3 + j) * 3 + kk] = f2_fma(w2, c2o, a2m[(i * 3 + j) * 3 + kk]);
                   if (kk < 2) c01 = f2_add(c01, k01), c2o = f2_add(c2o, k2);

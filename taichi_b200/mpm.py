@@ -221,6 +221,16 @@ class Mpm3D:
         self._ok(lib.b2_mpm_grid_to_dense(self.handle, _ptr(out)))
         return out
 
+    def grid_blocks(self):
+        """Active 4^3 blocks as (keys[n] sorted ascending, cells[n][64][4]); key = (bx*nb+by)*nb+bz."""
+        n = int(lib.b2_mpm_grid_blocks(self.handle, None, None, 0))
+        L.check()
+        keys, cells = np.zeros(max(n, 1), np.int32), np.zeros((max(n, 1), 64, 4), np.float32)
+        lib.b2_mpm_grid_blocks(self.handle, _ptr(keys), _ptr(cells), n)
+        L.check()
+        order = np.argsort(keys[:n])
+        return keys[:n][order], cells[:n][order]
+
     def active_blocks(self):
         """Sorted (nblocks, 3) block coordinates of the active 4^3 leaf blocks (listgen contents)."""
         n = lib.b2_listgen(self.tree, self.leaf)
