@@ -121,7 +121,7 @@ __device__ __forceinline__ u8 *mpm_chunk_ptr(const MpmDev &M, int gen, u32 id1) 
 // Appends one particle to the bin of block `key` in generation `gen`.  Must be called by all 32
 // lanes of the warp (valid = false for idle lanes): lanes that go to the same bin share one
 // atomicAdd (match_any), the lane that opens a new chunk allocates it, the others wait for it.
-__device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, bool valid, float4 p0, float4 p1, float4 p2, float4 p3, u32 id) {
+__device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, int cell, bool valid, float4 p0, float4 p1, float4 p2, float4 p3, u32 id) {
   const int lane = threadIdx.x & 31;
   int slot = -1;
   if (valid) {
@@ -190,12 +190,14 @@ __device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, bo
     ((float4 *)(ch + 2 * MPM_PLANE_BYTES))[i] = p2;
     ((float4 *)(ch + 3 * MPM_PLANE_BYTES))[i] = p3;
     ((u32 *)(ch + 4 * MPM_PLANE_BYTES))[i] = id;
+    (ch + MPM_CELL_OFF)[i] = (u8)cell;
   }
 }
 
-__device__ __forceinline__ int mpm_key_of_position(const MpmDev &M, float x, float y, float z, bool *ok) {
+// block key of a position; *cell = its cell inside the block ((base & 3) per axis, x-major)
+__device__ __forceinline__ int mpm_key_of_position(const MpmDev &M, float x, float y, float z, bool *ok, int *cell) {
   const float xp[3] = {x, y, z};
-  int b[3];
+  int b[3], l[3];
   // one unsigned compare per axis covers base < 0 and base + 2 >= n_grid; a NaN converts to base 0 and is caught once,
   // on the sum, below (this runs for every particle of G2P: 40 instructions before, 25 now)
   const unsigned lim = (unsigned)(M.n_grid - 2);
@@ -209,8 +211,10 @@ __device__ __forceinline__ int mpm_key_of_position(const MpmDev &M, float x, flo
       base = base < 0 ? 0 : M.n_grid - 3;
     }
     b[d] = base >> 2;
+    l[d] = base & 3;
   }
   *ok = good;
+  *cell = (l[0] << 4) | (l[1] << 2) | l[2];
   return mpm_key(M, b[0], b[1], b[2]);
 }
 
@@ -225,7 +229,7 @@ __global__ void __launch_bounds__(256) k_mpm_insert(MpmDev M, int gen, const flo
   for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < nround; p += (long long)gridDim.x * blockDim.x) {
     const bool valid = p < n;
     float4 p0 = make_float4(0, 0, 0, 1), p1 = make_float4(0, 0, 0, 0), p2 = p1, p3 = p1;
-    int key = 0;
+    int key = 0, cell = 0;
     u32 id = 0;
     if (valid) {
       p0 = make_float4(x[p * 3], x[p * 3 + 1], x[p * 3 + 2], J ? J[p] : 1.f);
@@ -238,10 +242,10 @@ __global__ void __launch_bounds__(256) k_mpm_insert(MpmDev M, int gen, const flo
       }
       id = ids ? (u32)ids[p] : (u32)(id0 + p);
       bool ok;
-      key = mpm_key_of_position(M, p0.x, p0.y, p0.z, &ok);
+      key = mpm_key_of_position(M, p0.x, p0.y, p0.z, &ok, &cell);
       if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)p);
     }
-    mpm_insert(M, gen, key, valid, p0, p1, p2, p3, id);
+    mpm_insert(M, gen, key, cell, valid, p0, p1, p2, p3, id);
   }
 }
 
@@ -543,7 +547,7 @@ __global__ void __launch_bounds__(G2P_PLAIN_THREADS, 3) k_mpm_g2p(MpmDev M, int 
       __syncthreads();
       const bool valid = tid < n;
       float4 o0 = make_float4(0.f, 0.f, 0.f, 1.f), o1 = make_float4(0.f, 0.f, 0.f, 0.f), o2 = o1, o3 = o1;
-      int nkey = 0;
+      int nkey = 0, ncell = 0;
       if (valid) {
         p0 = sP0[tid];
         id = sId[tid];
@@ -601,10 +605,10 @@ __global__ void __launch_bounds__(G2P_PLAIN_THREADS, 3) k_mpm_g2p(MpmDev M, int 
         o2 = make_float4(C01, C02, C10, C11);
         o3 = make_float4(C12, C20, C21, C22);
         bool ok;
-        nkey = mpm_key_of_position(M, nx, ny, nz, &ok);
+        nkey = mpm_key_of_position(M, nx, ny, nz, &ok, &ncell);
         if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)id);
       }
-      mpm_insert(M, gen ^ 1, nkey, valid, o0, o1, o2, o3, id);
+      mpm_insert(M, gen ^ 1, nkey, ncell, valid, o0, o1, o2, o3, id);
       __syncthreads();
     }
     // this generation's bin is consumed: leave it empty for the generation after next

@@ -4,8 +4,10 @@
 
 #define MPM_CHUNK 256            /* particles per bin chunk                      */
 #define MPM_PLANE_BYTES 4096     /* 256 x float4                                 */
-#define MPM_CHUNK_BYTES 17920    /* 4 float4 planes + 256 x u32 particle ids + 256 x u16 cell-sorted order */
+#define MPM_CHUNK_BYTES 18176    /* 4 float4 planes + 256 x u32 particle ids + 256 x u16 cell-sorted order + 256 x u8 cell */
 #define MPM_PERM_OFF 17408       /* byte offset of the u16 order plane (written by P2G, read by G2P) */
+#define MPM_CELL_OFF 17920       /* byte offset of the u8 cell plane: cell of the entry inside its 4^3 block, 0xff = tombstone (written with the
+                                    position by insert / G2P, read by P2G's count phase instead of the 16-byte position) */
 #define MPM_PASS 1024            /* bin entries per P2G pass (4 chunks) = per G2P pass when it follows P2G */
 #define MPM_MAXPASS 8            /* passes per bin: maxc * 256 / MPM_PASS                                  */
 #define MPM_SB 2048              /* particles cell-sorted per pass (shared-memory keys) */

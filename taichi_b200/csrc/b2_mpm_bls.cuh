@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
         const int t = t0 + tid;
         const bool valid = t < nlive;
         float4 o0 = make_float4(0.f, 0.f, 0.f, 1.f), o1 = make_float4(0.f, 0.f, 0.f, 0.f), o2 = o1, o3 = o1;
-        int nkey = -1;
+        int nkey = -1, ncell = 0;
         const float4 p0 = np0;
         u32 id = nid;
         if (t + G2P_THREADS < nlive) {
@@ -270,7 +270,7 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
           o2 = make_float4(C01, C02, C10, C11);
           o3 = make_float4(C12, C20, C21, C22);
           bool ok;
-          nkey = mpm_key_of_position(M, nx, ny, nz, &ok);
+          nkey = mpm_key_of_position(M, nx, ny, nz, &ok, &ncell);
           if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)id);
         }
         const bool stay = valid && nkey == key;
@@ -290,16 +290,20 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
               ((float4 *)(ch + 2 * MPM_PLANE_BYTES))[i] = o2;
               ((float4 *)(ch + 3 * MPM_PLANE_BYTES))[i] = o3;
               ((u32 *)(ch + 4 * MPM_PLANE_BYTES))[i] = id;
+              (ch + MPM_CELL_OFF)[i] = (u8)ncell;
             }
           }
         }
-        if (__any_sync(0xffffffffu, valid && !stay)) mpm_insert(M, g1, nkey, valid && !stay, o0, o1, o2, o3, id);
+        if (__any_sync(0xffffffffu, valid && !stay)) mpm_insert(M, g1, nkey, ncell, valid && !stay, o0, o1, o2, o3, id);
       }
       __syncthreads();
       // unused tail of the reservation (one entry per particle that left the block)
       for (u32 pos = base + sStay + tid; pos < base + (u32)nlive; pos += G2P_THREADS) {
         const u32 c = pos / MPM_CHUNK;
-        if (c <= c1) ((float4 *)sOut[c - c0])[pos % MPM_CHUNK] = make_float4(MPM_TOMB, 0.f, 0.f, 1.f);
+        if (c <= c1) {
+          ((float4 *)sOut[c - c0])[pos % MPM_CHUNK] = make_float4(MPM_TOMB, 0.f, 0.f, 1.f);
+          (sOut[c - c0] + MPM_CELL_OFF)[pos % MPM_CHUNK] = 0xffu;
+        }
       }
     }
     // this generation's bin is consumed: leave it empty for the generation after next

@@ -6,8 +6,9 @@
 // r1's kernel spent a third of its warp samples at CTA barriers between its five phases and moved every
 // particle through shared memory twice.  Here ONE WARP owns one occupied 4^3 block's bin from the first
 // load to the last red: there is no CTA-wide barrier anywhere in the kernel.
-//   count    the warp reads the position plane of a pass (<= MPM_PASS = 1024 bin entries = 4 whole chunks),
-//            finds every entry's cell and takes its rank inside the cell from the native integer ATOMS.ADD;
+//   count    the warp reads the u8 cell plane of a pass (<= MPM_PASS = 1024 bin entries = 4 whole chunks; the cell of
+//            an entry is written with its position by whoever bins it) and takes every entry's rank inside its cell
+//            from the native integer ATOMS.ADD;
 //   order    a warp scan of the 64 counts gives the cell-major order of the entries (kept in shared
 //            memory, and written to the chunks' u16 order plane for the G2P that follows);
 //   rank     the cells (cut into units of <= P2W_UNIT particles) are ranked by length with a counting sort, so that
@@ -49,7 +50,6 @@ struct P2WWarp {                      // private state of one warp
   };
   float4 pad[216];                    // (4+2)^3 nodes {sum w mv_x, sum w mv_y, sum w mv_z, sum w}
   unsigned short order[MPM_PASS];     // cell-major position -> entry of the pass
-  u32 liveb[MPM_PASS / 32];           // entry -> live (not a tombstone)
   int cnt[64];                        // particles per cell
   int hist[64];                       // units per length
   unsigned short cstart[64];          // first cell-major position of the cell
@@ -85,18 +85,6 @@ __device__ __forceinline__ void p2w_stencil(const MpmDev &M, const float4 p0, fl
     w[2][d] = 0.5f * (fx[d] - 0.5f) * (fx[d] - 0.5f);
   }
 }
-template <bool POT>
-__device__ __forceinline__ int p2w_cell_of(const MpmDev &M, const float4 p0) {
-  const float xp[3] = {p0.x, p0.y, p0.z};
-  int l[3];
-#pragma unroll
-  for (int d = 0; d < 3; d++) {
-    const float X = POT ? xp[d] * M.inv_dx : xp[d] / M.dx;
-    l[d] = ((int)(X - 0.5f)) & 3;
-  }
-  return (l[0] << 4) | (l[1] << 2) | l[2];
-}
-
 template <bool POT, int CTAS>
 __global__ void __launch_bounds__(P2W_WARPS * 32, CTAS) k_mpm_p2g(MpmDev M, int gen) {
   extern __shared__ __align__(16) unsigned char p2w_smem[];
@@ -122,11 +110,13 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, CTAS) k_mpm_p2g(MpmDev M, int 
   for (;;) {
     const u32 slot = next, hdr = hnext;
     if (slot >= nslots) break;
-    if (lane == 0) next = atomicAdd(&M.work_counter[0], 1u);
-    next = __shfl_sync(FULL, next, 0);
-    hnext = header(next);
+    if (lane == 0) next = atomicAdd(&M.work_counter[0], 1u);  // (read after the count phase: its latency is covered)
     const u32 total = __shfl_sync(FULL, hdr, 0);
-    if (total == 0) continue;
+    if (total == 0) {
+      next = __shfl_sync(FULL, next, 0);
+      hnext = header(next);
+      continue;
+    }
     const int key = (int)__shfl_sync(FULL, hdr, 1);
     int bx, by, bz;
     mpm_unkey(M, key, bx, by, bz);
@@ -145,28 +135,35 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, CTAS) k_mpm_p2g(MpmDev M, int 
       S.cnt[cA] = 0, S.cnt[cB] = 0, S.hist[cA] = 0, S.hist[cB] = 0;
       __syncwarp();
       auto entry = [&](int t) -> const u8 * { return S.ch[t >> 8] + (t & (MPM_CHUNK - 1)) * 16; };
-      // ---- count: cell and rank inside the cell of every entry (P2W_COUNT_U loads in flight per lane) ----------
-      for (int tb = 0; tb < n; tb += 32 * P2W_COUNT_U) {
-        const int t0 = tb + lane;
-        float4 pv[P2W_COUNT_U];
+      // ---- count: rank of every entry inside its cell.  The cells come from the chunks' u8 cell plane (written with the
+      // positions): one 16-byte load per lane covers 16 entries, the whole pass is two loads deep.
+      uint4 cbv[2];
 #pragma unroll
-        for (int u = 0; u < P2W_COUNT_U; u++)
-          if (t0 + 32 * u < n) pv[u] = *(const float4 *)entry(t0 + 32 * u);
+      for (int h = 0; h < 2; h++) {
+        const int t = h * 512 + lane * 16;
+        cbv[h] = make_uint4(~0u, ~0u, ~0u, ~0u);
+        if (t < n) cbv[h] = *(const uint4 *)(S.ch[t >> 8] + MPM_CELL_OFF + (t & (MPM_CHUNK - 1)));
+      }
+      auto cell_at = [&](int h, int e) -> int {  // cell of entry h * 512 + lane * 16 + e; >= 64: tombstone or past the end
+        const u32 wv = e < 4 ? cbv[h].x : e < 8 ? cbv[h].y : e < 12 ? cbv[h].z : cbv[h].w;
+        const int c = (int)((wv >> ((e & 3) * 8)) & 0xffu);
+        return h * 512 + lane * 16 + e < n ? c : 255;
+      };
 #pragma unroll
-        for (int u = 0; u < P2W_COUNT_U; u++) {
-          const int t = t0 + 32 * u;  // t >> 5 is warp-uniform
-          if ((t & ~31) < n) {
-            const bool live = t < n && pv[u].x != MPM_TOMB;
-            if (live) {
-              const int c = p2w_cell_of<POT>(M, pv[u]);
-              S.ck[t] = (unsigned short)((c << 10) | atomicAdd(&S.cnt[c], 1));
-            }
-            const u32 lb = __ballot_sync(FULL, live);
-            if (lane == 0) S.liveb[t >> 5] = lb;
+      for (int h = 0; h < 2; h++) {
+        if (h * 512 < n) {
+#pragma unroll
+          for (int e = 0; e < 16; e++) {
+            const int c = cell_at(h, e);
+            if (c < 64) S.ck[h * 512 + lane * 16 + e] = (unsigned short)((c << 10) | atomicAdd(&S.cnt[c], 1));
           }
         }
       }
       __syncwarp();
+      if (pass == 0) {  // the next bin's header travels while this bin is gathered
+        next = __shfl_sync(FULL, next, 0);
+        hnext = header(next);
+      }
       // ---- scan: cell-major start of every cell; rank of the cells by count ------------------------------------
       const int nA = S.cnt[cA], nB = S.cnt[cB];
       touched |= __reduce_or_sync(FULL, (nA > 0 ? p2w_touch_mask(cA) : 0u) | (nB > 0 ? p2w_touch_mask(cB) : 0u));
@@ -203,10 +200,17 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, CTAS) k_mpm_p2g(MpmDev M, int 
       for (int sg = 0; sg < uA - 1; sg++) S.unit[fA + sg] = (unsigned short)(cA | sg << 6);  // (no unit is longer than a full one)
       for (int sg = 0; sg < uB - 1; sg++) S.unit[fB + sg] = (unsigned short)(cB | sg << 6);
       // ---- order: cell-major position -> entry; the order plane of the chunks is what G2P will read ---------------
-      for (int t = lane; (t & ~31) < n; t += 32) {
-        if ((S.liveb[t >> 5] >> lane) & 1u) {
-          const int ck = S.ck[t];
-          S.order[S.cstart[ck >> 10] + (ck & 1023)] = (unsigned short)t;
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        if (h * 512 < n) {
+#pragma unroll
+          for (int e = 0; e < 16; e++) {
+            const int t = h * 512 + lane * 16 + e;
+            if (cell_at(h, e) < 64) {
+              const int ck = S.ck[t];
+              S.order[S.cstart[ck >> 10] + (ck & 1023)] = (unsigned short)t;
+            }
+          }
         }
       }
       __syncwarp();

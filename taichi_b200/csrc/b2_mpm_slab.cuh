@@ -143,18 +143,18 @@ __global__ void __launch_bounds__(256) k_mpm_insert_records(MpmDev M, int gen, c
     bool valid = p < n;
     MpmParticleRec rec;
     rec.p0 = make_float4(0, 0, 0, 1), rec.p1 = rec.p2 = rec.p3 = make_float4(0, 0, 0, 0), rec.id = 0;
-    int key = 0;
+    int key = 0, cell = 0;
     if (valid) {
       rec = recs[p];
       if (rec.p0.x == MPM_TOMB) {
         valid = false;
       } else {
         bool ok;
-        key = mpm_key_of_position(M, rec.p0.x, rec.p0.y, rec.p0.z, &ok);
+        key = mpm_key_of_position(M, rec.p0.x, rec.p0.y, rec.p0.z, &ok, &cell);
         if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)rec.id);
       }
     }
-    mpm_insert(M, gen, key, valid, rec.p0, rec.p1, rec.p2, rec.p3, rec.id);
+    mpm_insert(M, gen, key, cell, valid, rec.p0, rec.p1, rec.p2, rec.p3, rec.id);
   }
 }
 // compact export of the live particles with their ids (original order is the caller's business)
