@@ -415,11 +415,16 @@ TI_DLL_EXPORT int32_t b2_mpm_export_async(B2Mpm mpm, float *x, float *v, float *
 TI_DLL_EXPORT TiRuntime b2_mpm_runtime(B2Mpm mpm);
 TI_DLL_EXPORT int32_t b2_comm_unique_id(uint8_t *out128);
 TI_DLL_EXPORT B2Comm b2_comm_init(TiRuntime runtime, const uint8_t *id128, int32_t rank, int32_t world);
+/* Loopback communicator: all `world` slabs live in this process on one device; a message is a device-to-device copy
+ * into the peer's receive buffer (same call order and layout as the NCCL path).  Slabs created on it advance together
+ * through b2_slab_substep_lockstep (slabs[r] = rank r).  For single-GPU testing of the native driver. */
+TI_DLL_EXPORT B2Comm b2_comm_loopback(TiRuntime runtime, int32_t world);
 TI_DLL_EXPORT void b2_comm_destroy(B2Comm comm);
 TI_DLL_EXPORT B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_t world, int32_t block_lo, int32_t block_hi,
                                     int64_t cap_blocks, int64_t cap_particles);
 TI_DLL_EXPORT void b2_slab_destroy(B2Slab slab);
 TI_DLL_EXPORT int32_t b2_slab_substep(B2Slab slab, int32_t nsteps);
+TI_DLL_EXPORT int32_t b2_slab_substep_lockstep(B2Slab *slabs, int32_t world, int32_t nsteps);
 TI_DLL_EXPORT int32_t b2_slab_tune(B2Slab slab); /* message sizes := 2x last counts (synchronises) */
 /* Whole-domain particle diagnostics: out[0] live particles, [1..3] momentum, [4] kinetic energy, [5] sum J,
  * [6] max |v| (CFL), [7] max |J - 1|; local reduction + ncclAllReduce (SUM / MAX) over the slabs. Synchronises. */

@@ -16,7 +16,7 @@ def find(pat, start=0):
     raise KeyError(pat)
 
 
-marks = [("helpers", 1), ("stencil", find(r"void p2w_stencil")), ("cell_of", find(r"int p2w_cell_of")), ("kernel_head", find(r"__global__")),
+marks = [("helpers", 1), ("stencil", find(r"void p2w_stencil")), ("kernel_head", find(r"__global__")),
          ("count", find(r"---- count:")), ("scan+units", find(r"---- scan:")), ("order", find(r"---- order:")), ("roundsetup", find(r"---- rounds:")),
          ("main", find(r"pragma unroll 1", find(r"---- rounds:"))), ("padflush", find(r"---- pad:")), ("globalflush", find(r"---- flush:"))]
 
@@ -26,7 +26,7 @@ def phase(line):
     for n, l in marks:
         if line >= l:
             name = n
-    return {"stencil": "main", "helpers": "main", "cell_of": "count"}.get(name, name)
+    return {"stencil": "main", "helpers": "main"}.get(name, name)
 
 
 def rows(path):

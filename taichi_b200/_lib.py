@@ -187,10 +187,12 @@ SIGNATURES = {
     "b2_mpm_runtime": (C.c_void_p, [C.c_void_p]),
     "b2_comm_unique_id": (C.c_int32, [C.c_void_p]),
     "b2_comm_init": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
+    "b2_comm_loopback": (C.c_void_p, [C.c_void_p, C.c_int32]),
     "b2_comm_destroy": (None, [C.c_void_p]),
     "b2_slab_create": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64]),
     "b2_slab_destroy": (None, [C.c_void_p]),
     "b2_slab_substep": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "b2_slab_substep_lockstep": (C.c_int32, [C.POINTER(C.c_void_p), C.c_int32, C.c_int32]),
     "b2_slab_tune": (C.c_int32, [C.c_void_p]),
     "b2_mpm_export": (C.c_int64, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
     "b2_mpm_export_async": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),

@@ -107,19 +107,31 @@ __global__ void __launch_bounds__(256) k_mpm_extract_migrants(MpmDev M, int gen,
     if (!mine) continue;
     __syncthreads();
     if (threadIdx.x == 0) {
-      long long b = (long long)atomicAdd(count, total);  // tombstones are dropped below; count is fixed up by the reader via live flags
-      if (b + total > cap) {
-        b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, -3);
-        b = -1;
+      // reserve [b, b + total) only if it fits: a message that is full leaves the bin where it is (its particles travel
+      // with a later substep, nothing is lost) and the published count never exceeds what was written
+      long long b = -1;
+      u32 seen = *(volatile u32 *)count;
+      for (;;) {
+        if ((long long)seen + (long long)total > cap) {
+          b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, -3);
+          break;
+        }
+        const u32 prev = atomicCAS(count, seen, seen + total);
+        if (prev == seen) {
+          b = (long long)seen;
+          break;
+        }
+        seen = prev;
       }
       sBase = b;
     }
     __syncthreads();
     const long long base = sBase;
+    if (base < 0) continue;  // (uniform: sBase is shared)
     for (u32 q = threadIdx.x; q < total; q += blockDim.x) {
       const u8 *ch = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + q / MPM_CHUNK]);
       const u32 i = q % MPM_CHUNK;
-      if (base >= 0) {
+      {
         MpmParticleRec rec;
         rec.p0 = ((const float4 *)ch)[i];
         rec.p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[i];

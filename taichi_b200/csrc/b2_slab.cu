@@ -59,9 +59,15 @@ static NcclApi &nccl() {
     if (_r != 0) throw B2Error(TI_ERROR_INVALID_STATE, std::string(#expr) + ": " + nccl().GetErrorString(_r)); \
   } while (0)
 
+struct B2Slab_t;
 struct B2Comm_t {
   ncclComm_t comm = nullptr;
   int rank = 0, world = 1;
+  // loopback transport: all slabs of the domain live in THIS process on one device and one stream; a "send" is a
+  // device-to-device copy into the peer's receive buffer (same call order and message layout as the NCCL path), so
+  // the native driver can be tested at world > 1 on a single GPU.
+  bool loopback = false;
+  std::vector<B2Slab_t *> peers;
 };
 
 static const int64_t BLOCK_REC = 1040, PART_REC = 80, HEADER = 16;
@@ -75,6 +81,7 @@ struct B2Slab_t {
   // bytes actually put on the wire per message (<= capacity; see b2_slab_tune)
   int64_t sendA_bytes, recvA_bytes, sendB_bytes, recvB_bytes, sendL_bytes, recvL_bytes, sendR_bytes, recvR_bytes;
   uint8_t *sendA, *recvA, *sendB, *recvB, *sendL, *sendR, *recvL, *recvR;
+  bool tuned = false;   // message sizes only grow after the first tune
   uint32_t *sizes_dev;  // tune: 4 counts out, 4 counts in
   double *diag_dev;     // diagnostics: 8 doubles, reduced over the slabs in place
   std::vector<void *> allocs;
@@ -87,6 +94,7 @@ struct B2Slab_t {
   }
 };
 
+static uint8_t *recv_buffer(B2Slab_t *s, int which) { return which == 0 ? s->recvA : which == 1 ? s->recvB : which == 2 ? s->recvL : s->recvR; }
 static void require(bool ok, TiError code, const char *msg) {
   if (!ok) throw B2Error(code, msg);
 }
@@ -100,11 +108,17 @@ static void ok0(int32_t rc) {
   }
 }
 
-// one phase's messages: (send -> dst) and (recv <- src), both optional
-static void exchange(B2Slab_t *s, const void *send, int64_t sbytes, int dst, void *recv, int64_t rbytes, int src) {
+// one phase's messages: (send -> dst) and (recv <- src), both optional.  `which` names the receive buffer on the
+// destination rank (0 recvA, 1 recvB, 2 recvL, 3 recvR) for the loopback transport.
+static uint8_t *recv_buffer(B2Slab_t *s, int which);
+static void exchange(B2Slab_t *s, const void *send, int64_t sbytes, int dst, int which, void *recv, int64_t rbytes, int src) {
   if (dst < 0 && src < 0) return;
-  NcclApi &n = nccl();
   cudaStream_t st = s->rt->stream();
+  if (s->comm->loopback) {  // the receiving side is filled by the sender's copy
+    if (dst >= 0) B2_CUDA(cudaMemcpyAsync(recv_buffer(s->comm->peers[dst], which), send, (size_t)sbytes, cudaMemcpyDeviceToDevice, st));
+    return;
+  }
+  NcclApi &n = nccl();
   B2_NCCL(n.GroupStart());
   if (dst >= 0) B2_NCCL(n.Send(send, (size_t)sbytes, NCCL_UINT8, dst, s->comm->comm, st));
   if (src >= 0) B2_NCCL(n.Recv(recv, (size_t)rbytes, NCCL_UINT8, src, s->comm->comm, st));
@@ -134,6 +148,16 @@ B2Comm b2_comm_init(TiRuntime rt, const uint8_t *id128, int32_t rank, int32_t wo
   return c;
   B2_API_END(nullptr)
 }
+B2Comm b2_comm_loopback(TiRuntime rt, int32_t world) {
+  B2_API_BEGIN
+  require(rt != nullptr, TI_ERROR_ARGUMENT_NULL, "runtime");
+  require(world >= 1, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "world");
+  B2Comm_t *c = new B2Comm_t();
+  c->world = world, c->loopback = true;
+  c->peers.assign((size_t)world, nullptr);
+  return c;
+  B2_API_END(nullptr)
+}
 void b2_comm_destroy(B2Comm c) {
   if (!c) return;
   if (c->comm) nccl().CommDestroy(c->comm);
@@ -158,6 +182,10 @@ B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_t world, int32
   s->diag_dev = (double *)s->buf(64);
   s->sendA_bytes = s->recvA_bytes = s->sendB_bytes = s->recvB_bytes = bb;
   s->sendL_bytes = s->recvL_bytes = s->sendR_bytes = s->recvR_bytes = pb;
+  if (comm && comm->loopback) {
+    require(world == comm->world && rank >= 0 && rank < world, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "rank / world of the loopback communicator");
+    comm->peers[(size_t)rank] = s;
+  }
   return s;
   B2_API_END(nullptr)
 }
@@ -168,45 +196,85 @@ void b2_slab_destroy(B2Slab s) {
   delete s;
 }
 
+// The decomposed substep in four compute phases with the three exchanges between them (b2_mpm_slab.cuh):
+//   phase 0: clear, P2G, pack ghost layer | A | phase 1: add ghosts, grid-op, pack owned layer | B |
+//   phase 2: overwrite ghosts, G2P, extract migrants | C | phase 3: insert arrivals
+static void slab_phase(B2Slab_t *s, int ph) {
+  B2Mpm m = s->mpm;
+  const int64_t capA = (s->sendA_bytes - HEADER) / BLOCK_REC, capB = (s->sendB_bytes - HEADER) / BLOCK_REC;
+  const int64_t capL = (s->sendL_bytes - HEADER) / PART_REC, capR = (s->sendR_bytes - HEADER) / PART_REC;
+  switch (ph) {
+    case 0:
+      ok0(b2_mpm_clear_grid(m));
+      ok0(b2_mpm_p2g(m));
+      if (s->up >= 0) ok0(b2_mpm_pack_blocks(m, s->hi, s->sendA, capA));
+      break;
+    case 1:
+      if (s->down >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvA, (s->recvA_bytes - HEADER) / BLOCK_REC, 0));
+      ok0(b2_mpm_grid_op(m));
+      if (s->down >= 0) ok0(b2_mpm_pack_blocks(m, s->lo, s->sendB, capB));
+      break;
+    case 2:
+      if (s->up >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvB, (s->recvB_bytes - HEADER) / BLOCK_REC, 1));
+      ok0(b2_mpm_g2p(m));
+      if (s->down >= 0) ok0(b2_mpm_extract_migrants(m, 0, s->sendL, capL));
+      if (s->up >= 0) ok0(b2_mpm_extract_migrants(m, 1, s->sendR, capR));
+      break;
+    default:
+      if (s->up >= 0) ok0(b2_mpm_insert_records(m, s->recvR, (s->recvR_bytes - HEADER) / PART_REC));
+      if (s->down >= 0) ok0(b2_mpm_insert_records(m, s->recvL, (s->recvL_bytes - HEADER) / PART_REC));
+  }
+}
+static void slab_exchange(B2Slab_t *s, int ex) {
+  if (s->world == 1) return;
+  if (ex == 0) {
+    exchange(s, s->sendA, s->sendA_bytes, s->up, 0, s->recvA, s->recvA_bytes, s->down);
+  } else if (ex == 1) {
+    exchange(s, s->sendB, s->sendB_bytes, s->down, 1, s->recvB, s->recvB_bytes, s->up);
+  } else if (s->comm->loopback) {
+    exchange(s, s->sendL, s->sendL_bytes, s->down, 3, nullptr, 0, -1);  // my left migrants are the lower rank's arrivals from above
+    exchange(s, s->sendR, s->sendR_bytes, s->up, 2, nullptr, 0, -1);
+  } else {  // both directions in one NCCL group
+    NcclApi &n = nccl();
+    cudaStream_t st = s->rt->stream();
+    B2_NCCL(n.GroupStart());
+    if (s->down >= 0) {
+      B2_NCCL(n.Send(s->sendL, (size_t)s->sendL_bytes, NCCL_UINT8, s->down, s->comm->comm, st));
+      B2_NCCL(n.Recv(s->recvL, (size_t)s->recvL_bytes, NCCL_UINT8, s->down, s->comm->comm, st));
+    }
+    if (s->up >= 0) {
+      B2_NCCL(n.Send(s->sendR, (size_t)s->sendR_bytes, NCCL_UINT8, s->up, s->comm->comm, st));
+      B2_NCCL(n.Recv(s->recvR, (size_t)s->recvR_bytes, NCCL_UINT8, s->up, s->comm->comm, st));
+    }
+    B2_NCCL(n.GroupEnd());
+  }
+}
+
 int32_t b2_slab_substep(B2Slab s, int32_t nsteps) {
   B2_API_BEGIN
   require(s != nullptr, TI_ERROR_ARGUMENT_NULL, "slab");
-  B2Mpm m = s->mpm;
-  const int64_t cb = s->cap_blocks, cp = s->cap_particles;
-  // capacities the kernels enforce = what fits into the bytes that travel
-  const int64_t capA = (s->sendA_bytes - HEADER) / BLOCK_REC, capB = (s->sendB_bytes - HEADER) / BLOCK_REC;
-  const int64_t capL = (s->sendL_bytes - HEADER) / PART_REC, capR = (s->sendR_bytes - HEADER) / PART_REC;
-  (void)cb, (void)cp;
-  for (int it = 0; it < nsteps; it++) {
-    ok0(b2_mpm_clear_grid(m));
-    ok0(b2_mpm_p2g(m));
-    if (s->up >= 0) ok0(b2_mpm_pack_blocks(m, s->hi, s->sendA, capA));
-    exchange(s, s->sendA, s->sendA_bytes, s->up, s->recvA, s->recvA_bytes, s->down);
-    if (s->down >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvA, (s->recvA_bytes - HEADER) / BLOCK_REC, 0));
-    ok0(b2_mpm_grid_op(m));
-    if (s->down >= 0) ok0(b2_mpm_pack_blocks(m, s->lo, s->sendB, capB));
-    exchange(s, s->sendB, s->sendB_bytes, s->down, s->recvB, s->recvB_bytes, s->up);
-    if (s->up >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvB, (s->recvB_bytes - HEADER) / BLOCK_REC, 1));
-    ok0(b2_mpm_g2p(m));
-    if (s->down >= 0) ok0(b2_mpm_extract_migrants(m, 0, s->sendL, capL));
-    if (s->up >= 0) ok0(b2_mpm_extract_migrants(m, 1, s->sendR, capR));
-    if (s->world > 1) {  // both directions in one NCCL group
-      NcclApi &n = nccl();
-      cudaStream_t st = s->rt->stream();
-      B2_NCCL(n.GroupStart());
-      if (s->down >= 0) {
-        B2_NCCL(n.Send(s->sendL, (size_t)s->sendL_bytes, NCCL_UINT8, s->down, s->comm->comm, st));
-        B2_NCCL(n.Recv(s->recvL, (size_t)s->recvL_bytes, NCCL_UINT8, s->down, s->comm->comm, st));
-      }
-      if (s->up >= 0) {
-        B2_NCCL(n.Send(s->sendR, (size_t)s->sendR_bytes, NCCL_UINT8, s->up, s->comm->comm, st));
-        B2_NCCL(n.Recv(s->recvR, (size_t)s->recvR_bytes, NCCL_UINT8, s->up, s->comm->comm, st));
-      }
-      B2_NCCL(n.GroupEnd());
+  require(s->world == 1 || !s->comm->loopback, TI_ERROR_INVALID_STATE, "loopback slabs advance together: b2_slab_substep_lockstep");
+  for (int it = 0; it < nsteps; it++)
+    for (int ph = 0; ph < 4; ph++) {
+      slab_phase(s, ph);
+      if (ph < 3) slab_exchange(s, ph);
     }
-    if (s->up >= 0) ok0(b2_mpm_insert_records(m, s->recvR, (s->recvR_bytes - HEADER) / PART_REC));
-    if (s->down >= 0) ok0(b2_mpm_insert_records(m, s->recvL, (s->recvL_bytes - HEADER) / PART_REC));
-  }
+  return 0;
+  B2_API_END(-1)
+}
+// All slabs of a loopback communicator, phase by phase (what the ranks of an NCCL job do concurrently).
+int32_t b2_slab_substep_lockstep(B2Slab *slabs, int32_t world, int32_t nsteps) {
+  B2_API_BEGIN
+  require(slabs != nullptr, TI_ERROR_ARGUMENT_NULL, "slabs");
+  for (int r = 0; r < world; r++)
+    require(slabs[r] != nullptr && slabs[r]->world == world && slabs[r]->rank == r && (world == 1 || slabs[r]->comm->loopback), TI_ERROR_INVALID_ARGUMENT,
+            "slabs[r] must be rank r of one loopback communicator");
+  for (int it = 0; it < nsteps; it++)
+    for (int ph = 0; ph < 4; ph++) {
+      for (int r = 0; r < world; r++) slab_phase(slabs[r], ph);
+      if (ph < 3)
+        for (int r = 0; r < world; r++) slab_exchange(slabs[r], ph);
+    }
   return 0;
   B2_API_END(-1)
 }
@@ -218,6 +286,17 @@ int32_t b2_slab_diagnostics(B2Slab s, double *out8) {
   B2_API_BEGIN
   require(s != nullptr && out8 != nullptr, TI_ERROR_ARGUMENT_NULL, "slab/out");
   cudaStream_t st = s->rt->stream();
+  if (s->world > 1 && s->comm->loopback) {  // peers live in this process: reduce their vectors on the host
+    double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (B2Slab_t *p : s->comm->peers) {
+      double v[8];
+      ok0(b2_mpm_diagnostics(p->mpm, v));
+      for (int k = 0; k < 6; k++) acc[k] += v[k];
+      for (int k = 6; k < 8; k++) acc[k] = std::max(acc[k], v[k]);
+    }
+    memcpy(out8, acc, sizeof(acc));
+    return 0;
+  }
   ok0(b2_mpm_diagnostics_device(s->mpm, s->diag_dev));
   if (s->world > 1) {
     NcclApi &n = nccl();
@@ -244,10 +323,21 @@ int32_t b2_slab_tune(B2Slab s) {
   for (int k = 0; k < 4; k++) B2_CUDA(cudaMemcpyAsync(&cnt[k], src[k], 4, cudaMemcpyDeviceToHost, st));
   B2_CUDA(cudaStreamSynchronize(st));
   auto want = [&](uint32_t c, int64_t cap, int64_t rec) { return HEADER + std::min<int64_t>(cap, 2 * (int64_t)c + 256) * rec; };
-  uint32_t out[4];
   int64_t sb[4] = {want(cnt[0], s->cap_blocks, BLOCK_REC), want(cnt[1], s->cap_blocks, BLOCK_REC), want(cnt[2], s->cap_particles, PART_REC),
                    want(cnt[3], s->cap_particles, PART_REC)};
+  if (s->tuned) {  // ghost layers and migration grow as material reaches a boundary: after the first tune a message never shrinks
+    const int64_t prev[4] = {s->sendA_bytes, s->sendB_bytes, s->sendL_bytes, s->sendR_bytes};
+    for (int k = 0; k < 4; k++) sb[k] = std::max(sb[k], prev[k]);
+  }
+  s->tuned = true;
+  uint32_t out[4];
   for (int k = 0; k < 4; k++) out[k] = (uint32_t)((sb[k] - HEADER) / (k < 2 ? BLOCK_REC : PART_REC));
+  if (s->comm->loopback) {  // the peers are in this process: set their receive sizes directly
+    s->sendA_bytes = sb[0], s->sendB_bytes = sb[1], s->sendL_bytes = sb[2], s->sendR_bytes = sb[3];
+    if (s->up >= 0) s->comm->peers[s->up]->recvA_bytes = sb[0], s->comm->peers[s->up]->recvL_bytes = sb[3];
+    if (s->down >= 0) s->comm->peers[s->down]->recvB_bytes = sb[1], s->comm->peers[s->down]->recvR_bytes = sb[2];
+    return 0;
+  }
   // to up: {A, R}; to down: {B, L}.  from down: its {A, R}; from up: its {B, L}
   uint32_t to_up[2] = {out[0], out[3]}, to_down[2] = {out[1], out[2]}, from_down[2] = {0, 0}, from_up[2] = {0, 0};
   B2_CUDA(cudaMemcpyAsync(s->sizes_dev, to_up, 8, cudaMemcpyHostToDevice, st));

@@ -124,13 +124,13 @@ class NativeSlabDriver:
     ncclSend/ncclRecv on one stream).  torch.distributed is only used once, to hand rank 0's NCCL
     unique id to the other ranks."""
 
-    def __init__(self, slab, rank, world, cap_blocks=8192, cap_particles=131072):
-        import torch
-        import torch.distributed as dist
+    def __init__(self, slab, rank, world, cap_blocks=8192, cap_particles=131072, comm=None):
         L = slab.L
         self.slab, self.L, self.lib = slab, L, L.lib
-        self.comm = None
-        if world > 1:
+        self.comm, self.own_comm = comm, comm is None
+        if world > 1 and comm is None:
+            import torch
+            import torch.distributed as dist
             idt = torch.zeros(128, dtype=torch.uint8)
             if rank == 0:
                 buf = (C.c_uint8 * 128)()
@@ -167,6 +167,38 @@ class NativeSlabDriver:
         if self.handle:
             self.lib.b2_slab_destroy(self.handle)
             self.handle = None
+        if self.comm and self.own_comm:
+            self.lib.b2_comm_destroy(self.comm)
+        self.comm = None
+
+
+class LoopbackSlabGroup:
+    """All slabs of a domain in ONE process on one GPU, advanced by the native driver (b2_slab_substep_lockstep): the
+    NCCL send/recv pairs become device-to-device copies, everything else is the production path."""
+
+    def __init__(self, slabs, cap_blocks=8192, cap_particles=131072):
+        L = slabs[0].L
+        self.L, self.lib, self.world = L, L.lib, len(slabs)
+        self.comm = self.lib.b2_comm_loopback(self.lib.b2_mpm_runtime(slabs[0].handle), self.world)
+        L.check()
+        self.drivers = [NativeSlabDriver(s, r, self.world, cap_blocks, cap_particles, comm=self.comm) for r, s in enumerate(slabs)]
+        self.handles = (C.c_void_p * self.world)(*[d.handle for d in self.drivers])
+
+    def substep(self, n=1):
+        rc = self.lib.b2_slab_substep_lockstep(self.handles, self.world, n)
+        self.L.check()
+        assert rc == 0
+
+    def tune(self):
+        for d in self.drivers:
+            d.tune()
+
+    def diagnostics(self):
+        return self.drivers[0].diagnostics()
+
+    def destroy(self):
+        for d in self.drivers:
+            d.destroy()
         if self.comm:
             self.lib.b2_comm_destroy(self.comm)
             self.comm = None

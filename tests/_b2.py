@@ -22,7 +22,7 @@ def runtime():
     global _RT
     from taichi_b200 import _lib as L
     if _RT is None:
-        L.lib.b2_set_pool_size(C.c_uint64(2 << 30))
+        L.lib.b2_set_pool_size(C.c_uint64(8 << 30))  # the C4 full-size case needs 32768 x 131 KB containers
         _RT = L.lib.ti_create_runtime(L.TI_ARCH_CUDA, 0)
         L.check()
         assert _RT

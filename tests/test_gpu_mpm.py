@@ -197,7 +197,9 @@ def test_binned_one_substep_vs_oracle(rt, layout, bls):
     xr, vr, Cr, Jr = s.get_particles()
     assert np.allclose(xr, xs, rtol=0, atol=1e-6)
     assert np.allclose(vr, vs, rtol=1e-4, atol=1e-4)
-    assert np.allclose(Cr, Cs, rtol=1e-3, atol=2e-2)  # C = 4/dx * (cancelling sums): abs error ~ eps*|v|*4/dx
+    # C = 4/dx^2 * sum w g (x) dpos: a difference of O(|v|/dx) terms, so its error is the velocity tolerance (1e-4 of the
+    # velocity scale) divided by dx / 4: BASELINE.md section 6 "rel 1e-4", stated on the quantity that carries it
+    assert np.allclose(Cr, Cs, rtol=1e-4, atol=1e-4 * 4.0 * n_grid * max(1.0, float(np.abs(vs).max())))
     assert np.allclose(Jr, Js, rtol=1e-5)
     assert s.stats()["particles"] == N
     s.destroy()

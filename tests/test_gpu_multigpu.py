@@ -79,6 +79,80 @@ def test_emulated_slabs_on_one_gpu(world):
         s.destroy()
 
 
+@pytest.mark.parametrize("world", [2, 3])
+def test_native_driver_loopback(world):
+    """The production C++ driver (b2_slab.cu: kernels + three exchanges per substep, message tuning, whole-domain
+    diagnostics) at world = 2 and 3 on ONE GPU: the loopback communicator replaces every ncclSend/ncclRecv pair by a
+    device-to-device copy into the peer's receive buffer, everything else is the code an NCCL job runs.  The decomposed
+    result must match the CPU oracle (and so the single-domain solver) particle by particle."""
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    from taichi_b200 import multigpu as mg
+    from taichi_b200 import _lib as L
+    rt = get_rt()
+    x, v, Cm, J, ids = cloud()
+    owner = mg.partition_particles(x, N_GRID, world)
+    slabs = []
+    for r in range(world):
+        lo, hi = mg.slab_bounds(N_GRID // 4, world, r)
+        s = mg.CudaSlab(rt, N_GRID, N, DT, lo, hi)
+        sel = owner == r
+        s.set_particles(x[sel], v[sel], Cm[sel], J[sel], ids[sel])
+        slabs.append(s)
+    g = mg.LoopbackSlabGroup(slabs, cap_blocks=1024, cap_particles=8192)
+    before = [len(s.export(N)[4]) for s in slabs]
+    g.substep(STEPS // 2)
+    g.tune()                          # messages shrink to 2x the observed counts, then the run continues
+    g.substep(STEPS - STEPS // 2)
+    g.tune()                          # a second tune never shrinks a message
+    parts = [s.export(N) for s in slabs]
+    assert [len(p[4]) for p in parts] != before                   # particles migrated
+    for s, p in zip(slabs, parts):                                # ownership invariant
+        bx = (p[0][:, 0] * np.float32(N_GRID) - np.float32(0.5)).astype(np.int32) >> 2
+        assert ((bx >= s.lo) & (bx < s.hi)).all()
+    xs, vs, Cs, Js, *_ = oracle_mpm3d(N_GRID, x, v, Cm, J, DT, STEPS)
+    compare(parts, (xs, vs, Cs, Js))
+    d = g.diagnostics()
+    local = np.stack([s.diagnostics() for s in slabs])
+    assert d[0] == N and np.allclose(d[:6], local[:, :6].sum(0), rtol=1e-12) and np.array_equal(d[6:], local[:, 6:].max(0))
+    buf = C.create_string_buffer(256)
+    assert L.lib.b2_check_runtime_error(rt.handle, buf, 256) == 0, buf.value
+    g.destroy()
+    for s in slabs:
+        s.destroy()
+
+
+def test_full_migrant_message_keeps_the_particles():
+    """A migrant message that is too small must not destroy particles: the bin that does not fit stays where
+    it is, the published count covers written records only, the overflow raises the device error flag, and once the
+    capacity is there the particles travel."""
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    from taichi_b200 import multigpu as mg
+    from taichi_b200 import _lib as L
+    rt = get_rt()
+    x, v, Cm, J, ids = cloud()
+    world = 2
+    owner = mg.partition_particles(x, N_GRID, world)
+    slabs = []
+    for r in range(world):
+        lo, hi = mg.slab_bounds(N_GRID // 4, world, r)
+        s = mg.CudaSlab(rt, N_GRID, N, DT, lo, hi)
+        sel = owner == r
+        s.set_particles(x[sel], v[sel], Cm[sel], J[sel], ids[sel])
+        slabs.append(s)
+    g = mg.LoopbackSlabGroup(slabs, cap_blocks=1024, cap_particles=1)    # one record: far too few for this cloud
+    g.substep(STEPS)
+    buf = C.create_string_buffer(256)
+    assert L.lib.b2_check_runtime_error(rt.handle, buf, 256) != 0 and b"overflow" in buf.value.lower()
+    parts = [s.export(N) for s in slabs]
+    all_ids = np.concatenate([p[4] for p in parts])
+    assert len(all_ids) == N and len(np.unique(all_ids)) == N          # nobody lost, nobody duplicated
+    g.destroy()
+    for s in slabs:
+        s.destroy()
+
+
 def test_native_driver_world1_equals_plain_substep():
     """b2_slab_substep with world = 1 is the plain substep sequence (no NCCL touched)."""
     if not have_gpu():

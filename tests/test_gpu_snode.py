@@ -335,3 +335,39 @@ def test_error_convention(impls):
     assert L.lib.ti_create_runtime(4, 0) is None  # TI_ARCH_X64: no CPU path in this library
     assert L.last_error()[0] == -1
     L.lib.ti_set_last_error(0, None)
+
+
+@pytest.mark.parametrize("kind,frac", [("uniform", 0.01), ("clustered", 0.10)])
+def test_c4_full_size_lists_vs_oracle(impls, kind, frac):
+    """config[3] at full size (pointer(32).bitmasked(8).dense(4) = 1024^3, 16.7M blocks, 1 % uniform /
+    10 % clustered occupancy): the element lists of all three levels as sorted sets, bit-exact against the oracle
+    (VERDICT r1 #1d: the bench only compared counts), before and after a deactivate_all + GC + re-activation cycle."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench_listgen as bl
+    g, o = impls
+    n = 1024
+    tb = TreeBuilder()
+    p = tb.pointer(0, "ijk", n // 32)
+    b = tb.bitmasked(p, "ijk", 8)
+    d = tb.dense(b, "ijk", 4)
+    tb.place(d, 4)
+    blocks = bl.block_set(kind, frac, n // 4)
+    g.create(tb)
+    o.create(tb)
+    for impl in (g, o):
+        impl.activate(d, blocks * 4)
+    for lvl in (d, b, p):
+        lg, lo = g.list(lvl), o.list(lvl)
+        assert len(lg) == len(lo) and np.array_equal(lg, lo)
+    assert len(g.list(d)) == len(blocks)
+    assert np.array_equal(g.stats(p), o.stats(p))
+    half = blocks[: len(blocks) // 2]
+    for impl in (g, o):
+        impl.deactivate_all(p)
+        impl.activate(d, half * 4)
+    for lvl in (d, b, p):
+        assert np.array_equal(g.list(lvl), o.list(lvl))
+    assert np.array_equal(g.stats(p), o.stats(p))
+    o.create(TreeBuilder())   # release the oracle's host memory
