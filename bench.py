@@ -10,8 +10,10 @@ pointer->bitmasked->dense(4^3) grid, 8M particles (SURVEY 8d C3 cloud).  `value`
 particles resident in HBM; `e2e` re-uploads the particle state from pinned host memory through
 the C ABI (b2_mpm_set_particles) and reads the positions back (b2_mpm_get_particles) every step.
 N>1 (torchrun): one process per GPU, weak scaling (8M particles per rank).
---impl reference: the CPU restatement of the reference's kernels (oracle/mpm_oracle.c, multi-threaded
-fp32 CAS atomics as the reference's x64 backend) on the host cores; one step = ONE substep.
+--impl reference: the CPU restatement of the reference's kernels on a SPARSE grid (oracle/mpm_oracle.c
+orc_mpm3d_sparse_substeps: blocked active set, clear / grid-op over active blocks only, multi-threaded fp32 CAS
+atomics as the reference's x64 backend, the same deactivate_every life cycle) on all host cores, same `config`;
+each step executes a bounded sample (CPU_SAMPLE_SUBSTEPS of the step's 25 substeps) so that the run ends in minutes.
 """
 import argparse
 import ctypes as C
@@ -29,6 +31,8 @@ sys.path.insert(0, REPO)
 sys.path.insert(0, os.path.join(REPO, "tests"))
 
 SUBSTEPS = 25
+CPU_SAMPLE_SUBSTEPS = 2   # substeps a CPU step really executes (the metric is a rate: updates/s)
+DEACTIVATE_EVERY = 1      # the reference's sparse-MPM idiom: grid.deactivate_all() every substep (test_mpm_particle_list.py:9-53)
 WORKLOADS = {
     # name: (n_grid, particles, dt, layout, description)
     "c3": (512, 8 * 1024 * 1024, 2e-5, "pointer_bitmasked",
@@ -129,6 +133,14 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(self.rows)}
 
 
+def config_of(name, deactivate_every):
+    """The workload both arms run (identical dict in both JSON lines)."""
+    n_grid, n_p, dt, layout, desc = WORKLOADS[name]
+    return {"workload": desc, "n_grid": n_grid, "particles_per_gpu": n_p, "substeps_per_step": SUBSTEPS, "dt": dt,
+            "deactivate_every": deactivate_every if layout != "dense" else 0,
+            "l2": "particle state (>=512 MiB/substep) exceeds the 126 MB L2: no flush needed", "parallelism": "single GPU"}
+
+
 def hbm_peak():
     try:
         return float(json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
@@ -136,40 +148,45 @@ def hbm_peak():
         return 6650.0, "fallback"
 
 
-def cpu_reference(name, steps, warmup, sample_particles=None):
-    """The reference's CPU path restated (oracle/mpm_oracle.c mode 1): one substep per step."""
+def cpu_reference(name, steps, warmup, deactivate_every):
+    """The reference's CPU path restated on a sparse grid (oracle/mpm_oracle.c mode 1), all host cores.  A step runs
+    CPU_SAMPLE_SUBSTEPS substeps of the same cloud (state carried from step to step)."""
     from _desc import load_oracle
     orc = load_oracle()
-    n_grid, n_p, dt, _, desc = WORKLOADS[name]
+    n_grid, n_p, dt, layout, desc = WORKLOADS[name]
     cores = os.cpu_count() or 1
     threads = min(cores, 256)
     x, v, Cm, J = make_cloud(name, n_p, seed=3)
-    gv = np.zeros((n_grid,) * 3 + (3,), np.float32)
-    gm = np.zeros((n_grid,) * 3, np.float32)
     fp = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))  # noqa: E731
+    cap = min((n_grid // 4) ** 3, 1 << 18)
+    nblk = C.c_int32(0)
+    k = deactivate_every if layout != "dense" else 0
 
     def one():
-        orc.orc_mpm3d_substeps(n_grid, C.c_int64(n_p), fp(x), fp(v), fp(Cm), fp(J), C.c_float(dt), C.c_float(400.0),
-                               C.c_float(1.0), C.c_float(9.8), 3, 1, 1, threads, fp(gv), fp(gm), None, None)
+        rc = orc.orc_mpm3d_sparse_substeps(n_grid, C.c_int64(n_p), fp(x), fp(v), fp(Cm), fp(J), C.c_float(dt), C.c_float(400.0),
+                                           C.c_float(1.0), C.c_float(9.8), 3, CPU_SAMPLE_SUBSTEPS, 1, threads, k, cap, C.byref(nblk),
+                                           None, None, None)
+        assert rc == 0
     for _ in range(warmup):
         one()
     t0 = time.perf_counter()
     for _ in range(steps):
         one()
     dt_s = (time.perf_counter() - t0) / max(steps, 1)
-    return n_p / dt_s, dt_s * 1e3, threads, f"1 substep of {desc} per step (dense {n_grid}^3 host grid), {threads} threads, fp32 CAS atomics"
+    sample = (f"{CPU_SAMPLE_SUBSTEPS} of the {SUBSTEPS} substeps of every step on the full cloud ({n_p} particles, sparse blocked grid, "
+              f"{nblk.value} active 4^3 blocks, deactivate_every={k}), {threads} threads, fp32 CAS atomics (atomic.h:75)")
+    return n_p * CPU_SAMPLE_SUBSTEPS / dt_s, dt_s * 1e3, threads, sample
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    val, ms, threads, sample = cpu_reference(args.workload, max(1, args.steps), min(args.warmup, 1))
-    n_grid, n_p, dt, layout, desc = WORKLOADS[args.workload]
+    val, ms, threads, sample = cpu_reference(args.workload, max(1, args.steps), args.warmup, args.deactivate_every)
     line = {"impl": "reference", "metric": "MPM particle-updates/s", "value": val, "unit": "particle-updates/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "n_grid": n_grid, "particles": n_p, "substeps_per_step": 1, "dt": dt},
+            "config": config_of(args.workload, args.deactivate_every),
             "cpu_baseline": {"value": val, "unit": "particle-updates/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "particle-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
@@ -189,8 +206,9 @@ def run_ours(args):
     if world > 1:
         return run_slabs(args, world, rank, local)
     n_grid, n_p, dt, layout, desc = WORKLOADS[args.workload]
-    rt = tb.Runtime(local, device_memory_GB=4 if args.workload == "c3" else 1)
-    solver = tb.Mpm3D(rt, n_grid, n_p, dt, layout=layout)
+    rt = tb.Runtime(local, device_memory_GB=10 if args.workload == "c3" else 1)  # (the C4 listgen block needs 4.3 GB of containers)
+    k_life = args.deactivate_every if layout != "dense" else 0
+    solver = tb.Mpm3D(rt, n_grid, n_p, dt, layout=layout, deactivate_every=k_life)
     x, v, Cm, J = make_cloud(args.workload, n_p, seed=3, rank=rank)
     # pinned host buffers (e2e) and the initial upload
     hx, hv, hC, hJ = (torch.from_numpy(a).pin_memory() for a in (x, v, Cm, J))
@@ -261,25 +279,26 @@ def run_ours(args):
     e2e_value = world * n_p * SUBSTEPS / (e2e_ms / max(1, args.steps) * 1e-3)
     cells = st["active_blocks"] * 64
     peak, peak_kind = hbm_peak()
+    extras = {} if args.no_extras else bench_extras(args, rt, tb, solver, timed, peak)
     alg = {"p2g": 64 * n_p + 32 * cells, "g2p": 80 * n_p + 12 * cells, "clear": 16 * cells, "grid_op": 28 * cells}
     dom = max(("p2g", "g2p"), key=lambda k: phases[k])
     traffic = None  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (C3 only)
     try:
         if args.workload == "c3":
-            traffic = json.load(open(os.path.join(REPO, "profiles", "r1_traffic.json"))).get("k_mpm_" + dom)
+            traffic = json.load(open(os.path.join(REPO, "profiles", "r2_traffic.json"))).get("k_mpm_" + dom)
     except (OSError, ValueError):
         pass
     ach = alg[dom] / (phases[dom] * 1e-3) / 1e9 if phases[dom] > 0 else 0.0
-    sub_ms = sum(phases[k] for k in ("clear", "p2g", "listgen", "grid_op", "g2p"))
+    sub_ms = sum(phases[k] for k in ("deactivate_gc", "clear", "p2g", "listgen", "grid_op", "g2p"))
     sub_alg = 144 * n_p + 88 * cells
     line = {
         "metric": "MPM particle-updates/s", "value": value, "unit": "particle-updates/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "n_grid": n_grid, "particles_per_gpu": n_p, "substeps_per_step": SUBSTEPS, "dt": dt,
-                   "active_cells": cells, "l2": "particle state (>=512 MiB/substep) exceeds the 126 MB L2: no flush needed",
-                   "parallelism": "1 process/GPU, independent domains" if world > 1 else "single GPU"},
-        "e2e": {"value": e2e_value, "unit": "particle-updates/s", "h2d_bytes_per_step": int(n_p * 64), "d2h_bytes_per_step": int(n_p * 12)},
+        "config": config_of(args.workload, args.deactivate_every),
+        "state": {"active_cells": cells, "active_blocks": st["active_blocks"], "occupied_bins": st["occupied_slots"]},
+        "e2e": {"value": e2e_value, "unit": "particle-updates/s", "h2d_bytes_per_step": int(n_p * 64), "d2h_bytes_per_step": int(n_p * 12),
+                "returns": "positions only (12 of the 64 B/particle state); uploads and downloads of neighbouring steps are pipelined"},
         "gpu_launches": int(launches),
         "clocks": clocks.summary(),
         "roofline": {"bound": "hbm", "kernel": "k_mpm_" + dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
@@ -288,14 +307,62 @@ def run_ours(args):
                              "frac": (sub_alg / (sub_ms * 1e-3) / 1e9 / peak) if sub_ms else 0},
         "phase_ms": phases,
     }
+    line.update(extras)
     if rank == 0:
         if world == 1 and not args.no_cpu:
-            cv, cms, threads, sample = cpu_reference(args.workload, 1, 1)
+            cv, cms, threads, sample = cpu_reference(args.workload, 3, 1, args.deactivate_every)
             line["cpu_baseline"] = {"value": cv, "unit": "particle-updates/s", "cores": threads, "kind": "port", "sample": sample}
         emit(line)
     solver.destroy()
     if world > 1:
         dist.destroy_process_group()
+
+
+def bench_extras(args, rt, tb, solver, timed, peak):
+    """Numbers BASELINE.json names beside the headline: the sparse life cycle at K = 1 / 25 / never, the C4 listgen
+    microbenchmark (one case; bench_listgen.py runs all four) and the one figure the reference publishes for this path
+    (8M-f32 max-reduction: 57 us on an RTX 3090, docs/lang/articles/performance_tuning/performance.md:125-127)."""
+    import torch
+    lib = tb._lib.lib
+    out = {}
+    n_grid, n_p, dt, layout, desc = WORKLOADS[args.workload]
+    if layout != "dense":
+        life = {}
+        for k in (1, SUBSTEPS, 0):
+            lib.b2_mpm_set_deactivate_every(solver.handle, k)
+            solver.substep(SUBSTEPS)
+            solver.set_profiling(True)
+            ms = timed(lambda: solver.substep(SUBSTEPS), 2) / 2
+            ph = solver.phase_ms()
+            solver.set_profiling(False)
+            life["never" if k == 0 else f"every_{k}"] = {"value": n_p * SUBSTEPS / (ms * 1e-3), "ms_per_step": ms, "phase_ms": ph,
+                                                          "active_blocks": solver.stats()["active_blocks"]}
+        lib.b2_mpm_set_deactivate_every(solver.handle, args.deactivate_every)
+        out["lifecycle"] = life
+    if args.workload == "c3":
+        import bench_listgen
+        out["listgen"] = bench_listgen.run_case(lib, tb._lib, rt.handle, 1024, "uniform", 0.01, reps=10, cpu=not args.no_cpu, peak=peak)
+        n = 8 * 1024 * 1024
+        data = torch.rand(n, device="cuda")
+        res = torch.zeros(1, device="cuda")
+        fn = lambda: lib.b2_reduce_device(rt.handle, C.c_void_p(data.data_ptr()), n, 2, 0, C.c_void_p(res.data_ptr()))  # noqa: E731
+        fn()
+        torch.cuda.synchronize()
+        assert float(res.item()) == float(data.max().item())
+        big = torch.empty(256 * 1024 * 1024 // 4, device="cuda")   # 256 MiB written between the reps: the 32 MB input never sits in L2
+        ts = []
+        for _ in range(20):
+            big.fill_(1.0)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            e1.synchronize()
+            ts.append(e0.elapsed_time(e1) * 1e3)
+        us = float(np.median(ts))
+        out["reduce_8m_f32_us"] = {"value": us, "unit": "us", "op": "max", "launches": 2, "achieved_gbs": 4 * n / us / 1e3, "frac": 4 * n / us / 1e3 / peak,
+                                   "reference_published_us": 57.0, "reference_hw": "RTX 3090 (performance.md:125-127)", "l2": "flushed between reps"}
+    return out
 
 
 def run_slabs(args, world, rank, local):
@@ -419,6 +486,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--deactivate-every", type=int, default=DEACTIVATE_EVERY,
+                    help="sparse life cycle: deactivate_all + GC every K-th substep (0 = never; the reference idiom is 1)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the lifecycle / listgen / reduction blocks")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

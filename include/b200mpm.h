@@ -39,7 +39,11 @@ extern "C" {
 
 /* ===================================================================================== */
 /* Part 1: Taichi C-API subset (taichi_core.h / taichi_cuda.h)                            */
+/* Skipped when the reference's own <taichi/taichi.h> (built with -DTI_WITH_CUDA) was     */
+/* included first: Part 2 then compiles against the reference's declarations, which is    */
+/* how tests/test_cabi_reference.py proves that the two agree.                            */
 /* ===================================================================================== */
+#ifndef TAICHI_H
 #ifndef TI_C_API_VERSION
 #define TI_C_API_VERSION 1007000 /* taichi_core.h:229 */
 #endif
@@ -249,6 +253,34 @@ TI_DLL_EXPORT TiMemory TI_API_CALL ti_import_cuda_memory(TiRuntime runtime, void
 TI_DLL_EXPORT void TI_API_CALL ti_set_cuda_stream(void *stream);
 TI_DLL_EXPORT void TI_API_CALL ti_get_cuda_stream(void **stream);
 
+/* Entry points the reference's header-only C++ wrapper (c_api/include/taichi/cpp/taichi.hpp) refers to.
+   Capabilities: LLVM archs report none (the reference fills them for SPIR-V devices only); the ext setter is accepted and
+   ignored.  ti_create_aot_module takes TCM bytes (:1084): there is no TCM loader here -> TI_ERROR_NOT_SUPPORTED.
+   Image / sampler entry points are graphics: TI_ERROR_NOT_SUPPORTED, as the reference answers on LLVM archs
+   (taichi_core_impl.cpp:515-519); their argument structs stay opaque. */
+typedef enum TiCapability { TI_CAPABILITY_RESERVED = 0, TI_CAPABILITY_MAX_ENUM = 0xffffffff } TiCapability; /* :380-407 */
+typedef struct TiCapabilityLevelInfo { /* :413-416 */
+  TiCapability capability;
+  uint32_t level;
+} TiCapabilityLevelInfo;
+TI_DLL_EXPORT void TI_API_CALL ti_set_runtime_capabilities_ext(TiRuntime runtime, uint32_t capability_count,
+                                                               const TiCapabilityLevelInfo *capabilities); /* :943 */
+TI_DLL_EXPORT void TI_API_CALL ti_get_runtime_capabilities(TiRuntime runtime, uint32_t *capability_count,
+                                                           TiCapabilityLevelInfo *capabilities);          /* :951 */
+TI_DLL_EXPORT TiAotModule TI_API_CALL ti_create_aot_module(TiRuntime runtime, const void *tcm, uint64_t size); /* :1084 */
+struct TiImageAllocateInfo;
+struct TiSamplerCreateInfo;
+struct TiImageSlice;
+TI_DLL_EXPORT TiImage TI_API_CALL ti_allocate_image(TiRuntime runtime, const struct TiImageAllocateInfo *allocate_info); /* :989 */
+TI_DLL_EXPORT void TI_API_CALL ti_free_image(TiRuntime runtime, TiImage image);                                         /* :995 */
+TI_DLL_EXPORT TiSampler TI_API_CALL ti_create_sampler(TiRuntime runtime, const struct TiSamplerCreateInfo *create_info); /* :998 */
+TI_DLL_EXPORT void TI_API_CALL ti_destroy_sampler(TiRuntime runtime, TiSampler sampler);
+TI_DLL_EXPORT void TI_API_CALL ti_copy_image_device_to_device(TiRuntime runtime, const struct TiImageSlice *dst_image,
+                                                              const struct TiImageSlice *src_image);
+TI_DLL_EXPORT void TI_API_CALL ti_track_image_ext(TiRuntime runtime, TiImage image, uint32_t layout);
+TI_DLL_EXPORT void TI_API_CALL ti_transition_image(TiRuntime runtime, TiImage image, uint32_t layout);
+#endif /* TAICHI_H */
+
 /* ===================================================================================== */
 /* Part 2: SNode trees, struct-for built-ins, MLS-MPM                                      */
 /* ===================================================================================== */
@@ -320,6 +352,8 @@ TI_DLL_EXPORT int32_t b2_field_from_dense(B2Tree tree, int32_t place, const void
 TI_DLL_EXPORT int32_t b2_field_reduce(B2Tree tree, int32_t place, int32_t op, int32_t dtype, void *out_host);
 /* Dense-array reductions (range-for with TLS). */
 TI_DLL_EXPORT int32_t b2_reduce(TiRuntime runtime, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_host);
+/* same, enqueue only: the 4-byte result lands in device memory (no host round trip) */
+TI_DLL_EXPORT int32_t b2_reduce_device(TiRuntime runtime, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_dev);
 
 /* runtime-level */
 TI_DLL_EXPORT void b2_sync(TiRuntime runtime);
@@ -345,6 +379,9 @@ typedef struct B2MpmParams {
   int32_t block_local;/* 1: shared-memory pad P2G/G2P (ti.block_local), 0: plain atomics   */
   int32_t bls_activate_halo; /* 1: reproduce the CUDA-BLS epilogue's wider active set      */
   int32_t slab_lo, slab_hi;  /* owned range of 4^3-block indices along i ([0,n/4) = all)    */
+  int32_t deactivate_every;  /* K > 0 (sparse layouts): every K-th substep starts with deactivate_all on the grid's
+                                pointer level + GC (snode.py:286-304, offload.cpp:671-695 -- the reference's sparse-MPM idiom,
+                                test_gc.py:40-52); P2G re-activates exactly the touched blocks.  0: the active set only grows */
   int64_t max_particles;
 } B2MpmParams;
 
@@ -386,12 +423,13 @@ TI_DLL_EXPORT int64_t b2_mpm_grid_blocks(B2Mpm mpm, int32_t *keys_any, float *ce
 /* out_host[8]: {n_particles, n_active_blocks, n_bins, n_work_items, sum_m, sum_px, sum_py, sum_pz} (doubles) */
 TI_DLL_EXPORT int32_t b2_mpm_stats(B2Mpm mpm, double *out_host);
 /* per-phase device time of the last b2_mpm_substep call with profiling on, ms:
-   {clear, p2g, listgen, grid_op, g2p, rebin} */
+   {clear, p2g, listgen, grid_op, g2p, deactivate_gc} (deactivate_gc averaged over ALL substeps) */
 /* The solver keeps the leaf element list of its grid current incrementally (a block that P2G activates appends
  * itself; the reference regenerates every list before every struct-for, transforms/offload.cpp:174-264).  Call this
  * after changing the solver's tree through the b2_* tree API (activate / deactivate / gc): the next phase then
  * regenerates the lists from the root. */
 TI_DLL_EXPORT int32_t b2_mpm_invalidate_lists(B2Mpm mpm);
+TI_DLL_EXPORT int32_t b2_mpm_set_deactivate_every(B2Mpm mpm, int32_t k); /* B2MpmParams.deactivate_every, changeable between substeps */
 TI_DLL_EXPORT int32_t b2_mpm_set_profiling(B2Mpm mpm, int32_t on);
 TI_DLL_EXPORT int32_t b2_mpm_phase_ms(B2Mpm mpm, float *out_host6);
 

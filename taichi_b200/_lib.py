@@ -31,7 +31,7 @@ class B2MpmParams(C.Structure):
     _fields_ = [("n_grid", C.c_int32), ("layout", C.c_int32), ("dt", C.c_float), ("E", C.c_float),
                 ("p_rho", C.c_float), ("gravity", C.c_float), ("bound", C.c_int32),
                 ("block_local", C.c_int32), ("bls_activate_halo", C.c_int32),
-                ("slab_lo", C.c_int32), ("slab_hi", C.c_int32), ("max_particles", C.c_int64)]
+                ("slab_lo", C.c_int32), ("slab_hi", C.c_int32), ("deactivate_every", C.c_int32), ("max_particles", C.c_int64)]
 
 
 class TiMemoryAllocateInfo(C.Structure):
@@ -109,6 +109,16 @@ SIGNATURES = {
     "ti_launch_kernel": (None, [C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(TiArgument)]),
     "ti_launch_compute_graph": (None, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "ti_flush": (None, [C.c_void_p]),
+    "ti_set_runtime_capabilities_ext": (None, [C.c_void_p, C.c_uint32, C.c_void_p]),
+    "ti_get_runtime_capabilities": (None, [C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p]),
+    "ti_create_aot_module": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "ti_allocate_image": (C.c_void_p, [C.c_void_p, C.c_void_p]),
+    "ti_free_image": (None, [C.c_void_p, C.c_void_p]),
+    "ti_create_sampler": (C.c_void_p, [C.c_void_p, C.c_void_p]),
+    "ti_destroy_sampler": (None, [C.c_void_p, C.c_void_p]),
+    "ti_copy_image_device_to_device": (None, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ti_track_image_ext": (None, [C.c_void_p, C.c_void_p, C.c_uint32]),
+    "ti_transition_image": (None, [C.c_void_p, C.c_void_p, C.c_uint32]),
     "ti_wait": (None, [C.c_void_p]),
     "ti_load_aot_module": (C.c_void_p, [C.c_void_p, C.c_char_p]),
     "ti_destroy_aot_module": (None, [C.c_void_p]),
@@ -143,6 +153,7 @@ SIGNATURES = {
     "b2_field_from_dense": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p]),
     "b2_field_reduce": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "b2_reduce": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
+    "b2_reduce_device": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
     "b2_sync": (None, [C.c_void_p]),
     "b2_device_index": (C.c_int32, [C.c_void_p]),
     "b2_pool_bytes_used": (C.c_int64, [C.c_void_p]),
@@ -179,6 +190,7 @@ SIGNATURES = {
     "b2_jit_launch": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_uint64), C.c_int32]),
     "b2_jit_launch_range": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_uint64), C.c_int32]),
     "b2_mpm_set_profiling": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "b2_mpm_set_deactivate_every": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b2_mpm_phase_ms": (C.c_int32, [C.c_void_p, f32p]),
     "b2_mpm_pack_blocks": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]),
     "b2_mpm_unpack_blocks": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32]),

@@ -138,6 +138,45 @@ void ti_copy_memory_device_to_device(TiRuntime runtime, const TiMemorySlice *dst
   B2_CUDA(cudaMemcpyAsync((char *)dst->memory->dev + dst->offset, (char *)src->memory->dev + src->offset, src->size, cudaMemcpyDefault, runtime->stream()));
   B2_API_END_VOID
 }
+// Capabilities are a SPIR-V notion: the reference's LLVM runtimes report none (its CUDA runtime inherits the empty
+// default of taichi_core_impl.cpp); the ext setter is accepted and has nothing to override.
+void ti_set_runtime_capabilities_ext(TiRuntime runtime, uint32_t, const TiCapabilityLevelInfo *) {
+  B2_API_BEGIN
+  if (!runtime) throw B2Error(TI_ERROR_ARGUMENT_NULL, "runtime");
+  B2_API_END_VOID
+}
+void ti_get_runtime_capabilities(TiRuntime runtime, uint32_t *capability_count, TiCapabilityLevelInfo *) {
+  B2_API_BEGIN
+  if (!runtime) throw B2Error(TI_ERROR_ARGUMENT_NULL, "runtime");
+  if (!capability_count) throw B2Error(TI_ERROR_ARGUMENT_NULL, "capability_count");
+  *capability_count = 0;
+  B2_API_END_VOID
+}
+// TCM archives hold SPIR-V / LLVM modules of the reference's compiler: not loadable here (kernels are prebuilt tables or
+// NVRTC bodies).
+TiAotModule ti_create_aot_module(TiRuntime runtime, const void *tcm, uint64_t) {
+  B2_API_BEGIN
+  if (!runtime) throw B2Error(TI_ERROR_ARGUMENT_NULL, "runtime");
+  if (!tcm) throw B2Error(TI_ERROR_ARGUMENT_NULL, "tcm");
+  throw B2Error(TI_ERROR_NOT_SUPPORTED, "ti_create_aot_module: TCM modules are not supported (use ti_load_aot_module(\"builtin:...\"))");
+  B2_API_END(nullptr)
+}
+// graphics: unavailable on this box; same answer as the reference gives on LLVM archs (taichi_core_impl.cpp:515-519)
+static void not_supported(const char *what) { ti_set_last_error(TI_ERROR_NOT_SUPPORTED, what); }
+TiImage ti_allocate_image(TiRuntime, const TiImageAllocateInfo *) {
+  not_supported("ti_allocate_image");
+  return nullptr;
+}
+void ti_free_image(TiRuntime, TiImage) { not_supported("ti_free_image"); }
+TiSampler ti_create_sampler(TiRuntime, const TiSamplerCreateInfo *) {
+  not_supported("ti_create_sampler");
+  return nullptr;
+}
+void ti_destroy_sampler(TiRuntime, TiSampler) { not_supported("ti_destroy_sampler"); }
+void ti_copy_image_device_to_device(TiRuntime, const TiImageSlice *, const TiImageSlice *) { not_supported("ti_copy_image_device_to_device"); }
+void ti_track_image_ext(TiRuntime, TiImage, uint32_t) { not_supported("ti_track_image_ext"); }
+void ti_transition_image(TiRuntime, TiImage, uint32_t) { not_supported("ti_transition_image"); }
+
 void ti_flush(TiRuntime runtime) {
   B2_API_BEGIN
   require(runtime != nullptr, TI_ERROR_ARGUMENT_NULL, "runtime");  // no-op on LLVM archs (taichi_llvm_impl.cpp:129-132)

@@ -125,4 +125,7 @@ struct B2Tree_t {
   int64_t list_count(int target);  // synchronises
   void gc_async(int sid);
   void deactivate_all(int sid);
+  // one level only (listgen of that level + deactivate body + GC if it is a pointer SNode); reset_list: child list := empty
+  void deactivate_level_async(int sid);
+  void reset_list_async(int sid);
 };

@@ -634,6 +634,7 @@ struct B2Mpm_t {
   bool order_valid = false;  // P2G has left the cell order of the current generation in the chunks (G2P skips its sort)
   bool sparse = false;
   bool profiling = false;
+  long long substep_index = 0;  // substeps since the particles were set (deactivate_every counts on it)
   bool in_substep = false;  // inside substep(): k_mpm_clear resets the work counters / arena cursor for the phases that follow
   std::vector<cudaEvent_t> prof_events;
   double phase_sum[6] = {0, 0, 0, 0, 0, 0};
@@ -825,6 +826,7 @@ void B2Mpm_t::reset_bins() {
   gen = 0;
   n_particles = 0;
   order_valid = false;
+  substep_index = 0;
 }
 void B2Mpm_t::ensure_lists() {
   if (!lists_valid) {  // full regeneration (first use, or after the tree was changed behind the solver's back)
@@ -899,8 +901,9 @@ void B2Mpm_t::g2p() {
 }
 void B2Mpm_t::substep(int n) {
   cudaStream_t st = rt->stream();
+  constexpr int NE = 7;  // events per substep: [deactivate + GC] [clear] [p2g] [listgen] [grid-op] [g2p]
   if (profiling) {
-    while ((int)prof_events.size() < 6 * n) {
+    while ((int)prof_events.size() < NE * n) {
       cudaEvent_t e;
       B2_CUDA(cudaEventCreate(&e));
       prof_events.push_back(e);
@@ -911,27 +914,45 @@ void B2Mpm_t::substep(int n) {
     bool &f;
     ~Leave() { f = false; }
   } leave{in_substep};
-  for (int s = 0; s < n; s++) {
-    cudaEvent_t *e = profiling ? &prof_events[6 * s] : nullptr;
+  for (int s = 0; s < n; s++, substep_index++) {
+    cudaEvent_t *e = profiling ? &prof_events[NE * s] : nullptr;
     if (e) B2_CUDA(cudaEventRecord(e[0], st));
-    clear_grid();
+    if (sparse && prm.deactivate_every > 0 && substep_index % prm.deactivate_every == 0) {
+      // the reference's sparse life cycle, all enqueued: children first, then the pointer level, recycled containers
+      // zero-filled by the fused GC; the leaf list is regenerated (empty) and P2G activates what it touches
+      if (prm.layout == 1) {
+        // pointer -> bitmasked: the bitmasked container (cells + mask) IS the pointer level's NodeManager element, and the
+        // fused GC zero-fills recycled elements whole -- mask included -- so the children need no pass of their own:
+        // root listgen + deactivate body + GC = 3 launches; the leaf list and its bitmap are simply emptied
+        tree->deactivate_level_async(1);
+        tree->reset_list_async(2), tree->reset_list_async(M.leaf_sid);
+        B2_CUDA(cudaMemsetAsync(M.listed, 0, (size_t)((int64_t)M.nb * M.nb * M.nb + 31) / 32 * 4, st));
+        lists_valid = true;
+      } else {
+        tree->deactivate_all(1);
+        lists_valid = false;
+        ensure_lists();  // (full regeneration: counted with the life cycle, not with the clear)
+      }
+    }
     if (e) B2_CUDA(cudaEventRecord(e[1], st));
-    p2g();
+    clear_grid();
     if (e) B2_CUDA(cudaEventRecord(e[2], st));
-    ensure_lists();
+    p2g();
     if (e) B2_CUDA(cudaEventRecord(e[3], st));
-    grid_op();
+    ensure_lists();
     if (e) B2_CUDA(cudaEventRecord(e[4], st));
-    g2p();
+    grid_op();
     if (e) B2_CUDA(cudaEventRecord(e[5], st));
+    g2p();
+    if (e) B2_CUDA(cudaEventRecord(e[6], st));
   }
   if (profiling && n > 0) {  // one synchronisation per call, then accumulate every substep's phases
-    B2_CUDA(cudaEventSynchronize(prof_events[6 * (n - 1) + 5]));
+    B2_CUDA(cudaEventSynchronize(prof_events[NE * (n - 1) + NE - 1]));
     for (int s = 0; s < n; s++)
-      for (int k = 0; k < 5; k++) {
+      for (int k = 0; k < NE - 1; k++) {
         float ms;
-        B2_CUDA(cudaEventElapsedTime(&ms, prof_events[6 * s + k], prof_events[6 * s + k + 1]));
-        phase_sum[k] += ms;
+        B2_CUDA(cudaEventElapsedTime(&ms, prof_events[NE * s + k], prof_events[NE * s + k + 1]));
+        phase_sum[k == 0 ? 5 : k - 1] += ms;  // slots: clear, p2g, listgen, grid_op, g2p, deactivate_gc
       }
     phase_count += n;
   }
@@ -1172,6 +1193,11 @@ int32_t b2_mpm_diagnostics(B2Mpm m, double *out8) {
 int32_t b2_mpm_invalidate_lists(B2Mpm m) {
   if (!m) return -1;
   m->lists_valid = false;
+  return 0;
+}
+int32_t b2_mpm_set_deactivate_every(B2Mpm m, int32_t k) {
+  if (!m || k < 0) return -1;
+  m->prm.deactivate_every = k;
   return 0;
 }
 int32_t b2_mpm_set_profiling(B2Mpm m, int32_t on) {

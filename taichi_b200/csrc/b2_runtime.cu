@@ -799,13 +799,39 @@ struct BodyReduce {
   }
   __device__ void finish(B2TreeDev *) { b2_block_reduce_to<V>(acc, ident, op, dst); }
 };
+// 128-bit loads, four of them in flight per thread (8M f32 = 32 MB: the kernel is a pure HBM stream); dst is initialised by
+// CTA-independent means (k_set_u32) so the launch needs no host round trip
 template <typename V>
 __global__ void __launch_bounds__(256) k_reduce(const V *data, long long n, int op, V ident, V *dst) {
   V acc = ident;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    acc = b2_red_op(acc, data[i], op);
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  if ((((unsigned long long)data) & 15ull) == 0) {
+    const long long n4 = n >> 2;
+    const uint4 *d4 = (const uint4 *)data;
+    long long i = tid;
+    for (; i + 3 * nth < n4; i += 4 * nth) {
+      const uint4 a = d4[i], b = d4[i + nth], c = d4[i + 2 * nth], d = d4[i + 3 * nth];
+      const uint4 q[4] = {a, b, c, d};
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        V v[4];
+        memcpy(v, &q[k], 16);
+        acc = b2_red_op(b2_red_op(acc, v[0], op), b2_red_op(v[1], b2_red_op(v[2], v[3], op), op), op);
+      }
+    }
+    for (; i < n4; i += nth) {
+      V v[4];
+      const uint4 a = d4[i];
+      memcpy(v, &a, 16);
+      acc = b2_red_op(b2_red_op(acc, v[0], op), b2_red_op(v[1], b2_red_op(v[2], v[3], op), op), op);
+    }
+    for (long long j = (n4 << 2) + tid; j < n; j += nth) acc = b2_red_op(acc, data[j], op);
+  } else {
+    for (long long i = tid; i < n; i += nth) acc = b2_red_op(acc, data[i], op);
+  }
   b2_block_reduce_to<V>(acc, ident, op, dst);
 }
+__global__ void k_set_u32(u32 *dst, u32 v) { *dst = v; }
 
 // ------------------------------------------------------------------------------------------
 // coordinate-list kernels (activate / deactivate / is_active / read / write / dynamic)
@@ -982,6 +1008,21 @@ void B2Tree_t::gc_async(int sid) {
   B2_CUDA(cudaGetLastError());
 }
 
+void B2Tree_t::reset_list_async(int sid) {
+  check_snode(sid, "reset_list");
+  B2_CUDA(cudaMemsetAsync(&host_copy.lists[sid]->count, 0, 4, rt->stream()));
+}
+void B2Tree_t::deactivate_level_async(int sid) {
+  check_snode(sid, "deactivate");
+  if (s[sid].type != B2T_POINTER && s[sid].type != B2T_BITMASKED) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "deactivate_level: pointer or bitmasked SNode");
+  cudaStream_t st = rt->stream();
+  listgen_async(sid);
+  int block = (int)std::min<int64_t>(256, std::max<int64_t>(32, roundup(std::min<int64_t>(s[sid].num_cells, 1024), 32)));
+  k_struct_for<<<rt->num_sms * 8, block, 0, st>>>(dev, sid, BodyDeactivate{sid});
+  rt->count_launch();
+  if (s[sid].type == B2T_POINTER) gc_async(sid);
+  B2_CUDA(cudaGetLastError());
+}
 void B2Tree_t::deactivate_all(int sid) {
   check_snode(sid, "deactivate_all");
   for (int c : s[sid].ch)
@@ -989,11 +1030,7 @@ void B2Tree_t::deactivate_all(int sid) {
   cudaStream_t st = rt->stream();
   const int grid = rt->num_sms * 8;
   if (s[sid].type == B2T_POINTER || s[sid].type == B2T_BITMASKED) {
-    listgen_async(sid);
-    int block = (int)std::min<int64_t>(256, std::max<int64_t>(32, roundup(std::min<int64_t>(s[sid].num_cells, 1024), 32)));
-    k_struct_for<<<grid, block, 0, st>>>(dev, sid, BodyDeactivate{sid});
-    rt->count_launch();
-    if (s[sid].type == B2T_POINTER) gc_async(sid);
+    deactivate_level_async(sid);
   } else if (s[sid].type == B2T_DYNAMIC) {
     int par = s[sid].parent;
     listgen_async(par);
@@ -1348,32 +1385,43 @@ int32_t b2_field_reduce(B2Tree t, int32_t place, int32_t op, int32_t dtype, void
   return 0;
   B2_API_END(-1)
 }
-int32_t b2_reduce(TiRuntime rt, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_host) {
+// enqueue only: the 4-byte result lands in device memory
+int32_t b2_reduce_device(TiRuntime rt, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_dev) {
   B2_API_BEGIN
-  require(rt && out_host, TI_ERROR_ARGUMENT_NULL, "runtime/out");
+  require(rt && out_dev, TI_ERROR_ARGUMENT_NULL, "runtime/out");
   require(op >= 0 && op <= 2 && (dtype == 0 || dtype == 1), TI_ERROR_INVALID_ARGUMENT, "op/dtype");
   require(n == 0 || b2_is_device_pointer(data_dev), TI_ERROR_INVALID_ARGUMENT, "data must be a device pointer");
+  require(b2_is_device_pointer(out_dev), TI_ERROR_INVALID_ARGUMENT, "out must be a device pointer");
   cudaStream_t st = rt->stream();
-  u32 id = ident_bits(op, dtype);
-  u32 *dst = nullptr;
-  B2_CUDA(cudaMallocAsync((void **)&dst, 4, st));
-  B2_CUDA(cudaMemcpyAsync(dst, &id, 4, cudaMemcpyHostToDevice, st));
+  const u32 id = ident_bits(op, dtype);
+  k_set_u32<<<1, 1, 0, st>>>((u32 *)out_dev, id);
+  rt->count_launch();
   if (n > 0) {
-    const int grid = rt->grid_for(n, 256 * 8, 4);
+    const int grid = rt->grid_for(n, 256 * 16, 8);
     if (dtype == 0) {
       float idf;
       memcpy(&idf, &id, 4);
-      k_reduce<float><<<grid, 256, 0, st>>>((const float *)data_dev, n, op, idf, (float *)dst);
+      k_reduce<float><<<grid, 256, 0, st>>>((const float *)data_dev, n, op, idf, (float *)out_dev);
     } else {
-      k_reduce<int><<<grid, 256, 0, st>>>((const int *)data_dev, n, op, (int)id, (int *)dst);
+      k_reduce<int><<<grid, 256, 0, st>>>((const int *)data_dev, n, op, (int)id, (int *)out_dev);
     }
     rt->count_launch();
-    B2_CUDA(cudaGetLastError());
   }
-  B2_CUDA(cudaMemcpyAsync(out_host, dst, 4, cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaGetLastError());
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_reduce(TiRuntime rt, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_host) {
+  B2_API_BEGIN
+  require(rt && out_host, TI_ERROR_ARGUMENT_NULL, "runtime/out");
+  cudaStream_t st = rt->stream();
+  u32 *dst = nullptr;
+  B2_CUDA(cudaMallocAsync((void **)&dst, 4, st));
+  const int32_t rc = b2_reduce_device(rt, data_dev, n, op, dtype, dst);
+  if (rc == 0) B2_CUDA(cudaMemcpyAsync(out_host, dst, 4, cudaMemcpyDeviceToHost, st));
   rt->sync();
   cudaFreeAsync(dst, st);
-  return 0;
+  return rc;
   B2_API_END(-1)
 }
 

@@ -588,3 +588,69 @@ def test_c3_full_size_vs_oracle(rt):
     check_particles(s, xs, vs, Cs, Js, 1.0 / n_grid, max(1.0, float(np.abs(vs).max())))
     assert s.stats()["particles"] == N
     s.destroy()
+
+
+# --------------------------------------------------------------------------- sparse life cycle
+def test_deactivate_every_substep_life_cycle(rt):
+    """The reference's sparse-MPM idiom (snode.py:286-304 deactivate_all, offload.cpp:671-695 GC after the deactivating
+    task, test_gc.py:40-52, test_mpm_particle_list.py:9-53) inside the solver's own loop: with deactivate_every = 1 the
+    active-block set after EVERY substep is exactly the set of blocks the particles touched in that substep (bit-exact
+    against the oracle run with the same life cycle), the physics is unchanged, and the pointer level's allocator stays
+    bounded however long the run is (nodes are recycled through the GC, `_num_dynamically_allocated`)."""
+    import taichi_b200 as tb
+    lib = tb._lib.lib
+    n_grid, N, dt = 64, 20000, 2e-4
+    x0, v0, C0, J0 = cloud(41, N, lo=0.25, ext=0.3, vel=(4.0, -6.0, 2.0))     # fast: the cloud crosses many blocks
+    s = tb.Mpm3D(rt, n_grid, N, dt, layout="pointer_bitmasked", deactivate_every=1)
+    keep = tb.Mpm3D(rt, n_grid, N, dt, layout="pointer_bitmasked")            # never deactivates: the set only grows
+    for m in (s, keep):
+        m.set_particles(x0, v0, C0, J0)
+    xs, vs, Cs, Js = x0, v0, C0, J0
+    for step in range(12):
+        xb = xs
+        xs, vs, Cs, Js, keys_o, _ = oracle_sparse(n_grid, xs, vs, Cs, Js, dt, 1, deactivate_every=1, cap=4096)
+        s.substep(1)
+        keep.substep(1)
+        want = expected_blocks(xb, n_grid, halo=False)
+        got = s.active_blocks()
+        assert np.array_equal(got, want)
+        nb = n_grid // 4
+        assert np.array_equal(np.sort((got[:, 0] * nb + got[:, 1]) * nb + got[:, 2]), keys_o)
+        assert set(map(tuple, got)) <= set(map(tuple, keep.active_blocks()))
+    assert len(keep.active_blocks()) > len(s.active_blocks())                 # the cloud has left blocks behind
+    xr, vr, Cr, Jr = s.get_particles()
+    xk, vk, Ck, Jk = keep.get_particles()
+    assert np.allclose(xr, xs, rtol=0, atol=2e-6) and np.allclose(vr, vs, rtol=1e-4, atol=1e-3) and np.allclose(Jr, Js, rtol=1e-4)
+    assert np.allclose(xr, xk, rtol=0, atol=2e-6) and np.allclose(vr, vk, rtol=1e-4, atol=1e-3)
+    # allocator: bounded over 100 more frames of 4 substeps (every substep recycles and re-allocates the containers)
+    tree = lib.b2_mpm_tree(s.handle)
+    seen = []
+    for _ in range(100):
+        s.substep(4)
+        seen.append(int(lib.b2_num_dynamically_allocated(tree, 1)))
+    st = np.zeros(4, np.int32)
+    lib.b2_alloc_stats(tree, 1, st.ctypes.data_as(tb._lib.i32p))
+    assert max(seen) <= (n_grid // 32) ** 3 and st[0] <= 2 * (n_grid // 32) ** 3   # never more nodes than pointer cells (x2: ping-pong)
+    assert s.stats()["particles"] == N
+    buf = C.create_string_buffer(256)
+    assert lib.b2_check_runtime_error(rt.handle, buf, 256) == 0, buf.value
+    s.destroy()
+    keep.destroy()
+
+
+def test_deactivate_every_k(rt):
+    """deactivate_every = K > 1: the set is rebuilt on substeps 0, K, 2K, ... and grows in between."""
+    import taichi_b200 as tb
+    n_grid, N, dt, K = 64, 20000, 2e-4, 5
+    x0, v0, C0, J0 = cloud(42, N, lo=0.25, ext=0.3, vel=(4.0, -6.0, 2.0))
+    s = tb.Mpm3D(rt, n_grid, N, dt, layout="pointer_pointer", deactivate_every=K)
+    s.set_particles(x0, v0, C0, J0)
+    touched = set()
+    for step in range(2 * K + 1):
+        xb = s.get_particles()[0]
+        if step % K == 0:
+            touched = set()
+        touched |= set(map(tuple, expected_blocks(xb, n_grid, halo=False)))
+        s.substep(1)
+        assert set(map(tuple, s.active_blocks())) == touched
+    s.destroy()
