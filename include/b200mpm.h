@@ -383,6 +383,8 @@ typedef struct B2MpmParams {
                                 pointer level + GC (snode.py:286-304, offload.cpp:671-695 -- the reference's sparse-MPM idiom,
                                 test_gc.py:40-52); P2G re-activates exactly the touched blocks.  0: the active set only grows */
   int64_t max_particles;
+  int64_t max_bins;          /* occupied 4^3 blocks the particle bins can hold at once; 0 = max(4096, max_particles / 64).
+                                Vacated bins are recycled by a compaction pass every 64 substeps. */
 } B2MpmParams;
 
 TI_DLL_EXPORT B2Mpm b2_mpm_create(TiRuntime runtime, const B2MpmParams *params);
@@ -429,6 +431,7 @@ TI_DLL_EXPORT int32_t b2_mpm_stats(B2Mpm mpm, double *out_host);
  * after changing the solver's tree through the b2_* tree API (activate / deactivate / gc): the next phase then
  * regenerates the lists from the root. */
 TI_DLL_EXPORT int32_t b2_mpm_invalidate_lists(B2Mpm mpm);
+TI_DLL_EXPORT int32_t b2_mpm_set_compact_every(B2Mpm mpm, int32_t k);    /* substeps between bin-slot compactions (default 64, 0 = never) */
 TI_DLL_EXPORT int32_t b2_mpm_set_deactivate_every(B2Mpm mpm, int32_t k); /* B2MpmParams.deactivate_every, changeable between substeps */
 TI_DLL_EXPORT int32_t b2_mpm_set_profiling(B2Mpm mpm, int32_t on);
 TI_DLL_EXPORT int32_t b2_mpm_phase_ms(B2Mpm mpm, float *out_host6);

@@ -31,7 +31,7 @@ class B2MpmParams(C.Structure):
     _fields_ = [("n_grid", C.c_int32), ("layout", C.c_int32), ("dt", C.c_float), ("E", C.c_float),
                 ("p_rho", C.c_float), ("gravity", C.c_float), ("bound", C.c_int32),
                 ("block_local", C.c_int32), ("bls_activate_halo", C.c_int32),
-                ("slab_lo", C.c_int32), ("slab_hi", C.c_int32), ("deactivate_every", C.c_int32), ("max_particles", C.c_int64)]
+                ("slab_lo", C.c_int32), ("slab_hi", C.c_int32), ("deactivate_every", C.c_int32), ("max_particles", C.c_int64), ("max_bins", C.c_int64)]
 
 
 class TiMemoryAllocateInfo(C.Structure):
@@ -191,6 +191,7 @@ SIGNATURES = {
     "b2_jit_launch_range": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_uint64), C.c_int32]),
     "b2_mpm_set_profiling": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b2_mpm_set_deactivate_every": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "b2_mpm_set_compact_every": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b2_mpm_phase_ms": (C.c_int32, [C.c_void_p, f32p]),
     "b2_mpm_pack_blocks": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]),
     "b2_mpm_unpack_blocks": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32]),

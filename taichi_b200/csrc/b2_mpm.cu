@@ -128,26 +128,36 @@ __device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, in
     slot = ld_volatile_i32(&M.slot_of[key]);
     if (slot == -1) {
       if (atomicCAS(&M.slot_of[key], -1, -2) == -1) {  // this lane creates the slot
-        u32 s = atomicAdd(M.nslots, 1u);
+        const u32 s = atomicAdd(M.nslots, 1u);
         if (s >= (u32)M.max_slots) {
+          // no bin left: the particle is DROPPED and the error flag raised (never aliased onto another block's bin);
+          // the block stays without a slot, so it can get one after the next compaction
+          atomicSub(M.nslots, 1u);
           b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, key);
-          s = (u32)M.max_slots - 1;
+          __threadfence();
+          *(volatile int *)&M.slot_of[key] = -1;
+          slot = -3;
+        } else {
+          M.slot_key[s] = key;
+          __threadfence();
+          *(volatile int *)&M.slot_of[key] = (int)s;
+          slot = (int)s;
         }
-        M.slot_key[s] = key;
-        __threadfence();
-        *(volatile int *)&M.slot_of[key] = (int)s;
-        slot = (int)s;
       }
     }
   }
   __syncwarp();
-  if (valid && slot < 0) {
+  if (valid && (slot == -1 || slot == -2)) {  // somebody else is creating the slot: wait for the outcome
     unsigned ns = 8;
-    while ((slot = ld_volatile_i32(&M.slot_of[key])) < 0) {
+    while ((slot = ld_volatile_i32(&M.slot_of[key])) == -2) {
       __nanosleep(ns);
       if (ns < 256) ns *= 2;
     }
     __threadfence();
+  }
+  if (valid && slot < 0) {  // creation failed (here or in the creating lane): dropped, flag raised
+    b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, key);
+    valid = false;
   }
   const unsigned peers = __match_any_sync(0xffffffffu, valid ? slot : -1 - lane);
   const int leader = __ffs(peers) - 1;
@@ -167,9 +177,9 @@ __device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, in
       cslot = &M.chunk_of[gen][(u64)slot * M.maxc + c];
       if (i == 0) {
         u32 cid = atomicAdd(M.arena_next[gen], 1u);
-        if (cid >= M.arena_cap) {
+        if (cid >= M.arena_cap) {  // out of chunks: the data goes to the sink chunk (owned by no bin), flag raised
           b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, -1);
-          cid = M.arena_cap - 1;
+          cid = M.arena_cap;
         }
         __threadfence();
         *(volatile u32 *)cslot = cid + 1;
@@ -270,6 +280,35 @@ __global__ void __launch_bounds__(256) k_mpm_extract(MpmDev M, int gen, float *x
       if (C) {
         float *c = C + (u64)id * 9;
         c[0] = p1.w, c[1] = p2.x, c[2] = p2.y, c[3] = p2.z, c[4] = p2.w, c[5] = p3.x, c[6] = p3.y, c[7] = p3.z, c[8] = p3.w;
+      }
+    }
+  }
+}
+
+// Bin-slot compaction: a block gets a slot the first time a particle lands in it and material that moves on
+// leaves empty slots behind; every kernel walks all slots, and the table is finite.  Between two substeps only generation
+// `gen` holds particles: occupied slots are renumbered densely into the spare tables, vacated blocks lose their slot.
+__global__ void __launch_bounds__(256) k_mpm_compact(MpmDev M, int gen, u32 *count2, u32 *chunk2, int *key2, u32 *nslots2) {
+  const u32 ns = *M.nslots;
+  const int lane = threadIdx.x & 31;
+  for (u32 s0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; s0 < ns; s0 += gridDim.x * blockDim.x) {
+    const u32 s = s0 + lane;
+    const u32 cnt = s < ns ? M.count[gen][s] : 0u;
+    const unsigned m = __ballot_sync(0xffffffffu, cnt > 0);
+    u32 base = 0;
+    if (lane == 0 && m) base = atomicAdd(nslots2, (u32)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (s < ns) {
+      const int key = M.slot_key[s];
+      if (cnt > 0) {
+        const u32 n = base + __popc(m & ((1u << lane) - 1u));
+        count2[n] = cnt;
+        key2[n] = key;
+        M.slot_of[key] = (int)n;
+        const u32 nch = (cnt + MPM_CHUNK - 1) / MPM_CHUNK;
+        for (u32 c = 0; c < nch && c < (u32)M.maxc; c++) chunk2[(u64)n * M.maxc + c] = M.chunk_of[gen][(u64)s * M.maxc + c];
+      } else {
+        M.slot_of[key] = -1;
       }
     }
   }
@@ -635,6 +674,9 @@ struct B2Mpm_t {
   bool sparse = false;
   bool profiling = false;
   long long substep_index = 0;  // substeps since the particles were set (deactivate_every counts on it)
+  u32 *count_sp = nullptr, *chunk_sp = nullptr, *nslots_sp = nullptr;  // spare slot tables for compact_bins()
+  int *key_sp = nullptr;
+  int compact_every = 64;       // substeps between two bin-slot compactions
   bool in_substep = false;  // inside substep(): k_mpm_clear resets the work counters / arena cursor for the phases that follow
   std::vector<cudaEvent_t> prof_events;
   double phase_sum[6] = {0, 0, 0, 0, 0, 0};
@@ -667,6 +709,7 @@ struct B2Mpm_t {
   B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p);
   ~B2Mpm_t();
   void reset_bins();
+  void compact_bins();
   void ensure_lists();
   void clear_grid();
   void p2g();
@@ -748,7 +791,7 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
       (p.layout == 0 && tree->s[1].cell_size != 1024))
     throw B2Error(TI_ERROR_INVALID_STATE, "unexpected grid layout");
   const int64_t nblocks = (int64_t)nb * nb * nb;
-  M.max_slots = (int)std::min<int64_t>(nblocks, std::max<int64_t>(4096, p.max_particles / 64));
+  M.max_slots = (int)std::min<int64_t>(nblocks, p.max_bins > 0 ? p.max_bins : std::max<int64_t>(4096, p.max_particles / 64));
   M.maxc = 32;
   M.arena_cap = (u32)((p.max_particles + MPM_CHUNK - 1) / MPM_CHUNK + M.max_slots + 64);
   M.slot_of = dalloc<int>(nblocks, 0xFF);
@@ -759,11 +802,13 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
     M.chunk_of[g] = dalloc<u32>((size_t)M.max_slots * M.maxc);
     M.live[g] = dalloc<u32>((size_t)M.max_slots * MPM_MAXPASS);
     void *a = nullptr;
-    B2_CUDA(cudaMalloc(&a, (size_t)M.arena_cap * MPM_CHUNK_BYTES));
+    B2_CUDA(cudaMalloc(&a, ((size_t)M.arena_cap + 1) * MPM_CHUNK_BYTES));  // (+ the sink chunk of an exhausted arena)
     allocs.push_back(a);
     M.arena[g] = (u8 *)a;
     M.arena_next[g] = dalloc<u32>(4);
   }
+  count_sp = dalloc<u32>(M.max_slots), chunk_sp = dalloc<u32>((size_t)M.max_slots * M.maxc), key_sp = dalloc<int>(M.max_slots), nslots_sp = dalloc<u32>(4);
+  if (const char *e = getenv("B2_COMPACT_EVERY")) compact_every = atoi(e);
   M.dbg = getenv("B2_DBG") ? atoi(getenv("B2_DBG")) : 0;
   M.work_counter = dalloc<u32>(8);
   M.listed = dalloc<u32>((size_t)(nblocks + 31) / 32);
@@ -827,6 +872,17 @@ void B2Mpm_t::reset_bins() {
   n_particles = 0;
   order_valid = false;
   substep_index = 0;
+}
+void B2Mpm_t::compact_bins() {
+  cudaStream_t st = rt->stream();
+  B2_CUDA(cudaMemsetAsync(nslots_sp, 0, 16, st));
+  k_mpm_compact<<<rt->num_sms * 4, 256, 0, st>>>(M, gen, count_sp, chunk_sp, key_sp, nslots_sp);
+  rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  // the old tables become the (zeroed) spares
+  B2_CUDA(cudaMemsetAsync(M.count[gen], 0, (size_t)M.max_slots * 4, st));
+  B2_CUDA(cudaMemsetAsync(M.chunk_of[gen], 0, (size_t)M.max_slots * M.maxc * 4, st));
+  std::swap(M.count[gen], count_sp), std::swap(M.chunk_of[gen], chunk_sp), std::swap(M.slot_key, key_sp), std::swap(M.nslots, nslots_sp);
 }
 void B2Mpm_t::ensure_lists() {
   if (!lists_valid) {  // full regeneration (first use, or after the tree was changed behind the solver's back)
@@ -917,6 +973,7 @@ void B2Mpm_t::substep(int n) {
   for (int s = 0; s < n; s++, substep_index++) {
     cudaEvent_t *e = profiling ? &prof_events[NE * s] : nullptr;
     if (e) B2_CUDA(cudaEventRecord(e[0], st));
+    if (compact_every > 0 && substep_index > 0 && substep_index % compact_every == 0) compact_bins();
     if (sparse && prm.deactivate_every > 0 && substep_index % prm.deactivate_every == 0) {
       // the reference's sparse life cycle, all enqueued: children first, then the pointer level, recycled containers
       // zero-filled by the fused GC; the leaf list is regenerated (empty) and P2G activates what it touches
@@ -1193,6 +1250,11 @@ int32_t b2_mpm_diagnostics(B2Mpm m, double *out8) {
 int32_t b2_mpm_invalidate_lists(B2Mpm m) {
   if (!m) return -1;
   m->lists_valid = false;
+  return 0;
+}
+int32_t b2_mpm_set_compact_every(B2Mpm m, int32_t k) {
+  if (!m || k < 0) return -1;
+  m->compact_every = k;
   return 0;
 }
 int32_t b2_mpm_set_deactivate_every(B2Mpm m, int32_t k) {

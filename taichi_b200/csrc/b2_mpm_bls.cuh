@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
           u32 cid = atomicAdd(M.arena_next[g1], 1u);
           if (cid >= M.arena_cap) {
             b2_set_error(M.T->pool, B2E_BIN_OVERFLOW, -1);
-            cid = M.arena_cap - 1;
+            cid = M.arena_cap;  // the sink chunk
           }
           id1 = cid + 1;
           __threadfence();

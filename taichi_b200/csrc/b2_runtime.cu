@@ -120,7 +120,10 @@ int TiRuntime_t::check_error(std::string *msg) {
   sync();
   if (h.error == 0) return 0;
   static const char *names[] = {"", "device memory pool exhausted (raise device_memory_GB)", "element list overflow",
-                                "NodeManager chunk table overflow", "particle bin overflow", "assertion failed"};
+                                "NodeManager chunk table overflow",
+                                "particle bin overflow (more than 8192 particles in one 4^3 block, more occupied blocks than B2MpmParams.max_bins, or a full "
+                                "slab message)",
+                                "assertion failed"};
   if (msg) *msg = std::string(names[h.error < 6 ? h.error : 5]) + " [arg " + std::to_string(h.error_arg) + "]";
   int code = h.error;
   int zero[2] = {0, 0};

@@ -158,12 +158,12 @@ class Mpm3D:
     """
 
     def __init__(self, rt, n_grid, max_particles, dt, layout="pointer_bitmasked", E=400.0, p_rho=1.0, gravity=9.8,
-                 bound=3, block_local=True, bls_activate_halo=False, deactivate_every=0):
+                 bound=3, block_local=True, bls_activate_halo=False, deactivate_every=0, max_bins=0):
         self.rt = rt
         self.n_grid = n_grid
         p = L.B2MpmParams(n_grid=n_grid, layout=LAYOUTS[layout], dt=dt, E=E, p_rho=p_rho, gravity=gravity, bound=bound,
                           block_local=int(block_local), bls_activate_halo=int(bls_activate_halo), slab_lo=0, slab_hi=0,
-                          deactivate_every=int(deactivate_every), max_particles=max_particles)
+                          deactivate_every=int(deactivate_every), max_particles=max_particles, max_bins=int(max_bins))
         self.handle = lib.b2_mpm_create(rt.handle, C.byref(p))
         L.check()
         self.tree = lib.b2_mpm_tree(self.handle)

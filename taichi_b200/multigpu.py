@@ -47,7 +47,7 @@ class CudaSlab:
         self.lo, self.hi, self.nb, self.n_grid = lo, hi, n_grid // 4, n_grid
         p = L.B2MpmParams(n_grid=n_grid, layout=LAYOUTS[layout], dt=dt, E=kw.get("E", 400.0), p_rho=kw.get("p_rho", 1.0),
                           gravity=kw.get("gravity", 9.8), bound=kw.get("bound", 3), block_local=1, bls_activate_halo=0,
-                          slab_lo=lo, slab_hi=hi, max_particles=max_particles)
+                          slab_lo=lo, slab_hi=hi, deactivate_every=0, max_particles=max_particles, max_bins=0)
         self.handle = self.lib.b2_mpm_create(rt.handle, C.byref(p))
         L.check()
         self.device = torch.device("cuda", self.lib.b2_device_index(rt.handle))

@@ -654,3 +654,34 @@ def test_deactivate_every_k(rt):
         s.substep(1)
         assert set(map(tuple, s.active_blocks())) == touched
     s.destroy()
+
+
+def test_bin_slots_are_recycled(rt):
+    """a block gets a bin slot the first time a particle lands in it; without recycling a cloud that keeps moving
+    exhausts the table.  Here the table holds 24 bins, the cloud occupies <= 8 blocks at a time and crosses ~40 distinct
+    blocks: the periodic compaction returns vacated slots, nothing is dropped, no error is raised.  With compaction off
+    the same run overflows: the particles beyond the table are DROPPED and flagged (never aliased onto a foreign bin)."""
+    import taichi_b200 as tb
+    lib = tb._lib.lib
+    n_grid, N, dt = 64, 4000, 2e-4
+    rng = np.random.default_rng(77)
+    x0 = ((np.array([6.0, 31.0, 31.0]) + rng.random((N, 3)) * 2.0) / n_grid).astype(np.float32)   # straddles 2 x 2 blocks in y, z
+    v0 = np.tile(np.array([5.0, 0.0, 0.0], np.float32), (N, 1))
+    C0, J0 = np.zeros((N, 3, 3), np.float32), np.ones(N, np.float32)
+    buf = C.create_string_buffer(256)
+    for compact in (16, 0):
+        s = tb.Mpm3D(rt, n_grid, N, dt, layout="pointer_bitmasked", gravity=0.0, max_bins=24, deactivate_every=1)
+        assert lib.b2_mpm_set_compact_every(s.handle, compact) == 0
+        s.set_particles(x0, v0, C0, J0)
+        s.substep(700)                       # 5 * 2e-4 * 64 = 0.064 cells per substep: 45 cells = 11 block layers along x
+        st = s.stats()
+        err = lib.b2_check_runtime_error(rt.handle, buf, 256)
+        xr = s.get_particles()[0] if compact else None
+        if compact:
+            assert err == 0, buf.value
+            assert st["particles"] == N and st["slots"] <= 24
+            assert xr[:, 0].min() > (6.0 + 40.0) / n_grid and np.isfinite(xr).all()
+        else:
+            assert err != 0 and b"max_bins" in buf.value
+            assert st["particles"] < N         # dropped, and flagged
+        s.destroy()
