@@ -342,7 +342,8 @@ TI_DLL_EXPORT int32_t b2_read(B2Tree tree, int32_t place, const int32_t *coords_
 TI_DLL_EXPORT int32_t b2_dynamic_append_i32(B2Tree tree, int32_t dyn, const int32_t *coords_any, int64_t n, const int32_t *vals_any); /* ti.append */
 TI_DLL_EXPORT int32_t b2_dynamic_length(B2Tree tree, int32_t dyn, const int32_t *coords_any, int64_t n, int32_t *out_any);          /* ti.length */
 /* Whole-field operations = struct-fors with built-in bodies. */
-TI_DLL_EXPORT int32_t b2_field_fill(B2Tree tree, int32_t place, uint32_t value_bits);      /* field.fill over ACTIVE cells */
+TI_DLL_EXPORT int32_t b2_field_fill(B2Tree tree, int32_t place, uint64_t value_bits);      /* field.fill over ACTIVE cells; the value's bit
+                                                                                              pattern (1 / 2 / 4 / 8-byte places), zero-extended */
 /* dense row-major image of the field over `shape` (ndim = number of active axes of the place's
    path, ascending axis order); inactive cells read 0 (field.to_numpy, _kernels.py:40-60) */
 TI_DLL_EXPORT int32_t b2_field_to_dense(B2Tree tree, int32_t place, void *out_any);
@@ -489,6 +490,26 @@ TI_DLL_EXPORT int64_t b2_jit_log(B2JitKernel kernel, char *out, int64_t cap); /*
  * SNode ids (field f of the body); args: <= 16 64-bit slots (scalars bit-cast, DEVICE pointers). Asynchronous. */
 TI_DLL_EXPORT int32_t b2_jit_launch(B2JitKernel kernel, B2Tree tree, int32_t loop_snode, const int32_t *field_places,
                                     int32_t n_fields, const uint64_t *args, int32_t n_args);
+/* ti.block_local for run-time bodies (transforms/make_block_local.cpp:97-365, ir/scratch_pad.h:30-180).  One spec = one pad of
+ * field `field` (index into field_places): per pad axis d the loop's block covers `extent[d]` cells of the field's index space
+ * (0: the loop SNode's own shape, i.e. dense leaf loops; pid-list loops over a dynamic SNode pass the block size) starting at
+ * parent_coordinate * extent, and the body reaches offsets lo[d]..hi[d] (inclusive) around it, so the pad spans
+ * [lo, extent + hi) = ScratchPad::bounds.  mode 1: read-only (prologue loads, inactive / out-of-field cells read 0; body:
+ * c.bls_read<T>(slot, J)); mode 2 / 3 / 4: accumulate f32 / i32 / f64 (prologue zero-fills, body: c.bls_add<T>(slot, J, v), epilogue
+ * adds the pad back through an activating access -- every pad cell if halo != 0 (the reference's CUDA epilogue), else only
+ * non-zero sums (its x64 result)).  Also available in every struct-for body: c.reduce_add / reduce_min / reduce_max<T>(k, v), a
+ * thread-local accumulator reduced per CTA into the device pointer passed as argument k (make_thread_local.cpp:100-213). */
+typedef struct B2BlsSpec {
+  int32_t field, mode, ndim, halo;
+  int32_t axis[3], extent[3], lo[3], hi[3];
+} B2BlsSpec;
+TI_DLL_EXPORT int32_t b2_jit_launch_bls(B2JitKernel kernel, B2Tree tree, int32_t loop_snode, const int32_t *field_places, int32_t n_fields,
+                                        const uint64_t *args, int32_t n_args, const B2BlsSpec *bls, int32_t n_bls);
+/* ScratchPad geometry: block of block_size[d] loop cells, n_access accesses at offsets[a][d]  ->  low[d] = min offset,
+ * high[d] = block_size[d] + max offset, pad_size[d] = high - low (any output may be NULL); returns the number of pad cells
+ * (known answers: tests/cpp/analysis/bls_analyzer_test.cpp:51-77, tests/cpp/transforms/make_block_local_test.cpp:91-120). */
+TI_DLL_EXPORT int64_t b2_bls_pad_geometry(int32_t ndim, const int32_t *block_size, int32_t n_access, const int32_t *offsets, int32_t *low,
+                                          int32_t *high, int32_t *pad_size);
 /* Range-for (`for i in range(begin, end)`, gpu_parallel_range_for runtime.cpp:1541-1565) over a source holding
  *     B2_RANGE_BODY(c) { ... }                 // c.i = loop index; same field access and arguments
  * e.g. a particle loop scattering into a sparse grid with c.ref<float>(f, J) + atomicAdd (activates). */

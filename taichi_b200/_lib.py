@@ -27,6 +27,11 @@ class B2SNodeDesc(C.Structure):
                 ("dtype_bytes", C.c_int32), ("chunk_size", C.c_int32)]
 
 
+class B2BlsSpec(C.Structure):
+    _fields_ = [("field", C.c_int32), ("mode", C.c_int32), ("ndim", C.c_int32), ("halo", C.c_int32),
+                ("axis", C.c_int32 * 3), ("extent", C.c_int32 * 3), ("lo", C.c_int32 * 3), ("hi", C.c_int32 * 3)]
+
+
 class B2MpmParams(C.Structure):
     _fields_ = [("n_grid", C.c_int32), ("layout", C.c_int32), ("dt", C.c_float), ("E", C.c_float),
                 ("p_rho", C.c_float), ("gravity", C.c_float), ("bound", C.c_int32),
@@ -148,7 +153,7 @@ SIGNATURES = {
     "b2_read": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
     "b2_dynamic_append_i32": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
     "b2_dynamic_length": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
-    "b2_field_fill": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint32]),
+    "b2_field_fill": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint64]),
     "b2_field_to_dense": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p]),
     "b2_field_from_dense": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p]),
     "b2_field_reduce": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
@@ -188,6 +193,10 @@ SIGNATURES = {
     "b2_jit_destroy": (None, [C.c_void_p]),
     "b2_jit_log": (C.c_int64, [C.c_void_p, C.c_char_p, C.c_int64]),
     "b2_jit_launch": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_uint64), C.c_int32]),
+    "b2_jit_launch_bls": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_uint64), C.c_int32,
+                                      C.POINTER(B2BlsSpec), C.c_int32]),
+    "b2_bls_pad_geometry": (C.c_int64, [C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                        C.POINTER(C.c_int32)]),
     "b2_jit_launch_range": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_uint64), C.c_int32]),
     "b2_mpm_set_profiling": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b2_mpm_set_deactivate_every": (C.c_int32, [C.c_void_p, C.c_int32]),

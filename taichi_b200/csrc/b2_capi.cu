@@ -320,6 +320,15 @@ static float *nd_f32(const TiArgument &a, const char *what) {
   if (nd.shape.dim_count > 16 || nd.elem_shape.dim_count > 16) throw B2Error(TI_ERROR_ARGUMENT_OUT_OF_RANGE, std::string(what) + ".shape");
   return (float *)nd.memory->dev;
 }
+// ndarray argument with `elems` 4-byte elements of type `want` at least (every kernel argument goes through this: an undersized or
+// mistyped TiNdArray is TI_ERROR_ARGUMENT_OUT_OF_RANGE / INVALID_ARGUMENT, never an out-of-bounds device access)
+static void check_bytes(const TiArgument &a, uint64_t elems, const char *what);
+static float *nd_arg(const TiArgument &a, uint64_t elems, const char *what, TiDataType want = TI_DATA_TYPE_F32) {
+  float *p = nd_f32(a, what);
+  if (a.value.ndarray.elem_type != want) throw B2Error(TI_ERROR_INVALID_ARGUMENT, std::string(what) + (want == TI_DATA_TYPE_I32 ? ": expected an i32 ndarray" : ": expected an f32 ndarray"));
+  check_bytes(a, elems, what);
+  return p;
+}
 static void check_bytes(const TiArgument &a, uint64_t elems, const char *what) {
   const TiNdArray &nd = a.value.ndarray;
   uint64_t have = 1;
@@ -366,8 +375,8 @@ void ti_launch_kernel(TiRuntime runtime, TiKernel kernel, uint32_t arg_count, co
     case B2_K_INIT:
       need(3);
       particles(0);
-      a.v = nd_f32(args[1], "v");
-      a.J = nd_f32(args[2], "J");
+      a.v = nd_arg(args[1], (uint64_t)a.n_particles * D, "v");
+      a.J = nd_arg(args[2], (uint64_t)a.n_particles, "J");
       P.n_grid = 1;
       break;
     case B2_K_RESET:
@@ -387,16 +396,15 @@ void ti_launch_kernel(TiRuntime runtime, TiKernel kernel, uint32_t arg_count, co
       if (model == B2_MODEL_MPM128) {
         need(8);
         particles(0);
-        a.v = nd_f32(args[1], "v"), a.C = nd_f32(args[2], "C"), a.F = nd_f32(args[3], "F");
-        a.material = (int *)nd_f32(args[4], "material"), a.Jp = nd_f32(args[5], "Jp");
+        const uint64_t np_ = a.n_particles;
+        a.v = nd_arg(args[1], np_ * D, "v"), a.C = nd_arg(args[2], np_ * D * D, "C"), a.F = nd_arg(args[3], np_ * D * D, "F");
+        a.material = (int *)nd_arg(args[4], np_, "material", TI_DATA_TYPE_I32), a.Jp = nd_arg(args[5], np_, "Jp");
         grid(6, 7);
       } else {
         need(6);
         particles(0);
-        a.v = nd_f32(args[1], "v"), a.C = nd_f32(args[2], "C"), a.J = nd_f32(args[3], "J");
-        check_bytes(args[1], (uint64_t)a.n_particles * D, "v");
-        check_bytes(args[2], (uint64_t)a.n_particles * D * D, "C");
-        check_bytes(args[3], (uint64_t)a.n_particles, "J");
+        const uint64_t np_ = a.n_particles;
+        a.v = nd_arg(args[1], np_ * D, "v"), a.C = nd_arg(args[2], np_ * D * D, "C"), a.J = nd_arg(args[3], np_, "J");
         grid(4, 5);
       }
       break;
@@ -404,17 +412,15 @@ void ti_launch_kernel(TiRuntime runtime, TiKernel kernel, uint32_t arg_count, co
       if (model == B2_MODEL_MPM128) {
         need(4);
         particles(0);
-        a.v = nd_f32(args[1], "v"), a.C = nd_f32(args[2], "C");
+        a.v = nd_arg(args[1], (uint64_t)a.n_particles * D, "v"), a.C = nd_arg(args[2], (uint64_t)a.n_particles * D * D, "C");
         grid(3, ~0u);
       } else {
         need(5);
         particles(0);
-        a.v = nd_f32(args[1], "v"), a.C = nd_f32(args[2], "C"), a.J = nd_f32(args[3], "J");
+        const uint64_t np_ = a.n_particles;
+        a.v = nd_arg(args[1], np_ * D, "v"), a.C = nd_arg(args[2], np_ * D * D, "C"), a.J = nd_arg(args[3], np_, "J");
         grid(4, ~0u);
-        if (arg_count >= 6) {
-          a.pos3 = nd_f32(args[5], "pos");
-          check_bytes(args[5], (uint64_t)a.n_particles * 3, "pos");
-        }
+        if (arg_count >= 6) a.pos3 = nd_arg(args[5], np_ * 3, "pos");
       }
       break;
     default: throw B2Error(TI_ERROR_INVALID_ARGUMENT, "bad kernel handle");

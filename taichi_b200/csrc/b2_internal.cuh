@@ -19,7 +19,7 @@
 #endif
 
 #define B2_MAX_AXES 12
-#define B2_MAX_SNODES 64
+#define B2_MAX_SNODES 1024 /* taichi/inc/constants.h:7 taichi_max_num_snodes */
 #define B2_MAX_LEVELS 12
 #define B2_LISTGEN_MAX_ELEMENT 1024 /* taichi/inc/constants.h:28 */
 #define B2_LIST_MAX_CHUNKS 4096
@@ -385,6 +385,8 @@ __device__ __forceinline__ int b2_level_index(const B2TreeDev *T, const B2Path &
 }
 
 // Walks root..target. ACT: activate every level above the target (lower_access.cpp:254-279).
+// Where stores go after an allocation failure (never read back).
+static __device__ unsigned long long b2_sink[8];
 // Returns the container of the target SNode (or an ambient node) and the cell index in it.
 // *inactive is set when a non-activating walk crossed an inactive cell.
 template <bool ACT>
@@ -394,12 +396,12 @@ __device__ __forceinline__ u8 *b2_walk(B2TreeDev *T, const B2Path &P, const int 
   for (int l = 0; l + 1 < P.n; l++) {
     int sid = P.id[l];
     int i = b2_level_index(T, P, l, I);
-    if (ACT) {
+    if (ACT && !dead) {
       if (T->s[sid].type == B2T_POINTER) {
         node = b2_pointer_activate(T, sid, node, i);
-        if (!node) {  // pool exhausted: degrade to the ambient node, error already recorded
-          node = (u8 *)T->mgr[sid]->ambient;
-          dead = true;
+        if (!node) {  // pool exhausted (error already recorded): the rest of the walk only LOOKS UP inside the ambient node --
+          node = (u8 *)T->mgr[sid]->ambient;  // nothing is activated or stored through it; callers test *inactive and
+          dead = true;                        // send their store to b2_sink, so later reads of inactive cells stay zero
         }
       } else {
         b2_activate_cell(T, sid, node, i);

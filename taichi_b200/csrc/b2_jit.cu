@@ -63,6 +63,7 @@ struct B2JitKernel_t {
   B2JitTable *tab_dev = nullptr;  // launch table (fields + args), rewritten in stream order before every launch
   std::string log;
   size_t cubin_bytes = 0;
+  size_t bls_smem = 0;  // dynamic shared memory of the next struct-for launch (block-local pads)
 };
 
 static void jit_require(bool ok, TiError code, const char *msg) {
@@ -160,7 +161,8 @@ int64_t b2_jit_log(B2JitKernel k, char *out, int64_t cap) {
 }
 
 // fields + args -> the kernel's launch table, uploaded in stream order
-static void jit_upload_table(B2JitKernel k, B2Tree t, const int32_t *field_places, int32_t n_fields, const uint64_t *args, int32_t n_args) {
+static void jit_upload_table(B2JitKernel k, B2Tree t, const int32_t *field_places, int32_t n_fields, const uint64_t *args, int32_t n_args,
+                             int32_t loop_snode = -1, const B2BlsSpec *bls = nullptr, int32_t n_bls = 0) {
   jit_require(k != nullptr && t != nullptr, TI_ERROR_ARGUMENT_NULL, "kernel/tree");
   jit_require(k->rt == t->rt, TI_ERROR_INVALID_ARGUMENT, "kernel and tree belong to different runtimes");
   jit_require(n_fields >= 0 && n_fields <= B2_JIT_MAX_FIELDS, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "at most 8 fields per body");
@@ -181,13 +183,82 @@ static void jit_upload_table(B2JitKernel k, B2Tree t, const int32_t *field_place
     tab.f[i].bytes = p.dtype_bytes;
     tab.f[i].holder = p.parent;
   }
+  // block-local pads: geometry from the declared offsets (ScratchPad), staged per Element by the kernel
+  size_t smem = 0;
+  tab.n_bls = n_bls;
+  for (int b = 0; b < n_bls; b++) {
+    const B2BlsSpec &S = bls[b];
+    B2JitBls &B = tab.bls[b];
+    jit_require(S.field >= 0 && S.field < n_fields, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "block_local: field index");
+    jit_require(S.ndim >= 1 && S.ndim <= 3, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "block_local: 1..3 pad axes");
+    jit_require(S.mode >= 1 && S.mode <= 4, TI_ERROR_INVALID_ARGUMENT, "block_local: mode 1 read, 2 / 3 / 4 accumulate f32 / i32 / f64");
+    const B2SNodeHost &place = t->s[field_places[S.field]];
+    const B2SNodeHost &holder = t->s[place.parent];
+    B.field = S.field, B.mode = S.mode, B.ndim = S.ndim, B.halo = S.halo, B.bytes = place.dtype_bytes;
+    jit_require(B.bytes == 4 || B.bytes == 8, TI_ERROR_INVALID_ARGUMENT, "block_local: 4- or 8-byte fields");
+    jit_require(S.mode == 1 || (S.mode == 4) == (B.bytes == 8), TI_ERROR_INVALID_ARGUMENT, "block_local: accumulate mode does not match the field's width");
+    B.count = 1;
+    for (int d = 0; d < S.ndim; d++) {
+      const int a = S.axis[d];
+      jit_require(a >= 0 && a < B2_MAX_AXES, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "block_local: axis");
+      int ext = S.extent[d];
+      if (ext <= 0) ext = t->s[loop_snode].shape[a];  // the loop SNode's own block (dense leaf loops)
+      jit_require(ext >= 1 && S.lo[d] <= S.hi[d], TI_ERROR_INVALID_ARGUMENT, "block_local: extent / bounds");
+      B.axis[d] = a, B.extent[d] = ext, B.lo[d] = S.lo[d], B.hi[d] = S.hi[d];
+      B.size[d] = ext + S.hi[d] - S.lo[d];  // ScratchPad::pad_size = bounds.high - bounds.low
+      B.field_extent[d] = holder.from_root[a];
+      B.count *= B.size[d];
+    }
+    smem = (smem + 15) / 16 * 16;
+    B.smem_off = (int)smem;
+    smem += (size_t)B.count * B.bytes;
+  }
+  jit_require(smem <= 48 * 1024, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "block_local: the pads need more than 48 KB of shared memory");
+  k->bls_smem = smem;
   B2_CUDA(cudaSetDevice(t->rt->device));
   B2_CUDA(cudaMemcpyAsync(k->tab_dev, &tab, sizeof(tab), cudaMemcpyHostToDevice, t->rt->stream()));  // pageable source: staged before return
 }
 
+// ScratchPad geometry (ir/scratch_pad.h:30-180, analysis/bls_analyzer.cpp:8-106): a block of block_size[d] loop cells whose body
+// reaches the field at the given offsets needs the index range [low, high) = [min offset, block_size + max offset) per axis;
+// pad_size = high - low; the linear pad index of (i0, i1, ..) is row-major over pad_size.  Returns the number of pad cells.
+int64_t b2_bls_pad_geometry(int32_t ndim, const int32_t *block_size, int32_t n_access, const int32_t *offsets, int32_t *low, int32_t *high,
+                            int32_t *pad_size) {
+  B2_API_BEGIN
+  jit_require(ndim >= 1 && ndim <= B2_MAX_AXES && block_size && offsets && n_access >= 1, TI_ERROR_INVALID_ARGUMENT, "pad geometry arguments");
+  int64_t total = 1;
+  for (int d = 0; d < ndim; d++) {
+    int lo = offsets[d], hi = offsets[d];
+    for (int a = 1; a < n_access; a++) lo = std::min(lo, offsets[a * ndim + d]), hi = std::max(hi, offsets[a * ndim + d]);
+    const int l = lo, h = block_size[d] + hi;
+    if (low) low[d] = l;
+    if (high) high[d] = h;
+    if (pad_size) pad_size[d] = h - l;
+    total *= h - l;
+  }
+  return total;
+  B2_API_END(-1)
+}
+
+static int32_t jit_launch_struct_for(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t *field_places, int32_t n_fields, const uint64_t *args,
+                                     int32_t n_args, const B2BlsSpec *bls, int32_t n_bls);
 int32_t b2_jit_launch(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t *field_places, int32_t n_fields, const uint64_t *args, int32_t n_args) {
   B2_API_BEGIN
-  jit_upload_table(k, t, field_places, n_fields, args, n_args);
+  return jit_launch_struct_for(k, t, loop_snode, field_places, n_fields, args, n_args, nullptr, 0);
+  B2_API_END(-1)
+}
+int32_t b2_jit_launch_bls(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t *field_places, int32_t n_fields, const uint64_t *args, int32_t n_args,
+                          const B2BlsSpec *bls, int32_t n_bls) {
+  B2_API_BEGIN
+  jit_require(n_bls >= 0 && n_bls <= B2_JIT_MAX_BLS, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "at most 4 block-local pads per body");
+  jit_require(n_bls == 0 || bls != nullptr, TI_ERROR_ARGUMENT_NULL, "bls");
+  return jit_launch_struct_for(k, t, loop_snode, field_places, n_fields, args, n_args, bls, n_bls);
+  B2_API_END(-1)
+}
+static int32_t jit_launch_struct_for(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t *field_places, int32_t n_fields, const uint64_t *args,
+                                     int32_t n_args, const B2BlsSpec *bls, int32_t n_bls) {
+  {
+  jit_upload_table(k, t, field_places, n_fields, args, n_args, loop_snode, bls, n_bls);
   jit_require(k->fn != nullptr, TI_ERROR_INVALID_ARGUMENT, "this kernel has no B2_BODY (struct-for) entry");
   t->check_snode(loop_snode, "jit_launch");
   jit_require(t->s[loop_snode].type != B2T_PLACE && loop_snode != 0, TI_ERROR_INVALID_ARGUMENT, "loop SNode must be a non-root container SNode");
@@ -199,10 +270,10 @@ int32_t b2_jit_launch(B2JitKernel k, B2Tree t, int32_t loop_snode, const int32_t
   void *params[3] = {&dev, &sid, &tp};
   const int64_t nc = std::min<int64_t>(t->s[loop_snode].num_cells, 1024);
   const int block = (int)std::min<int64_t>(256, std::max<int64_t>(32, (nc + 31) / 32 * 32));
-  B2_CUDA(cudaLaunchKernel((const void *)k->fn, dim3(t->rt->num_sms * 8), dim3(block), params, 0, st));
+  B2_CUDA(cudaLaunchKernel((const void *)k->fn, dim3(t->rt->num_sms * 8), dim3(block), params, k->bls_smem, st));
   t->rt->count_launch();
   return 0;
-  B2_API_END(-1)
+  }
 }
 
 // `for i in range(begin, end)`: grid-stride loop, block 128 (the reference's default block_dim), grid capped at a

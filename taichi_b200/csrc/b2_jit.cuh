@@ -32,13 +32,52 @@ struct B2JitField {
   long long off;   // byte offset of the place inside that SNode's cell
   int bytes, holder;
 };
+// One block-local pad = ti.block_local(field) on a struct-for (transforms/make_block_local.cpp:97-365, ir/scratch_pad.h:30-180).
+// The loop's block is the Element's parent cell; per axis d of the pad (physical axis `axis[d]`) it covers
+// `extent[d]` cells of the FIELD's index space starting at corner = parent_coordinate * extent (BlockCornerIndexStmt,
+// make_block_local.cpp:196-203), and the body reaches offsets lo..hi around its cells, so the pad holds
+// bounds [lo, extent + hi) -- ScratchPad::bounds -- i.e. size = extent + hi - lo cells.
+// mode 1: read-only (prologue loads the pad; inactive / out-of-field cells read 0)
+// mode 2..4: accumulate f32 / i32 / f64 (prologue zero-fills, the body atomically adds into the pad, the epilogue adds the pad
+//            to the field through an ACTIVATING access: every pad cell when `halo`, else only cells that received a non-zero
+//            sum -- the reference's x64 result)
+#define B2_JIT_MAX_BLS 4
+struct B2JitBls {
+  int field, mode, ndim, halo;
+  int axis[3], extent[3], lo[3], hi[3];
+  int size[3], field_extent[3];
+  int count, bytes, smem_off, pad;
+};
 struct B2JitTable {
   int n_fields, n_args;
   unsigned long long args[B2_JIT_MAX_ARGS];
   B2JitField f[B2_JIT_MAX_FIELDS];
+  int n_bls, pad;
+  B2JitBls bls[B2_JIT_MAX_BLS];
 };
 
 #ifdef __CUDACC_RTC__  // everything below exists only in the run-time compiled translation unit
+__device__ __forceinline__ void b2_atomic_minmax(int *p, int v, bool mx) { mx ? atomicMax(p, v) : atomicMin(p, v); }
+__device__ __forceinline__ void b2_atomic_minmax(float *p, float v, bool mx) {  // CAS loop as atomic.h:75 (f32 min / max)
+  int old = *(volatile int *)p;
+  for (;;) {
+    const float f = __int_as_float(old);
+    if (mx ? !(v > f) : !(v < f)) return;
+    const int seen = atomicCAS((int *)p, old, __float_as_int(v));
+    if (seen == old) return;
+    old = seen;
+  }
+}
+__device__ __forceinline__ void b2_atomic_minmax(double *p, double v, bool mx) {
+  unsigned long long old = *(volatile unsigned long long *)p;
+  for (;;) {
+    const double f = __longlong_as_double((long long)old);
+    if (mx ? !(v > f) : !(v < f)) return;
+    const unsigned long long seen = atomicCAS((unsigned long long *)p, old, (unsigned long long)__double_as_longlong(v));
+    if (seen == old) return;
+    old = seen;
+  }
+}
 // Field access shared by both loop kinds (global pointer lowering, lower_access.cpp:42-281).
 struct B2Access {
   B2TreeDev *T;
@@ -60,8 +99,12 @@ struct B2Access {
   __device__ __forceinline__ V *walk(int f, const int *J) const {
     const B2JitField &F = tab->f[f];
     int cell;
-    u8 *node = b2_walk<ACT>(T, F.path, J, &cell, nullptr);
-    if (ACT) b2_activate_cell(T, F.holder, node, cell);
+    bool dead;
+    u8 *node = b2_walk<ACT>(T, F.path, J, &cell, &dead);
+    if (ACT) {
+      if (dead) return (V *)b2_sink;  // out of memory (flag raised): the store lands in the sink, never in the ambient node
+      b2_activate_cell(T, F.holder, node, cell);
+    }
     return (V *)(b2_lookup(T, F.holder, node, cell) + F.off);
   }
   // ti.is_active(ancestor, ti.rescale_index(field, ancestor, J)): `up` levels above the SNode that holds field f
@@ -100,7 +143,9 @@ struct B2Access {
     const B2JitField &F = tab->f[f];
     const B2SNodeDev &s = T->s[F.holder];
     int cell;
-    B2DynNode *d = (B2DynNode *)b2_walk<true>(T, F.path, J, &cell, nullptr);
+    bool dead;
+    B2DynNode *d = (B2DynNode *)b2_walk<true>(T, F.path, J, &cell, &dead);
+    if (dead) return -1;
     const u32 i = atomicAdd(&d->n, 1u);
     B2DynChunk *ch = b2_dynamic_chunk(T, F.holder, d, (int)(i / (u32)s.chunk_size));
     if (ch) *(V *)((u8 *)ch + 16 + (long long)(i % (u32)s.chunk_size) * s.cell_size + F.off) = v;
@@ -122,12 +167,74 @@ struct B2Access {
   }
 };
 
+// Thread-local reduction slots (make_thread_local.cpp:100-213: a 0-D destination becomes a thread-local accumulator; the
+// epilogue reduces the CTA -- warp shuffles, one shared-memory round -- and issues ONE atomic per CTA, codegen_cuda.cpp:358-392).
+// Slot k reduces into the device pointer passed as launch argument k.
+#define B2_TLS_SLOTS 4
+struct B2Tls {
+  unsigned long long bits[B2_TLS_SLOTS];  // the accumulator's bit pattern (f32 / i32 / f64)
+  int tag[B2_TLS_SLOTS];                  // 0 unused, else type (1 f32, 2 i32, 3 f64) | op << 4 (0 add, 1 min, 2 max)
+};
+template <typename V>
+struct B2TlsType;
+template <>
+struct B2TlsType<float> { static constexpr int id = 1; };
+template <>
+struct B2TlsType<int> { static constexpr int id = 2; };
+template <>
+struct B2TlsType<double> { static constexpr int id = 3; };
+template <typename V>
+__device__ __forceinline__ V b2_tls_combine(V a, V b, int op) {
+  return op == 0 ? a + b : op == 1 ? (b < a ? b : a) : (b > a ? b : a);
+}
+
 // struct-for: `for I in ti.grouped(loop_snode)`
 struct B2Ctx : B2Access {
   const B2SNodeDev *ts;  // the loop SNode
   const B2Element *E;    // the work item this cell belongs to
   int sid, j;            // loop SNode id, linear cell index inside E->node
   int I[B2_MAX_AXES];    // loop index (refine_coordinates, struct_llvm.cpp:171-188)
+  B2Tls *tls;            // this thread's reduction slots
+  unsigned char *smem;   // the Element's block-local pads
+
+  // ---- ti.block_local: pad `slot` at field index J (J must lie inside the declared bounds) ----
+  template <typename V>
+  __device__ __forceinline__ V *bls_ptr(int slot, const int *J) const {
+    const B2JitBls &B = tab->bls[slot];
+    int idx = 0;
+#pragma unroll
+    for (int d = 0; d < 3; d++)
+      if (d < B.ndim) idx = idx * B.size[d] + (J[B.axis[d]] - E->pcoord[B.axis[d]] * B.extent[d] - B.lo[d]);
+    return (V *)(smem + B.smem_off) + idx;
+  }
+  template <typename V>
+  __device__ __forceinline__ V bls_read(int slot, const int *J) const { return *bls_ptr<V>(slot, J); }
+  template <typename V>
+  __device__ __forceinline__ void bls_add(int slot, const int *J, V v) const { atomicAdd(bls_ptr<V>(slot, J), v); }
+
+  // ---- thread-local reductions: dst = launch argument k (a device pointer to V) ----
+  template <typename V>
+  __device__ __forceinline__ void reduce(int k, V v, int op) const {
+    union {
+      unsigned long long u;
+      V x;
+    } a;
+    a.u = 0;
+    if (tls->tag[k] == 0) {
+      a.x = v;
+      tls->tag[k] = B2TlsType<V>::id | op << 4;
+    } else {
+      a.u = tls->bits[k];
+      a.x = b2_tls_combine<V>(a.x, v, op);
+    }
+    tls->bits[k] = a.u;
+  }
+  template <typename V>
+  __device__ __forceinline__ void reduce_add(int k, V v) const { reduce<V>(k, v, 0); }
+  template <typename V>
+  __device__ __forceinline__ void reduce_min(int k, V v) const { reduce<V>(k, v, 1); }
+  template <typename V>
+  __device__ __forceinline__ void reduce_max(int k, V v) const { reduce<V>(k, v, 2); }
 
   template <typename V, bool ACT>
   __device__ __forceinline__ V *ptr(int f, const int *J) const {
@@ -170,22 +277,142 @@ struct B2RangeCtx : B2Access {
 
 #ifdef B2_JIT_HAS_BODY
 __device__ __forceinline__ void b2_body(B2Ctx &c);
-// parallel_struct_for (runtime.cpp:1422-1464): CTA <-> Element, thread <-> cell
+// pad cell p of pad B of the Element with parent coordinates pc -> field index J; false if it lies outside the field
+__device__ __forceinline__ bool b2_bls_coord(const B2JitBls &B, const int *pc, int p, int *J) {
+#pragma unroll
+  for (int a = 0; a < B2_MAX_AXES; a++) J[a] = 0;
+  bool inside = true;
+  for (int d = B.ndim - 1; d >= 0; d--) {
+    const int q = p % B.size[d];
+    p /= B.size[d];
+    const int x = pc[B.axis[d]] * B.extent[d] + B.lo[d] + q;
+    J[B.axis[d]] = x;
+    inside = inside && x >= 0 && x < B.field_extent[d];
+  }
+  return inside;
+}
+template <typename V>
+__device__ __forceinline__ void b2_tls_finish(const B2Access &A, B2Tls &tls, int k, int tag, unsigned long long *part) {
+  const int op = tag >> 4, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  union {
+    unsigned long long u;
+    V x;
+  } a, b;
+  a.u = tls.bits[k];
+  bool has = tls.tag[k] != 0;
+  // warp reduction over the lanes that hold a value, then one shared-memory round over the warps
+  for (int d = 16; d > 0; d >>= 1) {
+    b.u = __shfl_down_sync(0xffffffffu, a.u, d);
+    const bool bh = __shfl_down_sync(0xffffffffu, (int)has, d) != 0;
+    if (bh) a.x = has ? b2_tls_combine<V>(a.x, b.x, op) : b.x, has = true;
+  }
+  __syncthreads();
+  if (lane == 0) part[warp] = a.u, part[32 + warp] = has;
+  __syncthreads();
+  if (warp == 0) {
+    a.u = lane < nw ? part[lane] : 0ull;
+    has = lane < nw && part[32 + lane] != 0;
+    for (int d = 16; d > 0; d >>= 1) {
+      b.u = __shfl_down_sync(0xffffffffu, a.u, d);
+      const bool bh = __shfl_down_sync(0xffffffffu, (int)has, d) != 0;
+      if (bh) a.x = has ? b2_tls_combine<V>(a.x, b.x, op) : b.x, has = true;
+    }
+    if (lane == 0 && has) {
+      V *dst = A.arg<V *>(k);
+      if (op == 0)
+        atomicAdd(dst, a.x);
+      else
+        b2_atomic_minmax(dst, a.x, op == 2);
+    }
+  }
+}
+// parallel_struct_for (runtime.cpp:1422-1464): CTA <-> Element, thread <-> cell; with block-local pads the CTA stages them
+// before its Element's cells run and flushes the accumulating ones afterwards (make_block_local.cpp:97-365)
 extern "C" __global__ void __launch_bounds__(256) b2_jit_struct_for(B2TreeDev *T, int sid, const B2JitTable *tab) {
+  extern __shared__ __align__(16) unsigned char b2_bls_smem[];
+  __shared__ unsigned long long b2_tls_part[64];
   const B2SNodeDev &ts = T->s[sid];
   B2CList *L = T->lists[sid];
   const u32 ne = L->count;
+  const int nbls = tab->n_bls;
+  B2Tls tls;
+#pragma unroll
+  for (int k = 0; k < B2_TLS_SLOTS; k++) tls.bits[k] = 0ull, tls.tag[k] = 0;
+  B2Access A;
+  A.T = T, A.tab = tab;
   for (u32 e = blockIdx.x; e < ne; e += gridDim.x) {
     const B2Element E = *(const B2Element *)b2_list_get(L, e);
+    if (nbls) {  // prologue
+      __syncthreads();
+      for (int b = 0; b < nbls; b++) {
+        const B2JitBls &B = tab->bls[b];
+        for (int p = threadIdx.x; p < B.count; p += blockDim.x) {
+          int J[B2_MAX_AXES];
+          unsigned long long v = 0ull;
+          if (B.mode == 1 && b2_bls_coord(B, E.pcoord, p, J)) {
+            if (B.bytes == 8)
+              v = *A.walk<unsigned long long, false>(B.field, J);
+            else
+              v = *A.walk<unsigned int, false>(B.field, J);
+          }
+          if (B.bytes == 8)
+            ((unsigned long long *)(b2_bls_smem + B.smem_off))[p] = v;
+          else
+            ((unsigned int *)(b2_bls_smem + B.smem_off))[p] = (unsigned int)v;
+        }
+      }
+      __syncthreads();
+    }
     for (int j0 = E.lo; j0 < E.hi; j0 += blockDim.x) {
       const int j = j0 + threadIdx.x;
       if (j < E.hi && b2_is_active(ts, E.node, j)) {
         B2Ctx c;
-        c.T = T, c.tab = tab, c.ts = &ts, c.E = &E, c.sid = sid, c.j = j;
+        c.T = T, c.tab = tab, c.ts = &ts, c.E = &E, c.sid = sid, c.j = j, c.tls = &tls, c.smem = b2_bls_smem;
         b2_refine(ts, E.pcoord, c.I, j);
         b2_body(c);
       }
     }
+    if (nbls) {  // epilogue
+      __syncthreads();
+      for (int b = 0; b < nbls; b++) {
+        const B2JitBls &B = tab->bls[b];
+        if (B.mode < 2) continue;
+        for (int p = threadIdx.x; p < B.count; p += blockDim.x) {
+          int J[B2_MAX_AXES];
+          if (!b2_bls_coord(B, E.pcoord, p, J)) continue;
+          if (B.mode == 2) {
+            const float v = ((const float *)(b2_bls_smem + B.smem_off))[p];
+            if (v != 0.0f || B.halo) atomicAdd(A.walk<float, true>(B.field, J), v);
+          } else if (B.mode == 3) {
+            const int v = ((const int *)(b2_bls_smem + B.smem_off))[p];
+            if (v != 0 || B.halo) atomicAdd(A.walk<int, true>(B.field, J), v);
+          } else {
+            const double v = ((const double *)(b2_bls_smem + B.smem_off))[p];
+            if (v != 0.0 || B.halo) atomicAdd(A.walk<double, true>(B.field, J), v);
+          }
+        }
+      }
+    }
+  }
+  // thread-local reductions: one atomic per CTA and slot (the tag is the same in every thread that used the slot)
+  __shared__ int b2_tls_tag[B2_TLS_SLOTS];
+  if (threadIdx.x < B2_TLS_SLOTS) b2_tls_tag[threadIdx.x] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < B2_TLS_SLOTS; k++)
+    if (tls.tag[k]) b2_tls_tag[k] = tls.tag[k];  // (every user of a slot writes the same value)
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < B2_TLS_SLOTS; k++) {
+    const int tag = b2_tls_tag[k];
+    if (tag == 0) continue;
+    const int ty = tag & 15;
+    if (ty == 1)
+      b2_tls_finish<float>(A, tls, k, tag, b2_tls_part);
+    else if (ty == 2)
+      b2_tls_finish<int>(A, tls, k, tag, b2_tls_part);
+    else
+      b2_tls_finish<double>(A, tls, k, tag, b2_tls_part);
   }
 }
 #endif

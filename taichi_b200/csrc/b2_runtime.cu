@@ -268,7 +268,7 @@ void B2Tree_t::check_snode(int id, const char *what) const {
 B2Tree_t::B2Tree_t(TiRuntime_t *rt_, const B2SNodeDesc *desc, int n) : rt(rt_) {
   if (!desc) throw B2Error(TI_ERROR_ARGUMENT_NULL, "desc");
   if (n <= 0 || n > B2_MAX_SNODES || desc[0].type != B2_ROOT)
-    throw B2Error(TI_ERROR_INVALID_ARGUMENT, "tree must have 1..64 snodes and start with the root");
+    throw B2Error(TI_ERROR_INVALID_ARGUMENT, "tree must have 1..1024 snodes (taichi_max_num_snodes) and start with the root");
   s.resize(n);
   for (int i = 0; i < n; i++) {
     B2SNodeHost &x = s[i];
@@ -710,15 +710,19 @@ struct BodyDeactivateDynamic {  // snode_deactivate_dynamic: loop over the paren
 struct BodyFill {  // field.fill over active cells
   long long place_off;
   int bytes;
-  u32 bits;
+  u64 bits;  // the value's bit pattern, zero-extended to 64 bits
   int psid;
   __device__ void operator()(B2TreeDev *T, const B2SNodeDev &, const B2Element &E, int j, bool act) {
     if (act) {
       u8 *c = b2_lookup(T, psid, E.node, j) + place_off;
-      if (bytes == 4)
-        *(u32 *)c = bits;
+      if (bytes == 8)
+        *(u64 *)c = bits;
+      else if (bytes == 4)
+        *(u32 *)c = (u32)bits;
+      else if (bytes == 2)
+        *(unsigned short *)c = (unsigned short)bits;
       else
-        *(u64 *)c = (u64)bits;
+        *c = (u8)bits;
     }
   }
   __device__ void finish(B2TreeDev *) {}
@@ -853,8 +857,9 @@ __global__ void k_coord_op(B2TreeDev *T, B2Path P, const int *coords, long long 
     b2_load_coord(coords, k, I);
     const int sid = P.id[P.n - 1];
     if (mode == 0) {
-      u8 *node = b2_walk<true>(T, P, I, &cell, nullptr);
-      b2_activate_cell(T, sid, node, cell);
+      bool dead;
+      u8 *node = b2_walk<true>(T, P, I, &cell, &dead);
+      if (!dead) b2_activate_cell(T, sid, node, cell);
     } else {
       bool dead;
       u8 *node = b2_walk<false>(T, P, I, &cell, &dead);
@@ -873,7 +878,9 @@ __global__ void k_access(B2TreeDev *T, B2Path P, long long place_off, int bytes,
     b2_load_coord(coords, k, I);
     const int sid = P.id[P.n - 1];
     if (mode < 2) {
-      u8 *node = b2_walk<true>(T, P, I, &cell, nullptr);
+      bool dead;
+      u8 *node = b2_walk<true>(T, P, I, &cell, &dead);
+      if (dead) continue;  // out of memory (flag raised): the ambient node is never written
       b2_activate_cell(T, sid, node, cell);
       u8 *c = b2_lookup(T, sid, node, cell) + place_off;
       if (mode == 1)
@@ -906,7 +913,9 @@ __global__ void k_from_dense(B2TreeDev *T, B2Path P, long long place_off, int by
       r /= d;
     }
     const int sid = P.id[P.n - 1];
-    u8 *node = b2_walk<true>(T, P, I, &cell, nullptr);
+    bool dead;
+    u8 *node = b2_walk<true>(T, P, I, &cell, &dead);
+    if (dead) continue;
     b2_activate_cell(T, sid, node, cell);
     u8 *c = b2_lookup(T, sid, node, cell) + place_off;
     if (bytes == 4)
@@ -922,7 +931,9 @@ __global__ void k_dynamic_append(B2TreeDev *T, B2Path P, const int *coords, long
     b2_load_coord(coords, k, I);
     const int sid = P.id[P.n - 1];
     const B2SNodeDev &s = T->s[sid];
-    B2DynNode *d = (B2DynNode *)b2_walk<true>(T, P, I, &cell, nullptr);
+    bool dead;
+    B2DynNode *d = (B2DynNode *)b2_walk<true>(T, P, I, &cell, &dead);
+    if (dead) continue;
     u32 i = atomicAdd(&d->n, 1u);
     B2DynChunk *c = b2_dynamic_chunk(T, sid, d, (int)(i / (u32)s.chunk_size));
     if (c) *(int *)((u8 *)c + 16 + (long long)(i % (u32)s.chunk_size) * s.cell_size) = vals[k];
@@ -1011,6 +1022,9 @@ void B2Tree_t::gc_async(int sid) {
   B2_CUDA(cudaGetLastError());
 }
 
+__global__ void k_deactivate_root_dynamic(B2TreeDev *T, int dsid) {
+  b2_deactivate_cell(T, dsid, T->root + T->s[dsid].offset_in_parent_cell, 0);
+}
 void B2Tree_t::reset_list_async(int sid) {
   check_snode(sid, "reset_list");
   B2_CUDA(cudaMemsetAsync(&host_copy.lists[sid]->count, 0, 4, rt->stream()));
@@ -1036,13 +1050,14 @@ void B2Tree_t::deactivate_all(int sid) {
     deactivate_level_async(sid);
   } else if (s[sid].type == B2T_DYNAMIC) {
     int par = s[sid].parent;
-    listgen_async(par);
+    if (par != 0) listgen_async(par);
     int block = (int)std::min<int64_t>(256, std::max<int64_t>(32, roundup(std::min<int64_t>(s[par].num_cells, 1024), 32)));
     if (par == 0) {
-      // parent is the root cell: a single dynamic container
-      throw B2Error(TI_ERROR_NOT_SUPPORTED, "dynamic directly under root");
+      // ti.root.dynamic(...): the root cell holds the one list (test_dynamic.py:13, test_gc.py:64)
+      k_deactivate_root_dynamic<<<1, 1, 0, st>>>(dev, sid);
+    } else {
+      k_struct_for<<<grid, block, 0, st>>>(dev, par, BodyDeactivateDynamic{par, sid});
     }
-    k_struct_for<<<grid, block, 0, st>>>(dev, par, BodyDeactivateDynamic{par, sid});
     rt->count_launch();
     gc_async(sid);
   }
@@ -1284,7 +1299,7 @@ int32_t b2_dynamic_length(B2Tree t, int32_t dyn, const int32_t *coords, int64_t 
   B2_API_END(-1)
 }
 
-int32_t b2_field_fill(B2Tree t, int32_t place, uint32_t bits) {
+int32_t b2_field_fill(B2Tree t, int32_t place, uint64_t bits) {
   B2_API_BEGIN
   require(t, TI_ERROR_ARGUMENT_NULL, "tree");
   t->check_snode(place, "fill");

@@ -50,11 +50,24 @@ _prog = _Program()
 root = None
 
 
-def init(arch=cuda, device_memory_GB=None, device_memory_fraction=None, device_index=0, **_ignored):
-    """ti.init: only arch=ti.cuda exists in this library (no CPU fallback)."""
+# ti.init options that have no effect on this path and are accepted silently (lang/misc.py:323); anything else is an error
+_INIT_ACCEPTED = {"default_fp": "f32", "default_ip": "i32", "random_seed": None, "kernel_profiler": None, "debug": None, "offline_cache": None,
+                  "log_level": None, "verbose": None, "fast_math": None, "cpu_max_num_threads": None, "packed": None}
+
+
+def init(arch=cuda, device_memory_GB=None, device_memory_fraction=None, device_index=0, **options):
+    """ti.init: only arch=ti.cuda exists in this library (no CPU fallback).  Options this path cannot honour raise."""
     global root
     if arch not in (cuda,):
         raise RuntimeError("taichi_b200 implements arch=ti.cuda only (no ti.cpu fallback)")
+    for k, v in options.items():
+        if k not in _INIT_ACCEPTED:
+            raise TypeError(f"ti.init(): option {k!r} is not supported by taichi_b200")
+        if _INIT_ACCEPTED[k] is not None and v not in (_INIT_ACCEPTED[k], globals().get(_INIT_ACCEPTED[k])):
+            raise ValueError(f"ti.init({k}={v!r}): only {_INIT_ACCEPTED[k]} is implemented")
+    if device_memory_GB is None and device_memory_fraction is not None:
+        import torch
+        device_memory_GB = float(device_memory_fraction) * torch.cuda.get_device_properties(device_index).total_memory / (1 << 30)
     reset()
     if device_memory_GB is not None:
         lib.b2_set_pool_size(C.c_uint64(int(device_memory_GB * (1 << 30))))
@@ -179,6 +192,8 @@ class SNode:
 
     def _to_full(self, idx):
         c = np.atleast_2d(np.asarray(idx, dtype=np.int32))
+        if not self._axes():                       # the root cell: ti.append(x.parent(), [], v)
+            return np.zeros((max(c.shape[0], 1) if c.size else 1, 12), np.int32)
         out = np.zeros((c.shape[0], 12), np.int32)
         for t, a in enumerate(self._axes()):
             out[:, a] = c[:, t]
@@ -207,6 +222,8 @@ def is_active(snode, idx):
 
 def append(snode, idx, val):
     c = snode.parent()._to_full(idx) if np.ndim(idx) else snode.parent()._to_full([idx])
+    if not snode.parent()._axes() and np.ndim(val):  # root-level list: one append per value
+        c = np.zeros((len(val), 12), np.int32)
     v = np.ascontiguousarray(np.broadcast_to(val, (len(c),)), dtype=np.int32)
     lib.b2_dynamic_append_i32(_materialize(), snode.id, c.ctypes.data_as(C.c_void_p), len(c), v.ctypes.data_as(C.c_void_p))
     L.check()
@@ -284,8 +301,9 @@ class ScalarField:
         L.check()
 
     def fill(self, val):
-        bits = int(np.array([val], self.np_dtype).view(np.uint32)[0])
-        lib.b2_field_fill(_materialize(), self.place_id, C.c_uint32(bits))
+        raw = np.array([val], self.np_dtype).tobytes()                     # the value's bit pattern, any width up to 8 bytes
+        bits = int.from_bytes(raw, "little")
+        lib.b2_field_fill(_materialize(), self.place_id, C.c_uint64(bits))
         L.check()
 
     def to_numpy(self):
@@ -353,15 +371,32 @@ def field(dtype, shape=None):
 
 
 def block_local(*_fields):
-    """ti.block_local is a property of the prebuilt MPM kernels here (Mpm3D(block_local=True))."""
+    """ti.block_local(field) is a hint INSIDE a Python-compiled kernel in the reference (misc.py:480-496).  Here loop bodies are
+    CUDA C++ given to ti.struct_for, and the pad is declared at the launch: kernel(snode, fields=[..], block_local=[ti.bls(..)])."""
+    raise NotImplementedError("declare pads at the launch: kernel(snode, fields=[...], block_local=[ti.bls(field_index, 'read'|'add', lo, hi)]); "
+                              "the prebuilt MPM solver takes Mpm3D(block_local=True)")
 
 
 def no_activate(*_snodes):
-    pass
+    """ti.no_activate (misc.py:473): reads through c.read never activate; writes always do -- there is no per-SNode switch."""
+    raise NotImplementedError("ti.no_activate is not available: c.read<T>() never activates, c.write / c.ref always do")
 
 
 def loop_config(**_kw):
-    pass
+    """ti.loop_config(block_dim=..) (misc.py:612): launch shapes are chosen by the library."""
+    raise NotImplementedError("ti.loop_config is not available: launch shapes are chosen by the library")
+
+
+def bls(field, mode, lo, hi, axes=None, extent=None, halo=False):
+    """One block-local pad for a struct-for launch: `field` = index into the launch's field list; mode 'read' (stencil gather)
+    or 'add' (scatter with c.bls_add); lo / hi = smallest / largest offset the body reaches per pad axis (inclusive);
+    axes = physical axes of the pad (default 0..len(lo)-1); extent = block size per axis in the field's index space
+    (default: the loop SNode's own shape -- pass it for pid-list loops over a dynamic SNode); halo=True activates every pad
+    cell in the epilogue like the reference's CUDA backend, False only the cells that received something (its x64 result)."""
+    lo, hi = list(np.atleast_1d(lo)), list(np.atleast_1d(hi))
+    axes = list(range(len(lo))) if axes is None else list(axes)
+    extent = [0] * len(lo) if extent is None else list(np.atleast_1d(extent))
+    return dict(field=int(field), mode=mode, lo=lo, hi=hi, axes=axes, extent=extent, halo=bool(halo))
 
 
 # ---------------------------------------------------------------------------------------------
@@ -406,15 +441,27 @@ class StructFor:
         self._rt = _prog.rt
         _prog.kernels.append(self)  # unloaded with the runtime (ti.reset)
 
-    def __call__(self, snode, fields=(), args=(), gc=()):
+    def __call__(self, snode, fields=(), args=(), gc=(), block_local=()):
         """gc: pointer / dynamic SNodes whose cells the body deactivates -- their GC runs right after the launch,
-        which is where the reference's offloader puts it (offload.cpp:671-695)."""
+        which is where the reference's offloader puts it (offload.cpp:671-695).
+        block_local: pads made with ti.bls(...) -- slot k of the body (c.bls_read<T>(k, J) / c.bls_add<T>(k, J, v))."""
         if self.handle is None or self._rt != _prog.rt:
             raise RuntimeError("struct-for kernel belongs to a runtime that was reset")
         t = _materialize()
         places = (C.c_int32 * max(1, len(fields)))(*[f.place_id for f in fields])
         slots = (C.c_uint64 * max(1, len(args)))(*[_arg_bits(a) for a in args])
-        lib.b2_jit_launch(self.handle, t, snode.id, places, len(fields), slots, len(args))
+        if block_local:
+            specs = (L.B2BlsSpec * len(block_local))()
+            for sp, d in zip(specs, block_local):
+                f = fields[d["field"]]
+                acc = {np.dtype(np.float32): 2, np.dtype(np.int32): 3, np.dtype(np.float64): 4}
+                sp.field, sp.ndim, sp.halo = d["field"], len(d["lo"]), int(d["halo"])
+                sp.mode = 1 if d["mode"] == "read" else acc[np.dtype(f.np_dtype)]
+                for q in range(len(d["lo"])):
+                    sp.axis[q], sp.extent[q], sp.lo[q], sp.hi[q] = d["axes"][q], int(d["extent"][q]), int(d["lo"][q]), int(d["hi"][q])
+            lib.b2_jit_launch_bls(self.handle, t, snode.id, places, len(fields), slots, len(args), specs, len(block_local))
+        else:
+            lib.b2_jit_launch(self.handle, t, snode.id, places, len(fields), slots, len(args))
         L.check()
         for sn in gc:
             lib.b2_gc(t, sn.id)

@@ -97,3 +97,34 @@ def test_jit_body_compiles_without_a_device():
     code, msg = L.last_error()
     L.lib.ti_set_last_error(0, None)
     assert code == -4 and "nonsense" in msg and "bad_body" in msg
+
+
+def test_bls_pad_geometry_known_answers():
+    """ScratchPad bounds pinned by the reference's own unit tests: bls_analyzer_test.cpp:51-77 (block 8x8, accesses x[i+1, j]
+    and x[i, j-3]: bounds[0] = (0, 1 + 8), bounds[1] = (-3, 8)), :79-110 (offsets (0,0), (0,-3): (0, 8), (-3, 8)) and
+    make_block_local_test.cpp:91-120 (block 4x4, accesses (0,0) and (-1,-3): pad 5 x 7)."""
+    from taichi_b200 import _lib as L
+    i32 = C.c_int32
+
+    def geom(block, offsets):
+        nd = len(block)
+        off = (i32 * (nd * len(offsets)))(*[v for o in offsets for v in o])
+        low, high, size = (i32 * nd)(), (i32 * nd)(), (i32 * nd)()
+        n = L.lib.b2_bls_pad_geometry(nd, (i32 * nd)(*block), len(offsets), off, low, high, size)
+        return list(low), list(high), list(size), n
+    assert geom([8, 8], [(1, 0), (0, -3)]) == ([0, -3], [9, 8], [9, 11], 99)
+    assert geom([8, 8], [(0, 0), (0, -3)]) == ([0, -3], [8, 8], [8, 11], 88)
+    assert geom([4, 4], [(0, 0), (-1, -3)]) == ([-1, -3], [4, 4], [5, 7], 35)
+    assert geom([4, 4, 4], [(0, 0, 0), (2, 2, 2)])[2:] == ([6, 6, 6], 216)          # the MPM quadratic stencil: (4 + 2)^3
+
+
+def test_jit_check_block_local_and_reductions():
+    from taichi_b200 import _lib as L
+    ok = L.lib.b2_jit_check(b"""B2_BODY(c) {
+        int J[B2_MAX_AXES]; c.offset(J, 0, 1);
+        c.bls_add<float>(1, J, c.bls_read<float>(0, c.I));
+        c.reduce_add<float>(0, 1.0f); c.reduce_max<int>(1, c.I[0]); c.reduce_min<double>(2, 0.5);
+    }""", b"bls_body")
+    if ok < 0 and "libnvrtc" in L.last_error()[1]:
+        pytest.skip("libnvrtc not available here")
+    assert ok > 0, L.last_error()

@@ -915,3 +915,190 @@ def test_stencil_multiple_inputs(ti):
     sh = lambda A, di, dj: np.roll(A, (-di, -dj), axis=(0, 1))
     want = np.where(ins, sh(X, 0, -2) + sh(Y, 2, -1) + sh(Y, -1, 0) + sh(Z, -1, 0) + sh(Z, 1, 0), 0)
     assert np.array_equal(f[3].to_numpy(), want)
+
+
+# --------------------------------------------------------------------------- ti.block_local + thread-local reductions
+BLS_STENCIL_SRC = """
+B2_RANGE_BODY(c) {                                   // fill x over [lo, lo + cnt)
+  const int dim = c.arg<int>(0);
+  int I[B2_MAX_AXES] = {0};
+  long long r = c.i;
+  for (int d = dim - 1; d >= 0; d--) { const int n = c.arg<int>(5 + d); I[d] = c.arg<int>(2 + d) + (int)(r % n); r /= n; }
+  int v = 0;
+  for (int d = 0, p = 1; d < dim; d++) { p = 1; for (int q = 0; q <= d; q++) p *= I[d]; v += p; }
+  c.write<int>(0, I, v);
+}
+B2_BODY(c) {
+  const int dim = c.arg<int>(0), ns = c.arg<int>(1), use_bls = c.arg<int>(8), scatter = c.arg<int>(9);
+  const int *st = c.arg<const int *>(10);
+  int acc = 0;
+  const int mine = scatter ? c.read<int>(0, c.I) : 0;
+  for (int s = 0; s < ns; s++) {
+    int J[B2_MAX_AXES];
+    for (int a = 0; a < B2_MAX_AXES; a++) J[a] = c.I[a] + (a < dim ? st[3 * s + a] : 0);
+    if (scatter) {
+      if (use_bls) c.bls_add<int>(0, J, mine); else atomicAdd(c.ref<int>(1, J), mine);
+    } else {
+      acc += use_bls ? c.bls_read<int>(0, J) : c.read<int>(0, J);
+    }
+  }
+  if (!scatter) c.write<int>(1, c.I, acc);
+}
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dim,N,bs,stencil,scatter", [
+    (1, 128, 32, [(-1,), (0,)], False), (2, 128, 16, [(0, 0), (0, -1), (0, 1), (1, 0)], False),
+    (2, 128, (4, 16), [(0, 0), (0, -1), (0, 1), (1, 0)], False), (3, 128, (4, 8, 16), [(-1, -1, -1), (2, 0, 1)], False),
+    (1, 128, 32, [(1,), (0,)], True), (2, 128, 16, [(0, 0), (0, -1), (0, 1), (1, 0)], True),
+    (3, 128, (4, 8, 16), [(-1, -1, -1), (2, 0, 1)], True)])
+def test_block_local_equals_plain_stencils(ti, dim, N, bs, stencil, scatter):
+    """tests/python/test_bls.py:60-121 / bls_test_template.py:8-96: the same stencil body once through a block-local pad
+    (ti.block_local(x) for gathers, ti.block_local(y) for scatters) and once through plain global accesses must agree
+    exactly (int32), and both with NumPy; the pad geometry is ScratchPad's (block + offsets)."""
+    import torch
+    bs = [bs] * dim if isinstance(bs, int) else list(bs)
+    axes = [ti.i, ti.ij, ti.ijk][dim - 1]
+    grid = [N // b for b in bs]
+    x, y, y2 = ti.field(ti.i32), ti.field(ti.i32), ti.field(ti.i32)
+    block = ti.root.pointer(axes, grid)
+    xs, ys, ys2 = block.dense(axes, bs), block.dense(axes, bs), block.dense(axes, bs)
+    xs.place(x), ys.place(y), ys2.place(y2)
+    lo = [2 * b for b in bs] + [0] * (3 - dim)
+    cnt = [N - 4 * b for b in bs] + [1] * (3 - dim)
+    st = np.zeros((len(stencil), 3), np.int32)
+    st[:, :dim] = np.array(stencil, np.int32)
+    dst = torch.from_numpy(st).cuda()
+
+    def args(use_bls):
+        return [np.int32(dim), np.int32(len(stencil))] + [np.int32(v) for v in lo + cnt] + [np.int32(use_bls), np.int32(int(scatter)), dst]
+    k = ti.struct_for(BLS_STENCIL_SRC, "bls_stencil")
+    k.range(0, int(np.prod(cnt)), fields=[x, y], args=args(0))
+    off = np.array(stencil)
+    pad = ti.bls(1 if scatter else 0, "add" if scatter else "read", off.min(0), off.max(0))
+    k(xs, fields=[x, y], args=args(1), block_local=[pad])
+    k(xs, fields=[x, y2], args=args(0))
+    I = np.indices((N,) * dim)
+    inside = np.ones((N,) * dim, bool)
+    for d in range(dim):
+        inside &= (I[d] >= lo[d]) & (I[d] < lo[d] + cnt[d])
+    X = np.where(inside, sum(I[d].astype(np.int64) ** (d + 1) for d in range(dim)), 0).astype(np.int32)
+    want = np.zeros_like(X)
+    for o in stencil:
+        want += np.roll(X, tuple(-q for q in o) if not scatter else tuple(o), axis=tuple(range(dim)))
+    if not scatter:
+        want = np.where(inside, want, 0)
+    assert np.array_equal(y.to_numpy(), y2.to_numpy())       # BLS == non-BLS (bls_test_template.py:85-96)
+    assert np.array_equal(y.to_numpy(), want)
+    assert np.array_equal(x.to_numpy(), X)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("halo", [False, True])
+def test_block_local_particle_grid(ti, halo):
+    """bls_test_template.py:99-287 bls_particle_grid (N = 128, ppc = 10, block 8, pointer level 1): per-block particle-id
+    lists (block.dynamic), struct-for over the lists, P2G scatter into ti.block_local(m), then G2P gather out of
+    ti.block_local(m) -- BLS and plain agree within 1e-4 (float sums reorder), and with NumPy; halo=True activates the
+    whole pad like the reference's CUDA epilogue, halo=False only touched cells."""
+    import torch
+    N, bs, ppc = 128, 8, 10
+    m1, m2, pid = ti.field(ti.f32), ti.field(ti.f32), ti.field(ti.i32)
+    block = ti.root.pointer(ti.ij, N // bs)
+    block.dense(ti.ij, bs).place(m1)
+    block.dense(ti.ij, bs).place(m2)
+    plist = block.dynamic(ti.l, 4096, chunk_size=64)
+    plist.place(pid)
+    rng = np.random.default_rng(5)
+    npart = ppc * (N // 2) ** 2
+    xp = (rng.random((npart, 2)) * 0.5 + 0.2).astype(np.float32)
+    dx = torch.from_numpy(xp).cuda()
+    out = torch.zeros(2, npart, device="cuda")
+    k = ti.struct_for("""
+    B2_RANGE_BODY(c) {                                // build_pid: ti.append(pid.parent(), block index, p)
+      const float2 x = c.arg<const float2 *>(0)[c.i];
+      const int N = c.arg<int>(1), bs = c.arg<int>(2);
+      const int bi = (int)floorf(x.x * N - 0.5f), bj = (int)floorf(x.y * N - 0.5f);
+      int B[B2_MAX_AXES] = {bi / bs, bj / bs};
+      c.append<int>(0, B, (int)c.i);
+    }
+    B2_BODY(c) {                                      // for I in pid: p = pid[I]; scatter / gather around base
+      const int p = c.read<int>(0, c.I);
+      const float2 x = c.arg<const float2 *>(0)[p];
+      const int N = c.arg<int>(1), use_bls = c.arg<int>(3), phase = c.arg<int>(4);
+      const int bi = (int)floorf(x.x * N - 0.5f), bj = (int)floorf(x.y * N - 0.5f);
+      const float fx = x.x * N - bi, fy = x.y * N - bj;
+      const float wx[3] = {0.5f * (1.5f - fx) * (1.5f - fx), 0.75f - (fx - 1.0f) * (fx - 1.0f), 0.5f * (fx - 0.5f) * (fx - 0.5f)};
+      const float wy[3] = {0.5f * (1.5f - fy) * (1.5f - fy), 0.75f - (fy - 1.0f) * (fy - 1.0f), 0.5f * (fy - 0.5f) * (fy - 0.5f)};
+      float acc = 0.0f;
+      for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) {
+          int J[B2_MAX_AXES] = {bi + i, bj + j};
+          if (phase == 0) {
+            if (use_bls) c.bls_add<float>(0, J, wx[i] * wy[j]); else atomicAdd(c.ref<float>(1, J), wx[i] * wy[j]);
+          } else {
+            acc += wx[i] * wy[j] * (use_bls ? c.bls_read<float>(0, J) : c.read<float>(1, J));
+          }
+        }
+      if (phase == 1) c.arg<float *>(5)[p] = acc;
+    }""", "particle_grid")
+    base = [dx, np.int32(N), np.int32(bs)]
+    k.range(0, npart, fields=[pid], args=base)
+    assert int(ti.length(plist, ti.active_indices(block)[:, :2]).sum()) == npart
+    for use_bls, m, row in ((1, m1, 0), (0, m2, 1)):
+        a = base + [np.int32(use_bls), np.int32(0), out[row]]
+        pads = [ti.bls(1, "add", (0, 0), (2, 2), extent=(bs, bs), halo=halo)] if use_bls else []
+        k(plist, fields=[pid, m], args=a, block_local=pads)                     # P2G
+        a[4] = np.int32(1)
+        pads = [ti.bls(1, "read", (0, 0), (2, 2), extent=(bs, bs))] if use_bls else []
+        k(plist, fields=[pid, m], args=a, block_local=pads)                     # G2P
+    g1, g2 = m1.to_numpy(), m2.to_numpy()
+    assert np.allclose(g1, g2, rtol=0, atol=1e-4)                               # bls_test_template.py:258-272 (abs 1e-4)
+    assert np.allclose(out[0].cpu().numpy(), out[1].cpu().numpy(), rtol=0, atol=1e-4)
+    X = xp.astype(np.float32) * np.float32(N)
+    b = np.floor(X - np.float32(0.5)).astype(np.int32)
+    f = X - b
+    w = np.stack([0.5 * (1.5 - f) ** 2, 0.75 - (f - 1.0) ** 2, 0.5 * (f - 0.5) ** 2], 0).astype(np.float64)
+    want = np.zeros((N, N))
+    for i in range(3):
+        for j in range(3):
+            np.add.at(want, (b[:, 0] + i, b[:, 1] + j), w[i, :, 0] * w[j, :, 1])
+    assert np.allclose(g1, want, rtol=1e-5, atol=1e-4)
+    assert abs(g1.sum() - npart) < 1e-3 * npart                                 # partition of unity
+    # activation: plain scatter opens exactly the touched cells' blocks; the pad with halo opens every block it overlaps
+    act1 = set(map(tuple, ti.active_indices(block)[:, :2]))
+    occupied = set(map(tuple, np.unique(b // bs, axis=0)))
+    assert occupied <= act1
+
+
+@pytest.mark.gpu
+def test_thread_local_reductions(ti):
+    """make_thread_local.cpp:100-213 / runtime.cpp:1235-1266: 0-D reductions from a struct-for body go through a thread-local
+    accumulator and ONE atomic per CTA (c.reduce_add / reduce_min / reduce_max) instead of one atomic per cell."""
+    import torch
+    x = ti.field(ti.f32)
+    blk = ti.root.pointer(ti.ij, 32).bitmasked(ti.ij, 8)
+    blk.place(x)
+    rng = np.random.default_rng(3)
+    pts = rng.integers(0, 256, (5000, 2))
+    pts = np.unique(pts, axis=0)
+    vals = (rng.random(len(pts)) * 10 - 3).astype(np.float32)
+    for (i, j), v in zip(pts[:400], vals[:400]):
+        x[int(i), int(j)] = float(v)
+    k = ti.struct_for("""B2_BODY(c) {
+        const float v = c.read<float>(0, c.I);
+        c.reduce_add<float>(0, v);
+        c.reduce_add<int>(1, 1);
+        c.reduce_max<float>(2, v);
+        c.reduce_min<float>(3, v);
+    }""", "tls")
+    s = torch.zeros(1, device="cuda")
+    n = torch.zeros(1, dtype=torch.int32, device="cuda")
+    mx = torch.full((1,), -1e30, device="cuda")
+    mn = torch.full((1,), 1e30, device="cuda")
+    l0 = 0
+    k(blk, fields=[x], args=[s, n, mx, mn])
+    v = vals[:400].astype(np.float64)
+    assert int(n.item()) == 400
+    assert abs(float(s.item()) - v.sum()) < 1e-3
+    assert float(mx.item()) == float(vals[:400].max()) and float(mn.item()) == float(vals[:400].min())

@@ -131,3 +131,52 @@ def test_sparse_checkpoint_roundtrip(ti):
     x.from_sparse(coords, vals)
     assert np.array_equal(ti.active_indices(blk), act0)
     assert np.array_equal(x.to_numpy(), img0)
+
+
+def test_fill_eight_byte_fields(ti):
+    """ScalarField.fill on f64 / i64 fields stored the low 32 bits only (1.5 became 0.0)."""
+    x = ti.field(ti.f64)
+    y = ti.field(ti.i64)
+    z = ti.field(ti.f32)
+    ti.root.pointer(ti.i, 8).dense(ti.i, 8).place(x, y, z)
+    x[3] = 1.0                      # activates block 0
+    x[40] = 1.0
+    x.fill(1.5), y.fill(-7), z.fill(0.25)
+    gx, gy, gz = x.to_numpy(), y.to_numpy(), z.to_numpy()
+    act = np.zeros(64, bool)
+    act[0:8] = act[40:48] = True
+    assert (gx[act] == 1.5).all() and (gy[act] == -7).all() and (gz[act] == 0.25).all()
+    assert (gx[~act] == 0).all() and (gy[~act] == 0).all()
+
+
+def test_root_level_dynamic(ti):
+    """ti.root.dynamic(...) -- the reference's dominant Dynamic shape (test_dynamic.py:13-95, test_gc.py:61-72): element
+    writes, ti.append / ti.length on the root cell's list, deactivate_all + GC with a bounded allocator."""
+    n = 128
+    x = ti.field(ti.f32)
+    y = ti.field(ti.i32)
+    z = ti.field(ti.i32)
+    dx = ti.root.dynamic(ti.i, n, 32)
+    dx.place(x)
+    dy = ti.root.dynamic(ti.i, n, 32)
+    dy.place(y)
+    big = ti.root.dynamic(ti.i, 1024 * 1024, chunk_size=1024)
+    big.place(z)
+    for i in range(0, n, 3):                        # test_dynamic: x[i] = i, holes read as 0
+        x[i] = i
+    got = [x[i] for i in range(n)]
+    assert got == [float(i) if i % 3 == 0 else 0.0 for i in range(n)]
+    assert ti.length(dx, []) == 127                 # highest written index (126) + 1 (Dynamic_activate, node_dynamic.h:16-42)
+    ti.append(dy, [], np.arange(n))                 # test_append: every value lands exactly once
+    assert ti.length(dy, []) == n                   # test_length
+    assert sorted(y[i] for i in range(n)) == list(range(n))
+    assert len(ti.active_indices(dy)) == n          # struct-for over the list visits n cells
+    assert big._num_dynamically_allocated == 0      # test_gc.py:61-72
+    for _ in range(100):
+        z[1024] = 1
+        assert z[1024] == 1 and ti.length(big, []) == 1025
+        big.deactivate_all()
+        assert big._num_dynamically_allocated <= 2
+        assert ti.length(big, []) == 0 and z[1024] == 0
+    dx.deactivate_all()
+    assert ti.length(dx, []) == 0 and x[3] == 0.0

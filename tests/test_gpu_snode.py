@@ -307,7 +307,7 @@ def test_field_fill_to_dense_reduce(impls):
         assert g.lib.b2_field_reduce(g.tree, x, op, 0, out.ctypes.data_as(C.c_void_p)) == 0
         assert out[0] == np.float32(expect)
     one = np.float32(1.0).view(np.uint32)
-    assert g.lib.b2_field_fill(g.tree, x, C.c_uint32(int(one))) == 0
+    assert g.lib.b2_field_fill(g.tree, x, C.c_uint64(int(one))) == 0
     assert g.lib.b2_field_reduce(g.tree, x, 0, 0, out.ctypes.data_as(C.c_void_p)) == 0
     assert out[0] == 3 * 64  # three active 8x8 blocks
     full = np.arange(32 * 32, dtype=np.float32).reshape(32, 32)
@@ -371,3 +371,48 @@ def test_c4_full_size_lists_vs_oracle(impls, kind, frac):
         assert np.array_equal(g.list(lvl), o.list(lvl))
     assert np.array_equal(g.stats(p), o.stats(p))
     o.create(TreeBuilder())   # release the oracle's host memory
+
+
+def test_out_of_memory_never_writes_the_ambient_node():
+    """when the pool is exhausted an activating access used to degrade to the shared ambient (zero) node and
+    store into it, so every later read of an inactive cell returned garbage.  Now the error is raised, the store goes to a
+    sink, and inactive cells still read zero.  Uses its own runtime with a 48 MB pool."""
+    import ctypes as C
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    from taichi_b200 import _lib as L
+    from _b2 import vp
+    from _desc import coords12
+    lib = L.lib
+    lib.b2_set_pool_size(C.c_uint64(48 << 20))
+    rt = lib.ti_create_runtime(L.TI_ARCH_CUDA, 0)
+    L.check()
+    lib.b2_set_pool_size(C.c_uint64(8 << 30))               # (the shared test runtime keeps its size if created later)
+    tb = TreeBuilder()
+    p = tb.pointer(0, "i", 4096)
+    d = tb.dense(p, "i", 65536)                               # 256 KB per node: the pool holds < 200 of them
+    x = tb.place(d, 4)
+    arr = tb.array()
+    tree = lib.b2_create_tree(rt, C.cast(arr, C.POINTER(L.B2SNodeDesc)), len(tb))
+    L.check()
+    coords = coords12(np.arange(4096, dtype=np.int32)[:, None] * 65536 + 7)   # one cell in every pointer cell
+    vals = np.full(4096, 1234567, np.int32)
+    lib.b2_write(tree, x, vp(coords), len(coords), vp(vals), 0)
+    buf = C.create_string_buffer(256)
+    assert lib.b2_check_runtime_error(rt, buf, 256) != 0 and b"pool exhausted" in buf.value
+    act = np.zeros(4096, np.uint8)
+    lib.b2_is_active(tree, p, vp(coords12(np.arange(4096, dtype=np.int32)[:, None] * 65536)), 4096, vp(act))
+    L.check()
+    n_act = int(act.sum())
+    assert 0 < n_act < 4096
+    got = np.zeros(4096, np.int32)
+    lib.b2_read(tree, x, vp(coords), 4096, vp(got))
+    L.check()
+    assert np.array_equal(got[act == 1], vals[act == 1])      # what fitted was written
+    assert (got[act == 0] == 0).all()                         # everything else still reads the ambient ZERO
+    probe = coords12((np.flatnonzero(act == 0)[:64, None]) * 65536 + 12345)
+    got2 = np.ones(len(probe), np.int32)
+    lib.b2_read(tree, x, vp(probe), len(probe), vp(got2))
+    assert (got2 == 0).all()
+    lib.b2_destroy_tree(tree)
+    lib.ti_destroy_runtime(rt)
