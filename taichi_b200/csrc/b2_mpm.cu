@@ -408,6 +408,7 @@ __global__ void __launch_bounds__(256) k_mpm_gridop(MpmDev M) {
   const int sub = threadIdx.x >> 6, t = threadIdx.x & 63;
   for (u32 e = blockIdx.x * 4 + sub; e < ne; e += gridDim.x * 4) {
     const B2Element *E = (const B2Element *)b2_list_get(L, e);
+    if (M.flt_mode && ((E->pcoord[0] == M.flt_layer) != (M.flt_mode == 1))) continue;
     float4 *blk = (float4 *)E->node;
     const int I[3] = {E->pcoord[0] * 4 + (t >> 4), E->pcoord[1] * 4 + ((t >> 2) & 3), E->pcoord[2] * 4 + (t & 3)};
     float4 g = blk[t];
@@ -524,7 +525,7 @@ __global__ void __launch_bounds__(G2P_PLAIN_THREADS, 3) k_mpm_g2p(MpmDev M, int 
 
   for (;;) {
     __syncthreads();
-    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[1], 1u);
+    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[M.wc], 1u);
     __syncthreads();
     const u32 slot = (u32)sSlot;
     if (slot >= nslots) break;
@@ -532,6 +533,7 @@ __global__ void __launch_bounds__(G2P_PLAIN_THREADS, 3) k_mpm_g2p(MpmDev M, int 
     if (total == 0) continue;
     const int key = M.slot_key[slot];
     const int bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
+    if (M.flt_mode && ((bx == M.flt_layer) != (M.flt_mode == 1))) continue;
     if (BLS) {
       if (tid < 8) sNb[tid] = mpm_block_ptr<false>(M, bx + (tid >> 2), by + ((tid >> 1) & 1), bz + (tid & 1));
       __syncthreads();
@@ -713,8 +715,11 @@ struct B2Mpm_t {
   void ensure_lists();
   void clear_grid();
   void p2g();
-  void grid_op();
-  void g2p();
+  void grid_op(int mode = 0, int layer = 0);
+  void g2p(int mode = 0, int layer = 0, bool last = true);
+  void begin_substep();
+  void end_substep();
+  bool g2p_open = false;  // a layer-restricted G2P launch has run on this generation, more follow
   void substep(int n);
 };
 
@@ -811,6 +816,7 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   if (const char *e = getenv("B2_COMPACT_EVERY")) compact_every = atoi(e);
   M.dbg = getenv("B2_DBG") ? atoi(getenv("B2_DBG")) : 0;
   M.work_counter = dalloc<u32>(8);
+  M.wc = 1;
   M.listed = dalloc<u32>((size_t)(nblocks + 31) / 32);
   M.stats = dalloc<double>(8);
   B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
@@ -920,40 +926,54 @@ void B2Mpm_t::p2g() {
   rt->count_launch();
   // blocks that P2G activates append themselves to the leaf element list (mpm_block_ptr<true>)
 }
-void B2Mpm_t::grid_op() {
+void B2Mpm_t::grid_op(int mode, int layer) {
   ensure_lists();
+  M.flt_mode = mode, M.flt_layer = layer;
   k_mpm_gridop<<<rt->num_sms * 8, 256, 0, rt->stream()>>>(M);
+  M.flt_mode = 0;
   rt->count_launch();
 }
-void B2Mpm_t::g2p() {
+// mode / layer: restrict the launch to the bins of one block layer (slab driver: interior bins run while the ghost layer
+// travels); `last` = no further launch on this generation follows: the generations flip
+void B2Mpm_t::g2p(int mode, int layer, bool last) {
   cudaStream_t st = rt->stream();
   // the generation being written starts with an empty chunk arena
   if (!in_substep) {
-    B2_CUDA(cudaMemsetAsync(M.arena_next[gen ^ 1], 0, 16, st));
+    if (!g2p_open) B2_CUDA(cudaMemsetAsync(M.arena_next[gen ^ 1], 0, 16, st));
     B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
   }
-  if (prm.block_local)
-  {
+  M.flt_mode = mode, M.flt_layer = layer;
+  M.wc = g2p_open ? 2 : 1;  // (a second launch of the same substep draws from its own counter)
+  if (prm.block_local) {
     static const bool no_order = getenv("B2_G2P_SORT") != nullptr;  // experiment switch: always sort
-    static const int occ = getenv("B2_G2P_OCC") ? atoi(getenv("B2_G2P_OCC")) : 20;
-    if (order_valid && !no_order && occ == 32)
-      k_mpm_g2p_bls<32, 32, true><<<rt->num_sms * 32, 32, 0, st>>>(M, gen);
-    else if (order_valid && !no_order && occ == 16)
-      k_mpm_g2p_bls<64, 16, true><<<rt->num_sms * 16, 64, 0, st>>>(M, gen);
-    else if (order_valid && !no_order && occ == 20)
+    if (order_valid && !no_order)
       k_mpm_g2p_bls<64, 20, true><<<rt->num_sms * 20, 64, 0, st>>>(M, gen);
-    else if (order_valid && !no_order && occ == 24)
-      k_mpm_g2p_bls<64, 24, true><<<rt->num_sms * 24, 64, 0, st>>>(M, gen);
-    else if (order_valid && !no_order)
-      k_mpm_g2p_bls<64, 12, true><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
     else
       k_mpm_g2p_bls<64, 12, false><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
-  }
-  else
+  } else {
     k_mpm_g2p<false><<<rt->num_sms * 3, G2P_PLAIN_THREADS, 0, st>>>(M, gen);
+  }
+  M.flt_mode = 0, M.wc = 1;
   rt->count_launch();
-  gen ^= 1;
-  order_valid = false;
+  g2p_open = !last;
+  if (last) {
+    gen ^= 1;
+    order_valid = false;
+  }
+}
+// one substep's fixed points for drivers that enqueue the phases themselves (b2_slab.cu): cadence work (bin compaction,
+// sparse life cycle), counters reset by the clear kernel instead of memset nodes
+void B2Mpm_t::begin_substep() {
+  if (compact_every > 0 && substep_index > 0 && substep_index % compact_every == 0) compact_bins();
+  if (sparse && prm.deactivate_every > 0 && substep_index % prm.deactivate_every == 0) {
+    tree->deactivate_all(1);
+    lists_valid = false;
+  }
+  in_substep = true;
+}
+void B2Mpm_t::end_substep() {
+  in_substep = false;
+  substep_index++;
 }
 void B2Mpm_t::substep(int n) {
   cudaStream_t st = rt->stream();
@@ -1177,6 +1197,36 @@ int32_t b2_mpm_g2p(B2Mpm m) {
   return 0;
   B2_API_END(-1)
 }
+int32_t b2_mpm_begin_substep(B2Mpm m) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  m->begin_substep();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_end_substep(B2Mpm m) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  m->end_substep();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_grid_op_layer(B2Mpm m, int32_t mode, int32_t layer) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  require(mode >= 0 && mode <= 2, TI_ERROR_INVALID_ARGUMENT, "mode");
+  m->grid_op(mode, layer);
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_g2p_layer(B2Mpm m, int32_t mode, int32_t layer, int32_t last) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  require(mode >= 0 && mode <= 2, TI_ERROR_INVALID_ARGUMENT, "mode");
+  m->g2p(mode, layer, last != 0);
+  return 0;
+  B2_API_END(-1)
+}
 int32_t b2_mpm_grid_to_dense(B2Mpm m, float *out) {
   B2_API_BEGIN
   require(m != nullptr && out != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm/out");
@@ -1285,7 +1335,7 @@ int32_t b2_mpm_pack_blocks(B2Mpm m, int32_t layer, void *buf, int64_t cap) {
   require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
   check_msg(buf, cap);
   cudaStream_t st = m->rt->stream();
-  B2_CUDA(cudaMemsetAsync(buf, 0, MPM_MSG_HEADER, st));
+  if (!m->in_substep) B2_CUDA(cudaMemsetAsync(buf, 0, MPM_MSG_HEADER, st));  // (a driver inside begin/end_substep zeroes its headers itself)
   m->ensure_lists();
   k_mpm_pack_blocks<<<m->rt->num_sms * 4, 256, 0, st>>>(m->M, layer, (u8 *)buf, cap);
   m->rt->count_launch();
@@ -1304,25 +1354,49 @@ int32_t b2_mpm_unpack_blocks(B2Mpm m, const void *buf, int64_t cap, int32_t mode
   return 0;
   B2_API_END(-1)
 }
-int32_t b2_mpm_extract_migrants(B2Mpm m, int32_t side, void *buf, int64_t cap) {
+int32_t b2_mpm_extract_migrants2(B2Mpm m, void *bufL, int64_t capL, void *bufR, int64_t capR) {
   B2_API_BEGIN
   require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
-  check_msg(buf, cap);
-  require(side == 0 || side == 1, TI_ERROR_INVALID_ARGUMENT, "side");
+  if (bufL) check_msg(bufL, capL);
+  if (bufR) check_msg(bufR, capR);
+  if (!bufL && !bufR) return 0;
   cudaStream_t st = m->rt->stream();
-  B2_CUDA(cudaMemsetAsync(buf, 0, MPM_MSG_HEADER, st));
-  k_mpm_extract_migrants<<<m->rt->num_sms * 4, 256, 0, st>>>(m->M, m->gen, side, (u8 *)buf, cap);
+  if (!m->in_substep) {
+    if (bufL) B2_CUDA(cudaMemsetAsync(bufL, 0, MPM_MSG_HEADER, st));
+    if (bufR) B2_CUDA(cudaMemsetAsync(bufR, 0, MPM_MSG_HEADER, st));
+  }
+  k_mpm_extract_migrants<<<m->rt->num_sms * 4, 256, 0, st>>>(m->M, m->gen, (u8 *)bufL, capL, (u8 *)bufR, capR);
   m->rt->count_launch();
   B2_CUDA(cudaGetLastError());
   return 0;
   B2_API_END(-1)
 }
-int32_t b2_mpm_insert_records(B2Mpm m, const void *buf, int64_t cap) {
+int32_t b2_mpm_extract_migrants(B2Mpm m, int32_t side, void *buf, int64_t cap) {
+  if (side != 0 && side != 1) {
+    ti_set_last_error(TI_ERROR_INVALID_ARGUMENT, "side");
+    return -1;
+  }
+  return side == 0 ? b2_mpm_extract_migrants2(m, buf, cap, nullptr, 0) : b2_mpm_extract_migrants2(m, nullptr, 0, buf, cap);
+}
+int32_t b2_mpm_insert_records2(B2Mpm m, const void *bufA, int64_t capA, const void *bufB, int64_t capB) {
   B2_API_BEGIN
   require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
-  check_msg(buf, cap);
+  if (bufA) check_msg(bufA, capA);
+  if (bufB) check_msg(bufB, capB);
+  if (!bufA && !bufB) return 0;
   m->order_valid = false;
-  k_mpm_insert_records<<<m->rt->grid_for(std::max<int64_t>(cap, 1), 256, 4), 256, 0, m->rt->stream()>>>(m->M, m->gen, (const u8 *)buf, cap);
+  const int64_t work = std::max<int64_t>((bufA ? capA : 0) + (bufB ? capB : 0) + 32, 1);
+  k_mpm_insert_records<<<m->rt->grid_for(work, 256, 4), 256, 0, m->rt->stream()>>>(m->M, m->gen, (const u8 *)bufA, capA, (const u8 *)bufB, capB);
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_insert_records(B2Mpm m, const void *buf, int64_t cap) { return b2_mpm_insert_records2(m, buf, cap, nullptr, 0); }
+int32_t b2_mpm_zero_headers(B2Mpm m, void *a, void *b, void *c, void *d) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  k_mpm_zero_headers<<<1, 4, 0, m->rt->stream()>>>((u32 *)a, (u32 *)b, (u32 *)c, (u32 *)d);
   m->rt->count_launch();
   B2_CUDA(cudaGetLastError());
   return 0;

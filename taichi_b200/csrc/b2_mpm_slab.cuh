@@ -93,18 +93,20 @@ __global__ void __launch_bounds__(256) k_mpm_unpack_blocks(MpmDev M, const u8 *b
 
 // side 0: bins with bx < slab_lo, side 1: bins with bx >= slab_hi  ->  particle records; the bins
 // are emptied.  One CTA per slot.
-__global__ void __launch_bounds__(256) k_mpm_extract_migrants(MpmDev M, int gen, int side, u8 *buf, long long cap) {
+// (bufL, capL): message for the lower neighbour (bins with bx < slab_lo), (bufR, capR): for the upper one; either may be null
+__global__ void __launch_bounds__(256) k_mpm_extract_migrants(MpmDev M, int gen, u8 *bufL, long long capL, u8 *bufR, long long capR) {
   __shared__ long long sBase;
   const u32 ns = *M.nslots;
-  u32 *count = (u32 *)buf;
-  MpmParticleRec *recs = (MpmParticleRec *)(buf + MPM_MSG_HEADER);
   for (u32 slot = blockIdx.x; slot < ns; slot += gridDim.x) {
     const u32 total = M.count[gen][slot];
     if (total == 0) continue;
     int bx, by, bz;
     mpm_unkey(M, M.slot_key[slot], bx, by, bz);
-    const bool mine = side == 0 ? bx < M.slab_lo : bx >= M.slab_hi;
-    if (!mine) continue;
+    u8 *buf = bx < M.slab_lo ? bufL : bx >= M.slab_hi ? bufR : nullptr;
+    if (!buf) continue;
+    const long long cap = bx < M.slab_lo ? capL : capR;
+    u32 *count = (u32 *)buf;
+    MpmParticleRec *recs = (MpmParticleRec *)(buf + MPM_MSG_HEADER);
     __syncthreads();
     if (threadIdx.x == 0) {
       // reserve [b, b + total) only if it fits: a message that is full leaves the bin where it is (its particles travel
@@ -147,17 +149,18 @@ __global__ void __launch_bounds__(256) k_mpm_extract_migrants(MpmDev M, int gen,
     if (threadIdx.x == 0) M.count[gen][slot] = 0;
   }
 }
-__global__ void __launch_bounds__(256) k_mpm_insert_records(MpmDev M, int gen, const u8 *buf, long long cap) {
-  const u32 n = mpm_msg_count(buf, cap);
-  const MpmParticleRec *recs = (const MpmParticleRec *)(buf + MPM_MSG_HEADER);
+// records of up to two messages (either may be null) in one launch
+__global__ void __launch_bounds__(256) k_mpm_insert_records(MpmDev M, int gen, const u8 *bufA, long long capA, const u8 *bufB, long long capB) {
+  const u32 nA = bufA ? mpm_msg_count(bufA, capA) : 0u, nB = bufB ? mpm_msg_count(bufB, capB) : 0u;
+  const u32 nAr = (nA + 31) / 32 * 32, n = nAr + nB;  // (message B starts on a warp boundary)
   const u32 nround = (n + 31) / 32 * 32;
   for (u32 p = blockIdx.x * blockDim.x + threadIdx.x; p < nround; p += gridDim.x * blockDim.x) {
-    bool valid = p < n;
+    bool valid = p < nA || (p >= nAr && p < n);
     MpmParticleRec rec;
     rec.p0 = make_float4(0, 0, 0, 1), rec.p1 = rec.p2 = rec.p3 = make_float4(0, 0, 0, 0), rec.id = 0;
     int key = 0, cell = 0;
     if (valid) {
-      rec = recs[p];
+      rec = p < nA ? ((const MpmParticleRec *)(bufA + MPM_MSG_HEADER))[p] : ((const MpmParticleRec *)(bufB + MPM_MSG_HEADER))[p - nAr];
       if (rec.p0.x == MPM_TOMB) {
         valid = false;
       } else {
@@ -168,6 +171,10 @@ __global__ void __launch_bounds__(256) k_mpm_insert_records(MpmDev M, int gen, c
     }
     mpm_insert(M, gen, key, cell, valid, rec.p0, rec.p1, rec.p2, rec.p3, rec.id);
   }
+}
+__global__ void k_mpm_zero_headers(u32 *a, u32 *b, u32 *c, u32 *d) {
+  u32 *p = threadIdx.x == 0 ? a : threadIdx.x == 1 ? b : threadIdx.x == 2 ? c : d;
+  if (p) *p = 0u;
 }
 // compact export of the live particles with their ids (original order is the caller's business)
 __global__ void __launch_bounds__(256) k_mpm_export(MpmDev M, int gen, float *x, float *v, float *C, float *J, int *ids, long long cap, unsigned long long *counter) {

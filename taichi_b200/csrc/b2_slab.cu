@@ -1,8 +1,9 @@
 // b2_slab.cu -- native driver of the slab-decomposed substep: the whole sequence
 //   clear, P2G | A: ghost layer -> r+1 | grid-op | B: owned layer -> r-1 | G2P | C: migrants <-> r+-1
-// is enqueued from C++ on ONE CUDA stream: the pack/unpack kernels of b2_mpm_slab.cuh plus
-// ncclSend/ncclRecv (NCCL over NVLink/NVSwitch) inside ncclGroupStart/End.  No Python and no host
-// synchronisation in the loop.  (New: the reference has no multi-GPU path, cuda_context.cpp:22.)
+// is enqueued from C++: kernels on the runtime's stream, the three exchanges (ncclSend/ncclRecv over NVLink/NVSwitch
+// inside ncclGroupStart/End) on a second stream, ordered by events.  While A travels the grid-op runs on every block
+// outside the receiving layer; while B travels G2P runs on every bin that does not read the ghost layer (SURVEY 8e:
+// "interior blocks overlap").  No Python and no host synchronisation in the loop.  (New: the reference has no multi-GPU path, cuda_context.cpp:22.)
 // NCCL is bound at run time (dlopen of the libnccl.so.2 that torch already loaded), so the
 // library has no link-time dependency on it and single-GPU users never touch it.
 #include <dlfcn.h>
@@ -82,6 +83,12 @@ struct B2Slab_t {
   int64_t sendA_bytes, recvA_bytes, sendB_bytes, recvB_bytes, sendL_bytes, recvL_bytes, sendR_bytes, recvR_bytes;
   uint8_t *sendA, *recvA, *sendB, *recvB, *sendL, *sendR, *recvL, *recvR;
   bool tuned = false;   // message sizes only grow after the first tune
+  // The exchanges run on a second stream: ghost layers and migrants travel while the compute stream works on blocks / bins
+  // that do not depend on them.  ready[k]: message k packed (compute stream); arrived[k]: message k is in MY receive buffers
+  // (recorded by my own NCCL group, or -- loopback -- by the peer whose copy filled them).
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ready[3], arrived[3], arrived2, sent;  // sent: my own sends / copies of the substep have left their buffers  // (exchange C has two senders in loopback mode: arrived[2] from below, arrived2 from above)
+  bool overlap = true;
   uint32_t *sizes_dev;  // tune: 4 counts out, 4 counts in
   double *diag_dev;     // diagnostics: 8 doubles, reduced over the slabs in place
   std::vector<void *> allocs;
@@ -108,23 +115,7 @@ static void ok0(int32_t rc) {
   }
 }
 
-// one phase's messages: (send -> dst) and (recv <- src), both optional.  `which` names the receive buffer on the
-// destination rank (0 recvA, 1 recvB, 2 recvL, 3 recvR) for the loopback transport.
 static uint8_t *recv_buffer(B2Slab_t *s, int which);
-static void exchange(B2Slab_t *s, const void *send, int64_t sbytes, int dst, int which, void *recv, int64_t rbytes, int src) {
-  if (dst < 0 && src < 0) return;
-  cudaStream_t st = s->rt->stream();
-  if (s->comm->loopback) {  // the receiving side is filled by the sender's copy
-    if (dst >= 0) B2_CUDA(cudaMemcpyAsync(recv_buffer(s->comm->peers[dst], which), send, (size_t)sbytes, cudaMemcpyDeviceToDevice, st));
-    return;
-  }
-  NcclApi &n = nccl();
-  B2_NCCL(n.GroupStart());
-  if (dst >= 0) B2_NCCL(n.Send(send, (size_t)sbytes, NCCL_UINT8, dst, s->comm->comm, st));
-  if (src >= 0) B2_NCCL(n.Recv(recv, (size_t)rbytes, NCCL_UINT8, src, s->comm->comm, st));
-  B2_NCCL(n.GroupEnd());
-}
-
 extern "C" {
 int32_t b2_comm_unique_id(uint8_t *out128) {
   B2_API_BEGIN
@@ -186,68 +177,137 @@ B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_t world, int32
     require(world == comm->world && rank >= 0 && rank < world, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "rank / world of the loopback communicator");
     comm->peers[(size_t)rank] = s;
   }
+  if (const char *e = getenv("B2_SLAB_OVERLAP")) s->overlap = atoi(e) != 0;
+  B2_CUDA(cudaStreamCreateWithFlags(&s->comm_stream, cudaStreamNonBlocking));
+  for (int k = 0; k < 3; k++) {
+    B2_CUDA(cudaEventCreateWithFlags(&s->ready[k], cudaEventDisableTiming));
+    B2_CUDA(cudaEventCreateWithFlags(&s->arrived[k], cudaEventDisableTiming));
+  }
+  B2_CUDA(cudaEventCreateWithFlags(&s->arrived2, cudaEventDisableTiming));
+  B2_CUDA(cudaEventCreateWithFlags(&s->sent, cudaEventDisableTiming));
   return s;
   B2_API_END(nullptr)
 }
 void b2_slab_destroy(B2Slab s) {
   if (!s) return;
   cudaStreamSynchronize(b2_current_stream());
+  if (s->comm_stream) {
+    cudaStreamSynchronize(s->comm_stream);
+    for (int k = 0; k < 3; k++) cudaEventDestroy(s->ready[k]), cudaEventDestroy(s->arrived[k]);
+    cudaEventDestroy(s->arrived2), cudaEventDestroy(s->sent);
+    cudaStreamDestroy(s->comm_stream);
+  }
   for (void *p : s->allocs) cudaFree(p);
   delete s;
 }
 
-// The decomposed substep in four compute phases with the three exchanges between them (b2_mpm_slab.cuh):
-//   phase 0: clear, P2G, pack ghost layer | A | phase 1: add ghosts, grid-op, pack owned layer | B |
-//   phase 2: overwrite ghosts, G2P, extract migrants | C | phase 3: insert arrivals
+// The decomposed substep: four compute phases on the runtime's stream, three exchanges on the slab's comm stream.
+//   phase 0: clear, P2G, pack ghost layer hi                                  -> ready[0]
+//   A      : ghost layer -> rank + 1                                            (waits ready[0]; -> arrived[0] on the receiver)
+//   phase 1: grid-op on every block outside layer lo  ||  A in flight
+//            wait arrived[0]: add ghosts into layer lo, grid-op on layer lo, pack layer lo   -> ready[1]
+//   B      : owned layer lo -> rank - 1 (becomes its ghost layer)               (waits ready[1]; -> arrived[1])
+//   phase 2: G2P on every bin outside layer hi - 1  ||  B in flight
+//            wait arrived[1]: overwrite ghost layer, G2P on the bins of layer hi - 1, extract migrants  -> ready[2]
+//   C      : migrants <-> rank +- 1                                             (waits ready[2]; -> arrived[2])
+//   phase 3: wait arrived[2]: insert arrivals
+// With overlap off (B2_SLAB_OVERLAP=0) the same calls run unsplit and the comm stream is the compute stream.
 static void slab_phase(B2Slab_t *s, int ph) {
   B2Mpm m = s->mpm;
+  cudaStream_t st = s->rt->stream();
   const int64_t capA = (s->sendA_bytes - HEADER) / BLOCK_REC, capB = (s->sendB_bytes - HEADER) / BLOCK_REC;
   const int64_t capL = (s->sendL_bytes - HEADER) / PART_REC, capR = (s->sendR_bytes - HEADER) / PART_REC;
+  const bool multi = s->world > 1, split = multi && s->overlap;
   switch (ph) {
     case 0:
+      ok0(b2_mpm_begin_substep(m));
       ok0(b2_mpm_clear_grid(m));
+      if (multi) ok0(b2_mpm_zero_headers(m, s->up >= 0 ? s->sendA : nullptr, s->down >= 0 ? s->sendB : nullptr, s->down >= 0 ? s->sendL : nullptr,
+                                         s->up >= 0 ? s->sendR : nullptr));
       ok0(b2_mpm_p2g(m));
       if (s->up >= 0) ok0(b2_mpm_pack_blocks(m, s->hi, s->sendA, capA));
+      if (multi) B2_CUDA(cudaEventRecord(s->ready[0], st));
       break;
     case 1:
+      if (split && s->down >= 0) ok0(b2_mpm_grid_op_layer(m, 2, s->lo));  // everything but the layer that receives ghosts
+      if (multi) B2_CUDA(cudaStreamWaitEvent(st, s->arrived[0], 0));
       if (s->down >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvA, (s->recvA_bytes - HEADER) / BLOCK_REC, 0));
-      ok0(b2_mpm_grid_op(m));
+      if (split && s->down >= 0)
+        ok0(b2_mpm_grid_op_layer(m, 1, s->lo));
+      else
+        ok0(b2_mpm_grid_op(m));
       if (s->down >= 0) ok0(b2_mpm_pack_blocks(m, s->lo, s->sendB, capB));
+      if (multi) B2_CUDA(cudaEventRecord(s->ready[1], st));
       break;
     case 2:
+      if (split && s->up >= 0) ok0(b2_mpm_g2p_layer(m, 2, s->hi - 1, 0));  // bins that never read the ghost layer
+      if (multi) B2_CUDA(cudaStreamWaitEvent(st, s->arrived[1], 0));
       if (s->up >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvB, (s->recvB_bytes - HEADER) / BLOCK_REC, 1));
-      ok0(b2_mpm_g2p(m));
-      if (s->down >= 0) ok0(b2_mpm_extract_migrants(m, 0, s->sendL, capL));
-      if (s->up >= 0) ok0(b2_mpm_extract_migrants(m, 1, s->sendR, capR));
+      if (split && s->up >= 0)
+        ok0(b2_mpm_g2p_layer(m, 1, s->hi - 1, 1));
+      else
+        ok0(b2_mpm_g2p(m));
+      if (multi) ok0(b2_mpm_extract_migrants2(m, s->down >= 0 ? s->sendL : nullptr, capL, s->up >= 0 ? s->sendR : nullptr, capR));
+      if (multi) B2_CUDA(cudaEventRecord(s->ready[2], st));
       break;
     default:
-      if (s->up >= 0) ok0(b2_mpm_insert_records(m, s->recvR, (s->recvR_bytes - HEADER) / PART_REC));
-      if (s->down >= 0) ok0(b2_mpm_insert_records(m, s->recvL, (s->recvL_bytes - HEADER) / PART_REC));
+      if (multi) {
+        B2_CUDA(cudaStreamWaitEvent(st, s->arrived[2], 0));
+        if (s->comm->loopback) B2_CUDA(cudaStreamWaitEvent(st, s->arrived2, 0));
+        B2_CUDA(cudaStreamWaitEvent(st, s->sent, 0));  // the send buffers are packed again by the next substep
+        ok0(b2_mpm_insert_records2(m, s->up >= 0 ? s->recvR : nullptr, (s->recvR_bytes - HEADER) / PART_REC, s->down >= 0 ? s->recvL : nullptr,
+                                   (s->recvL_bytes - HEADER) / PART_REC));
+      }
+      ok0(b2_mpm_end_substep(m));
   }
 }
+// exchange ex of this rank, enqueued on its comm stream behind ready[ex]
 static void slab_exchange(B2Slab_t *s, int ex) {
   if (s->world == 1) return;
+  cudaStream_t sc = s->overlap ? s->comm_stream : s->rt->stream();
+  B2_CUDA(cudaStreamWaitEvent(sc, s->ready[ex], 0));
+  if (s->comm->loopback) {
+    // a "send" is a device-to-device copy into the peer's receive buffer; the peer's arrived event follows the copy
+    auto put = [&](const uint8_t *src, int64_t bytes, int dst, int which, bool second) {
+      B2Slab_t *p = s->comm->peers[dst];
+      B2_CUDA(cudaMemcpyAsync(recv_buffer(p, which), src, (size_t)bytes, cudaMemcpyDeviceToDevice, sc));
+      B2_CUDA(cudaEventRecord(second ? p->arrived2 : p->arrived[ex], sc));
+    };
+    if (ex == 0 && s->up >= 0) put(s->sendA, s->sendA_bytes, s->up, 0, false);
+    if (ex == 1 && s->down >= 0) put(s->sendB, s->sendB_bytes, s->down, 1, false);
+    if (ex == 2) {
+      if (s->down >= 0) put(s->sendL, s->sendL_bytes, s->down, 3, true);   // my left migrants arrive at the lower rank from above
+      if (s->up >= 0) put(s->sendR, s->sendR_bytes, s->up, 2, false);      // my right migrants arrive at the upper rank from below
+    }
+    // ranks at the ends of the chain receive nothing in some exchanges: their wait must not dangle
+    if (ex == 0 && s->down < 0) B2_CUDA(cudaEventRecord(s->arrived[0], sc));
+    if (ex == 1 && s->up < 0) B2_CUDA(cudaEventRecord(s->arrived[1], sc));
+    if (ex == 2 && s->down < 0) B2_CUDA(cudaEventRecord(s->arrived[2], sc));
+    if (ex == 2 && s->up < 0) B2_CUDA(cudaEventRecord(s->arrived2, sc));
+    if (ex == 2) B2_CUDA(cudaEventRecord(s->sent, sc));
+    return;
+  }
+  NcclApi &n = nccl();
+  B2_NCCL(n.GroupStart());
   if (ex == 0) {
-    exchange(s, s->sendA, s->sendA_bytes, s->up, 0, s->recvA, s->recvA_bytes, s->down);
+    if (s->up >= 0) B2_NCCL(n.Send(s->sendA, (size_t)s->sendA_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
+    if (s->down >= 0) B2_NCCL(n.Recv(s->recvA, (size_t)s->recvA_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
   } else if (ex == 1) {
-    exchange(s, s->sendB, s->sendB_bytes, s->down, 1, s->recvB, s->recvB_bytes, s->up);
-  } else if (s->comm->loopback) {
-    exchange(s, s->sendL, s->sendL_bytes, s->down, 3, nullptr, 0, -1);  // my left migrants are the lower rank's arrivals from above
-    exchange(s, s->sendR, s->sendR_bytes, s->up, 2, nullptr, 0, -1);
-  } else {  // both directions in one NCCL group
-    NcclApi &n = nccl();
-    cudaStream_t st = s->rt->stream();
-    B2_NCCL(n.GroupStart());
+    if (s->down >= 0) B2_NCCL(n.Send(s->sendB, (size_t)s->sendB_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
+    if (s->up >= 0) B2_NCCL(n.Recv(s->recvB, (size_t)s->recvB_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
+  } else {
     if (s->down >= 0) {
-      B2_NCCL(n.Send(s->sendL, (size_t)s->sendL_bytes, NCCL_UINT8, s->down, s->comm->comm, st));
-      B2_NCCL(n.Recv(s->recvL, (size_t)s->recvL_bytes, NCCL_UINT8, s->down, s->comm->comm, st));
+      B2_NCCL(n.Send(s->sendL, (size_t)s->sendL_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
+      B2_NCCL(n.Recv(s->recvL, (size_t)s->recvL_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
     }
     if (s->up >= 0) {
-      B2_NCCL(n.Send(s->sendR, (size_t)s->sendR_bytes, NCCL_UINT8, s->up, s->comm->comm, st));
-      B2_NCCL(n.Recv(s->recvR, (size_t)s->recvR_bytes, NCCL_UINT8, s->up, s->comm->comm, st));
+      B2_NCCL(n.Send(s->sendR, (size_t)s->sendR_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
+      B2_NCCL(n.Recv(s->recvR, (size_t)s->recvR_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
     }
-    B2_NCCL(n.GroupEnd());
   }
+  B2_NCCL(n.GroupEnd());
+  B2_CUDA(cudaEventRecord(s->arrived[ex], sc));
+  if (ex == 2) B2_CUDA(cudaEventRecord(s->sent, sc));
 }
 
 int32_t b2_slab_substep(B2Slab s, int32_t nsteps) {
