@@ -95,6 +95,30 @@ def make_slab_cloud(world, rank, per_rank, n_grid):
     return x, v, np.zeros((n, 3, 3), np.float32), np.ones(n, np.float32), ids
 
 
+def make_c5_cloud(world, rank, total, n_grid):
+    """the C3 cloud scaled x8 -- SIX balls spread along x (seed 5), same particle density as C3 (ball radius
+    64 cells at 1024^3 for 64M particles), v = (0.5,-1,0).  Slabs are static, so the ranks' loads differ (SURVEY hard part 7)."""
+    from taichi_b200 import multigpu as mg
+    per_ball = total // 6
+    radius = (3.0 * per_ball / 9.7 / (4.0 * np.pi)) ** (1.0 / 3.0) / n_grid
+    xs, ids = [], []
+    for b in range(6):
+        rng = np.random.default_rng(5 + b)
+        n = per_ball if b < 5 else total - 5 * per_ball
+        d = rng.standard_normal((n, 3)).astype(np.float32)
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        r = np.float32(radius) * rng.random(n, dtype=np.float32) ** np.float32(1.0 / 3.0)
+        x = (np.array([0.1 + 0.8 * (b + 0.5) / 6.0, 0.6 if b % 2 == 0 else 0.35, 0.5], np.float32) + d * r[:, None]).astype(np.float32)
+        keep = mg.partition_particles(x, n_grid, world) == rank
+        xs.append(np.ascontiguousarray(x[keep]))
+        ids.append(np.flatnonzero(keep).astype(np.int32) + np.int32(b * per_ball))
+        del d, r, x, keep
+    x, ids = np.concatenate(xs), np.concatenate(ids)
+    n = len(x)
+    v = np.tile(np.array([0.5, -1.0, 0.0], np.float32), (n, 1))
+    return x, v, np.zeros((n, 3, 3), np.float32), np.ones(n, np.float32), ids
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
 
@@ -203,7 +227,7 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    if world > 1:
+    if world > 1 or args.cloud == "c5" or args.force_slabs:
         return run_slabs(args, world, rank, local)
     n_grid, n_p, dt, layout, desc = WORKLOADS[args.workload]
     rt = tb.Runtime(local, device_memory_GB=10 if args.workload == "c3" else 1)  # (the C4 listgen block needs 4.3 GB of containers)
@@ -247,7 +271,7 @@ def run_ours(args):
     e2e_i = [0]
 
     def step_e2e():
-        solver.set_particles(hx, hv, hC, hJ)
+        solver.set_particles(hx, hv, None, hJ)      # C = 0 at injection (mpm3d.py:87-90) is not uploaded: 28 B per particle
         solver.substep(SUBSTEPS)
         solver.get_particles(x=hx_outs[e2e_i[0] & 1], wait=False)
         e2e_i[0] += 1
@@ -297,7 +321,8 @@ def run_ours(args):
         "dtype": "f32", "data": "synthetic",
         "config": config_of(args.workload, args.deactivate_every),
         "state": {"active_cells": cells, "active_blocks": st["active_blocks"], "occupied_bins": st["occupied_slots"]},
-        "e2e": {"value": e2e_value, "unit": "particle-updates/s", "h2d_bytes_per_step": int(n_p * 64), "d2h_bytes_per_step": int(n_p * 12),
+        "e2e": {"value": e2e_value, "unit": "particle-updates/s", "h2d_bytes_per_step": int(n_p * 28), "d2h_bytes_per_step": int(n_p * 12),
+                "uploads": "x, v, J (28 B/particle; C = 0 at injection)",
                 "returns": "positions only (12 of the 64 B/particle state); uploads and downloads of neighbouring steps are pipelined"},
         "gpu_launches": int(launches),
         "clocks": clocks.summary(),
@@ -373,21 +398,33 @@ def run_slabs(args, world, rank, local):
     import taichi_b200 as tb
     from taichi_b200 import multigpu as mg
     n_grid, per_rank, dt = 1024, 8 * 1024 * 1024, 1e-5
-    desc = "sparse 3D MLS-MPM 1024^3 pointer->bitmasked->dense(4^3), 8M particles/GPU, slabs along i, halo exchange + migration"
+    total_c5 = 64 * 1024 * 1024 if args.strong else per_rank * world
+    desc = ("sparse 3D MLS-MPM 1024^3 pointer->bitmasked->dense(4^3), " +
+            ("64M particles in total (strong scaling), " if args.strong else "8M particles/GPU (weak scaling), ") +
+            ("SURVEY C5 cloud: six balls along x, static slabs (unbalanced), " if args.cloud == "c5" else
+             "one ball per slab + half a ball on every slab boundary (balanced), ") + "slabs along i, halo exchange + migration")
     rt = tb.Runtime(local, device_memory_GB=6)
     lo, hi = mg.slab_bounds(n_grid // 4, world, rank)
-    slab = mg.CudaSlab(rt, n_grid, 2 * per_rank, dt, lo, hi)
-    x, v, Cm, J, ids = make_slab_cloud(world, rank, per_rank, n_grid)
+    if args.cloud == "c5":
+        x, v, Cm, J, ids = make_c5_cloud(world, rank, total_c5, n_grid)
+    else:
+        assert not args.strong, "--strong uses --cloud c5"
+        x, v, Cm, J, ids = make_slab_cloud(world, rank, per_rank, n_grid)
     n_local = len(x)
+    slab = mg.CudaSlab(rt, n_grid, max(2 * per_rank, n_local + n_local // 4 + (1 << 20)), dt, lo, hi)
     hx, hv, hC, hJ, hid = (torch.from_numpy(a).pin_memory() for a in (x, v, Cm, J, ids))
     slab.set_particles(hx, hv, hC, hJ, hid)
     drv = mg.NativeSlabDriver(slab, rank, world, cap_blocks=8192, cap_particles=131072)
-    ntot = torch.tensor([n_local], device="cuda", dtype=torch.int64)
-    dist.all_reduce(ntot)
-    n_total = int(ntot.item())
+    counts = torch.zeros(world, device="cuda", dtype=torch.int64)
+    counts[rank] = n_local
+    if world > 1:
+        dist.all_reduce(counts)
+    n_total = int(counts.sum().item())
+    per_rank_counts = [int(c) for c in counts.tolist()]
 
     def barrier():
-        dist.barrier()
+        if world > 1:
+            dist.barrier()
         torch.cuda.synchronize()
 
     def timed(fn, steps, finish=None):
@@ -401,7 +438,8 @@ def run_slabs(args, world, rank, local):
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
     def step_resident():
@@ -411,13 +449,13 @@ def run_slabs(args, world, rank, local):
     # neighbour exchange and downloads the positions of the particles the slab then owns (records compacted
     # on the device; out_cap entries are copied, the live count comes with them).  Asynchronous calls: upload
     # k+1 and download k overlap the substeps around them; all copies lie inside the timed region.
-    out_cap = per_rank + per_rank // 4
+    out_cap = max(per_rank, n_local) + max(per_rank, n_local) // 4
     hx_outs = [torch.empty(out_cap, 3).pin_memory() for _ in range(2)]
     hcounts = [torch.zeros(1, dtype=torch.int64).pin_memory() for _ in range(2)]
     e2e_i = [0]
 
     def step_e2e():
-        slab.set_particles(hx, hv, hC, hJ, hid)
+        slab.set_particles(hx, hv, None, hJ, hid)   # C = 0 at injection (mpm3d.py:87-90) is not uploaded: 32 B per particle
         drv.substep(SUBSTEPS)
         b = e2e_i[0] & 1
         slab.export_async(out_cap, hcounts[b], x=hx_outs[b])
@@ -448,12 +486,14 @@ def run_slabs(args, world, rank, local):
     ach = sub_alg / (sub_ms * 1e-3) / 1e9
     line = {
         "metric": "MPM particle-updates/s", "value": value, "unit": "particle-updates/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if args.strong else "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "n_grid": n_grid, "particles_total": n_total, "substeps_per_step": SUBSTEPS, "dt": dt,
+        "config": {"workload": desc, "n_grid": n_grid, "particles_total": n_total, "particles_per_rank": per_rank_counts, "cloud": args.cloud,
+                   "substeps_per_step": SUBSTEPS, "dt": dt,
                    "l2": "particle state per GPU (>=512 MiB/substep) exceeds the 126 MB L2: no flush needed",
                    "parallelism": f"slab{world}: 1 process/GPU, ncclSend/ncclRecv ghost-layer + migrant exchange enqueued from C++, no data-path collective"},
-        "e2e": {"value": e2e_value, "unit": "particle-updates/s", "h2d_bytes_per_step": int(n_total * 68), "d2h_bytes_per_step": int(world * (out_cap * 12 + 8))},
+        "e2e": {"value": e2e_value, "unit": "particle-updates/s", "h2d_bytes_per_step": int(n_total * 32), "d2h_bytes_per_step": int(world * (out_cap * 12 + 8)),
+                "uploads": "x, v, J, id (32 B/particle; C = 0 at injection)", "returns": "positions only; uploads and downloads of neighbouring steps are pipelined"},
         "gpu_launches": int(launches) * world,
         "clocks": clocks.summary(),
         "roofline": {"bound": "hbm", "kernel": "whole substep (per GPU)", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
@@ -461,8 +501,10 @@ def run_slabs(args, world, rank, local):
     }
     if rank == 0:
         emit(line)
+    drv.destroy()
     slab.destroy()
-    dist.destroy_process_group()
+    if world > 1:
+        dist.destroy_process_group()
 
 
 _REAL_STDOUT = None
@@ -489,6 +531,10 @@ def main():
     ap.add_argument("--deactivate-every", type=int, default=DEACTIVATE_EVERY,
                     help="sparse life cycle: deactivate_all + GC every K-th substep (0 = never; the reference idiom is 1)")
     ap.add_argument("--no-extras", action="store_true", help="skip the lifecycle / listgen / reduction blocks")
+    ap.add_argument("--cloud", default="balanced", choices=["balanced", "c5"],
+                    help="N > 1: balanced = one ball per slab (+ boundary balls), c5 = SURVEY C5: six balls along x under static slabs")
+    ap.add_argument("--force-slabs", action="store_true", help="N = 1 through the slab driver on the N > 1 workload (what one rank of a weak-scaling run does, minus the exchange)")
+    ap.add_argument("--strong", action="store_true", help="N > 1 with --cloud c5: 64M particles in total at every N (also N = 1 via torchrun)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -441,7 +441,7 @@ TI_DLL_EXPORT int32_t b2_mpm_phase_ms(B2Mpm mpm, float *out_host6);
    {u32 count; u32 pad[3]; records[cap]}: block records are 1040 B {i32 key; pad; float4 cells[64]},
    particle records 80 B {float4 x4; u32 id; pad}. All calls are asynchronous; counts stay on the device. */
 TI_DLL_EXPORT int32_t b2_mpm_pack_blocks(B2Mpm mpm, int32_t block_layer_i, void *buf_dev, int64_t cap_records);
-TI_DLL_EXPORT int32_t b2_mpm_unpack_blocks(B2Mpm mpm, const void *buf_dev, int64_t cap_records, int32_t mode); /* 0 activate+add, 1 overwrite-if-active */
+TI_DLL_EXPORT int32_t b2_mpm_unpack_blocks(B2Mpm mpm, const void *buf_dev, int64_t cap_records, int32_t mode); /* 0 activate+add, 1 overwrite-if-active, 2 add-if-active */
 TI_DLL_EXPORT int32_t b2_mpm_extract_migrants(B2Mpm mpm, int32_t side, void *buf_dev, int64_t cap_records);   /* 0: below slab_lo, 1: at/above slab_hi */
 TI_DLL_EXPORT int32_t b2_mpm_insert_records(B2Mpm mpm, const void *buf_dev, int64_t cap_records);
 /* both directions in one launch (either buffer may be NULL) */
@@ -449,14 +449,11 @@ TI_DLL_EXPORT int32_t b2_mpm_extract_migrants2(B2Mpm mpm, void *buf_lower_dev, i
 TI_DLL_EXPORT int32_t b2_mpm_insert_records2(B2Mpm mpm, const void *buf_a_dev, int64_t cap_a, const void *buf_b_dev, int64_t cap_b);
 /* Drivers that enqueue the phases of a substep themselves (b2_slab.cu) bracket them with begin / end: the cadence work (bin
  * compaction, sparse life cycle) runs in begin, the clear kernel resets the work counters (no memset nodes), message headers are
- * zeroed by ONE call instead of one memset per message.  grid_op_layer / g2p_layer restrict a launch to the leaf blocks / particle
- * bins of one block layer along i (mode 0 all, 1 only `layer`, 2 all but `layer`): interior work runs while ghost layers travel;
- * last != 0 on the final G2P launch of the substep (the particle generations flip). */
+ * zeroed by ONE call instead of one memset per message. */
 TI_DLL_EXPORT int32_t b2_mpm_begin_substep(B2Mpm mpm);
 TI_DLL_EXPORT int32_t b2_mpm_end_substep(B2Mpm mpm);
 TI_DLL_EXPORT int32_t b2_mpm_zero_headers(B2Mpm mpm, void *a_dev, void *b_dev, void *c_dev, void *d_dev);
-TI_DLL_EXPORT int32_t b2_mpm_grid_op_layer(B2Mpm mpm, int32_t mode, int32_t layer);
-TI_DLL_EXPORT int32_t b2_mpm_g2p_layer(B2Mpm mpm, int32_t mode, int32_t layer, int32_t last);
+
 /* compact copy of the live particles + their ids; returns how many (synchronises) */
 TI_DLL_EXPORT int64_t b2_mpm_export(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *J_any, int32_t *ids_any, int64_t cap);
 /* Same records into HOST arrays of `cap` entries each, filled by the solver's copy stream after return; *count

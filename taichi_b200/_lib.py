@@ -211,8 +211,7 @@ SIGNATURES = {
     "b2_mpm_begin_substep": (C.c_int32, [C.c_void_p]),
     "b2_mpm_end_substep": (C.c_int32, [C.c_void_p]),
     "b2_mpm_zero_headers": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
-    "b2_mpm_grid_op_layer": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32]),
-    "b2_mpm_g2p_layer": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
+
     "b2_mpm_runtime": (C.c_void_p, [C.c_void_p]),
     "b2_comm_unique_id": (C.c_int32, [C.c_void_p]),
     "b2_comm_init": (C.c_void_p, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),

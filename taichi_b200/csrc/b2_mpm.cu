@@ -408,7 +408,6 @@ __global__ void __launch_bounds__(256) k_mpm_gridop(MpmDev M) {
   const int sub = threadIdx.x >> 6, t = threadIdx.x & 63;
   for (u32 e = blockIdx.x * 4 + sub; e < ne; e += gridDim.x * 4) {
     const B2Element *E = (const B2Element *)b2_list_get(L, e);
-    if (M.flt_mode && ((E->pcoord[0] == M.flt_layer) != (M.flt_mode == 1))) continue;
     float4 *blk = (float4 *)E->node;
     const int I[3] = {E->pcoord[0] * 4 + (t >> 4), E->pcoord[1] * 4 + ((t >> 2) & 3), E->pcoord[2] * 4 + (t & 3)};
     float4 g = blk[t];
@@ -525,7 +524,7 @@ __global__ void __launch_bounds__(G2P_PLAIN_THREADS, 3) k_mpm_g2p(MpmDev M, int 
 
   for (;;) {
     __syncthreads();
-    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[M.wc], 1u);
+    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[1], 1u);
     __syncthreads();
     const u32 slot = (u32)sSlot;
     if (slot >= nslots) break;
@@ -533,7 +532,7 @@ __global__ void __launch_bounds__(G2P_PLAIN_THREADS, 3) k_mpm_g2p(MpmDev M, int 
     if (total == 0) continue;
     const int key = M.slot_key[slot];
     const int bz = key % M.nb, by = (key / M.nb) % M.nb, bx = key / (M.nb * M.nb);
-    if (M.flt_mode && ((bx == M.flt_layer) != (M.flt_mode == 1))) continue;
+
     if (BLS) {
       if (tid < 8) sNb[tid] = mpm_block_ptr<false>(M, bx + (tid >> 2), by + ((tid >> 1) & 1), bz + (tid & 1));
       __syncthreads();
@@ -715,11 +714,10 @@ struct B2Mpm_t {
   void ensure_lists();
   void clear_grid();
   void p2g();
-  void grid_op(int mode = 0, int layer = 0);
-  void g2p(int mode = 0, int layer = 0, bool last = true);
+  void grid_op();
+  void g2p();
   void begin_substep();
   void end_substep();
-  bool g2p_open = false;  // a layer-restricted G2P launch has run on this generation, more follow
   void substep(int n);
 };
 
@@ -816,7 +814,6 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   if (const char *e = getenv("B2_COMPACT_EVERY")) compact_every = atoi(e);
   M.dbg = getenv("B2_DBG") ? atoi(getenv("B2_DBG")) : 0;
   M.work_counter = dalloc<u32>(8);
-  M.wc = 1;
   M.listed = dalloc<u32>((size_t)(nblocks + 31) / 32);
   M.stats = dalloc<double>(8);
   B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
@@ -926,24 +923,18 @@ void B2Mpm_t::p2g() {
   rt->count_launch();
   // blocks that P2G activates append themselves to the leaf element list (mpm_block_ptr<true>)
 }
-void B2Mpm_t::grid_op(int mode, int layer) {
+void B2Mpm_t::grid_op() {
   ensure_lists();
-  M.flt_mode = mode, M.flt_layer = layer;
   k_mpm_gridop<<<rt->num_sms * 8, 256, 0, rt->stream()>>>(M);
-  M.flt_mode = 0;
   rt->count_launch();
 }
-// mode / layer: restrict the launch to the bins of one block layer (slab driver: interior bins run while the ghost layer
-// travels); `last` = no further launch on this generation follows: the generations flip
-void B2Mpm_t::g2p(int mode, int layer, bool last) {
+void B2Mpm_t::g2p() {
   cudaStream_t st = rt->stream();
   // the generation being written starts with an empty chunk arena
   if (!in_substep) {
-    if (!g2p_open) B2_CUDA(cudaMemsetAsync(M.arena_next[gen ^ 1], 0, 16, st));
+    B2_CUDA(cudaMemsetAsync(M.arena_next[gen ^ 1], 0, 16, st));
     B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));
   }
-  M.flt_mode = mode, M.flt_layer = layer;
-  M.wc = g2p_open ? 2 : 1;  // (a second launch of the same substep draws from its own counter)
   if (prm.block_local) {
     static const bool no_order = getenv("B2_G2P_SORT") != nullptr;  // experiment switch: always sort
     if (order_valid && !no_order)
@@ -953,13 +944,9 @@ void B2Mpm_t::g2p(int mode, int layer, bool last) {
   } else {
     k_mpm_g2p<false><<<rt->num_sms * 3, G2P_PLAIN_THREADS, 0, st>>>(M, gen);
   }
-  M.flt_mode = 0, M.wc = 1;
   rt->count_launch();
-  g2p_open = !last;
-  if (last) {
-    gen ^= 1;
-    order_valid = false;
-  }
+  gen ^= 1;
+  order_valid = false;
 }
 // one substep's fixed points for drivers that enqueue the phases themselves (b2_slab.cu): cadence work (bin compaction,
 // sparse life cycle), counters reset by the clear kernel instead of memset nodes
@@ -1211,22 +1198,6 @@ int32_t b2_mpm_end_substep(B2Mpm m) {
   return 0;
   B2_API_END(-1)
 }
-int32_t b2_mpm_grid_op_layer(B2Mpm m, int32_t mode, int32_t layer) {
-  B2_API_BEGIN
-  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
-  require(mode >= 0 && mode <= 2, TI_ERROR_INVALID_ARGUMENT, "mode");
-  m->grid_op(mode, layer);
-  return 0;
-  B2_API_END(-1)
-}
-int32_t b2_mpm_g2p_layer(B2Mpm m, int32_t mode, int32_t layer, int32_t last) {
-  B2_API_BEGIN
-  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
-  require(mode >= 0 && mode <= 2, TI_ERROR_INVALID_ARGUMENT, "mode");
-  m->g2p(mode, layer, last != 0);
-  return 0;
-  B2_API_END(-1)
-}
 int32_t b2_mpm_grid_to_dense(B2Mpm m, float *out) {
   B2_API_BEGIN
   require(m != nullptr && out != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm/out");
@@ -1347,7 +1318,7 @@ int32_t b2_mpm_unpack_blocks(B2Mpm m, const void *buf, int64_t cap, int32_t mode
   B2_API_BEGIN
   require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
   check_msg(buf, cap);
-  require(mode == 0 || mode == 1, TI_ERROR_INVALID_ARGUMENT, "mode");
+  require(mode >= 0 && mode <= 2, TI_ERROR_INVALID_ARGUMENT, "mode");
   k_mpm_unpack_blocks<<<m->rt->num_sms * 4, 256, 0, m->rt->stream()>>>(m->M, (const u8 *)buf, cap, mode);
   m->rt->count_launch();
   B2_CUDA(cudaGetLastError());

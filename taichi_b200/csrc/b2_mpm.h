@@ -46,8 +46,5 @@ struct MpmDev {
   u32 *work_counter;  // dynamic slot fetch for the persistent kernels [8]
   u32 *listed;        // [nb^3 / 32] bit per block: the block is in the leaf element list (kept current incrementally)
   int dbg;              // B2_DBG experiment switches (0 in production)
-  // slab driver: a launch may be restricted to one 4^3-block layer along i (0 all, 1 only flt_layer, 2 all but flt_layer);
-  // grid-op filters leaf blocks, G2P filters bins; wc = work counter the persistent G2P launch draws from
-  int flt_mode, flt_layer, wc;
   double *stats;      // [8]
 };

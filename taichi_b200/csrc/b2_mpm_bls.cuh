@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
 
   for (;;) {
     __syncthreads();
-    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[M.wc], 1u);
+    if (tid == 0) sSlot = (int)atomicAdd(&M.work_counter[1], 1u);
     __syncthreads();
     const u32 slot = (u32)sSlot;
     if (slot >= nslots) break;
@@ -135,7 +135,6 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
     const int key = M.slot_key[slot];
     int bx, by, bz;
     mpm_unkey(M, key, bx, by, bz);
-    if (M.flt_mode && ((bx == M.flt_layer) != (M.flt_mode == 1))) continue;  // (uniform) not this launch's layer
     const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
     for (int t = tid; t < (int)nchunks; t += G2P_THREADS) S.chunk[t] = mpm_chunk_ptr(M, gen, M.chunk_of[gen][(u64)slot * M.maxc + t]);
     constexpr int NB0 = G2P_THREADS >= 64 ? 32 : 0;  // second warp if there is one

@@ -1,9 +1,7 @@
 // b2_slab.cu -- native driver of the slab-decomposed substep: the whole sequence
-//   clear, P2G | A: ghost layer -> r+1 | grid-op | B: owned layer -> r-1 | G2P | C: migrants <-> r+-1
+//   clear, P2G | X: ghost layer -> r+1 and owned layer -> r-1 (both ranks end up with the sums) | grid-op, G2P | C: migrants <-> r+-1
 // is enqueued from C++: kernels on the runtime's stream, the three exchanges (ncclSend/ncclRecv over NVLink/NVSwitch
-// inside ncclGroupStart/End) on a second stream, ordered by events.  While A travels the grid-op runs on every block
-// outside the receiving layer; while B travels G2P runs on every bin that does not read the ghost layer (SURVEY 8e:
-// "interior blocks overlap").  No Python and no host synchronisation in the loop.  (New: the reference has no multi-GPU path, cuda_context.cpp:22.)
+// inside ncclGroupStart/End) on a second stream, ordered by events.  No Python and no host synchronisation in the loop.  (New: the reference has no multi-GPU path, cuda_context.cpp:22.)
 // NCCL is bound at run time (dlopen of the libnccl.so.2 that torch already loaded), so the
 // library has no link-time dependency on it and single-GPU users never touch it.
 #include <dlfcn.h>
@@ -84,11 +82,28 @@ struct B2Slab_t {
   uint8_t *sendA, *recvA, *sendB, *recvB, *sendL, *sendR, *recvL, *recvR;
   bool tuned = false;   // message sizes only grow after the first tune
   // The exchanges run on a second stream: ghost layers and migrants travel while the compute stream works on blocks / bins
-  // that do not depend on them.  ready[k]: message k packed (compute stream); arrived[k]: message k is in MY receive buffers
-  // (recorded by my own NCCL group, or -- loopback -- by the peer whose copy filled them).
+  // that do not depend on them.  ready[k]: the messages of exchange k are packed (compute stream); arrived_*[k]: they are in MY
+  // receive buffers (recorded by my own NCCL group, or -- loopback -- by the peer whose copy filled them).
   cudaStream_t comm_stream = nullptr;
-  cudaEvent_t ready[3], arrived[3], arrived2, sent;  // sent: my own sends / copies of the substep have left their buffers  // (exchange C has two senders in loopback mode: arrived[2] from below, arrived2 from above)
+  cudaEvent_t ready[2], arrived_lo[2], arrived_hi[2], sent;  // arrived_lo / _hi: the message from the lower / upper neighbour is in my buffers;
+                                                            // sent: my own sends / copies of the substep have left their buffers
   bool overlap = true;
+  // B2_SLAB_PROF=1: CUDA events on the compute stream around every part of the substep; averages printed at destroy
+  bool prof = false;
+  long long prof_every = 0;  // B2_SLAB_PROF = n > 1: print and reset after every n substeps
+  std::vector<cudaEvent_t> pev;
+  size_t pev_n = 0;
+  double psum[12] = {0};
+  long long pcount = 0;
+  void mark(cudaStream_t st) {
+    if (!prof) return;
+    if (pev_n == pev.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      pev.push_back(e);
+    }
+    cudaEventRecord(pev[pev_n++], st);
+  }
   uint32_t *sizes_dev;  // tune: 4 counts out, 4 counts in
   double *diag_dev;     // diagnostics: 8 doubles, reduced over the slabs in place
   std::vector<void *> allocs;
@@ -101,7 +116,6 @@ struct B2Slab_t {
   }
 };
 
-static uint8_t *recv_buffer(B2Slab_t *s, int which) { return which == 0 ? s->recvA : which == 1 ? s->recvB : which == 2 ? s->recvL : s->recvR; }
 static void require(bool ok, TiError code, const char *msg) {
   if (!ok) throw B2Error(code, msg);
 }
@@ -115,8 +129,8 @@ static void ok0(int32_t rc) {
   }
 }
 
-static uint8_t *recv_buffer(B2Slab_t *s, int which);
 extern "C" {
+static void slab_prof_print(B2Slab_t *s);
 int32_t b2_comm_unique_id(uint8_t *out128) {
   B2_API_BEGIN
   require(out128 != nullptr, TI_ERROR_ARGUMENT_NULL, "out");
@@ -178,12 +192,13 @@ B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_t world, int32
     comm->peers[(size_t)rank] = s;
   }
   if (const char *e = getenv("B2_SLAB_OVERLAP")) s->overlap = atoi(e) != 0;
+  if (const char *e = getenv("B2_SLAB_PROF")) s->prof = atoi(e) != 0, s->prof_every = atoi(e) > 1 ? atoi(e) : 0;
   B2_CUDA(cudaStreamCreateWithFlags(&s->comm_stream, cudaStreamNonBlocking));
-  for (int k = 0; k < 3; k++) {
+  for (int k = 0; k < 2; k++) {
     B2_CUDA(cudaEventCreateWithFlags(&s->ready[k], cudaEventDisableTiming));
-    B2_CUDA(cudaEventCreateWithFlags(&s->arrived[k], cudaEventDisableTiming));
+    B2_CUDA(cudaEventCreateWithFlags(&s->arrived_lo[k], cudaEventDisableTiming));
+    B2_CUDA(cudaEventCreateWithFlags(&s->arrived_hi[k], cudaEventDisableTiming));
   }
-  B2_CUDA(cudaEventCreateWithFlags(&s->arrived2, cudaEventDisableTiming));
   B2_CUDA(cudaEventCreateWithFlags(&s->sent, cudaEventDisableTiming));
   return s;
   B2_API_END(nullptr)
@@ -191,134 +206,159 @@ B2Slab b2_slab_create(B2Mpm mpm, B2Comm comm, int32_t rank, int32_t world, int32
 void b2_slab_destroy(B2Slab s) {
   if (!s) return;
   cudaStreamSynchronize(b2_current_stream());
+  if (s->prof) slab_prof_print(s);
+  for (cudaEvent_t e : s->pev) cudaEventDestroy(e);
   if (s->comm_stream) {
     cudaStreamSynchronize(s->comm_stream);
-    for (int k = 0; k < 3; k++) cudaEventDestroy(s->ready[k]), cudaEventDestroy(s->arrived[k]);
-    cudaEventDestroy(s->arrived2), cudaEventDestroy(s->sent);
+    for (int k = 0; k < 2; k++) cudaEventDestroy(s->ready[k]), cudaEventDestroy(s->arrived_lo[k]), cudaEventDestroy(s->arrived_hi[k]);
+    cudaEventDestroy(s->sent);
     cudaStreamDestroy(s->comm_stream);
   }
   for (void *p : s->allocs) cudaFree(p);
   delete s;
 }
 
-// The decomposed substep: four compute phases on the runtime's stream, three exchanges on the slab's comm stream.
-//   phase 0: clear, P2G, pack ghost layer hi                                  -> ready[0]
-//   A      : ghost layer -> rank + 1                                            (waits ready[0]; -> arrived[0] on the receiver)
-//   phase 1: grid-op on every block outside layer lo  ||  A in flight
-//            wait arrived[0]: add ghosts into layer lo, grid-op on layer lo, pack layer lo   -> ready[1]
-//   B      : owned layer lo -> rank - 1 (becomes its ghost layer)               (waits ready[1]; -> arrived[1])
-//   phase 2: G2P on every bin outside layer hi - 1  ||  B in flight
-//            wait arrived[1]: overwrite ghost layer, G2P on the bins of layer hi - 1, extract migrants  -> ready[2]
-//   C      : migrants <-> rank +- 1                                             (waits ready[2]; -> arrived[2])
-//   phase 3: wait arrived[2]: insert arrivals
-// With overlap off (B2_SLAB_OVERLAP=0) the same calls run unsplit and the comm stream is the compute stream.
+// The decomposed substep: three compute phases on the runtime's stream, two exchanges on the slab's comm stream.
+//   phase 0: clear, P2G, pack my ghost layer hi (for rank + 1) and my owned layer lo (for rank - 1)        -> ready[0]
+//   X      : both layers travel in ONE group: every node of a shared layer ends up with BOTH ranks' contributions on BOTH
+//            ranks (a + b == b + a bit for bit), so the owner's post-grid-op values never have to travel back
+//   phase 1: wait for X; add what arrived (from below: into my layer lo, activating; from above: into my ghost layer, existing
+//            blocks only); grid-op on every block incl. the ghost layer (pointwise: identical on both ranks); G2P; extract
+//            migrants                                                                                        -> ready[1]
+//   C      : migrants <-> rank +- 1
+//   phase 2: wait for C; insert arrivals
+// r1 sent the ghost layer up (A), ran the grid-op, and sent the finished layer back down (B): two dependent exchanges per
+// substep.  Measured on 2 B200 (B2_SLAB_PROF): running interior blocks / bins under A and B hid 40-60 us of waiting but the
+// boundary-only G2P launch that followed cost 56 us at 11 % machine fill; the symmetric exchange removes B altogether.
 static void slab_phase(B2Slab_t *s, int ph) {
   B2Mpm m = s->mpm;
   cudaStream_t st = s->rt->stream();
   const int64_t capA = (s->sendA_bytes - HEADER) / BLOCK_REC, capB = (s->sendB_bytes - HEADER) / BLOCK_REC;
   const int64_t capL = (s->sendL_bytes - HEADER) / PART_REC, capR = (s->sendR_bytes - HEADER) / PART_REC;
-  const bool multi = s->world > 1, split = multi && s->overlap;
+  const bool multi = s->world > 1;
   switch (ph) {
     case 0:
+      s->mark(st);  // 0
       ok0(b2_mpm_begin_substep(m));
       ok0(b2_mpm_clear_grid(m));
       if (multi) ok0(b2_mpm_zero_headers(m, s->up >= 0 ? s->sendA : nullptr, s->down >= 0 ? s->sendB : nullptr, s->down >= 0 ? s->sendL : nullptr,
                                          s->up >= 0 ? s->sendR : nullptr));
       ok0(b2_mpm_p2g(m));
+      s->mark(st);  // 1: clear + P2G
       if (s->up >= 0) ok0(b2_mpm_pack_blocks(m, s->hi, s->sendA, capA));
+      if (s->down >= 0) ok0(b2_mpm_pack_blocks(m, s->lo, s->sendB, capB));
       if (multi) B2_CUDA(cudaEventRecord(s->ready[0], st));
+      s->mark(st);  // 2: pack both layers
       break;
     case 1:
-      if (split && s->down >= 0) ok0(b2_mpm_grid_op_layer(m, 2, s->lo));  // everything but the layer that receives ghosts
-      if (multi) B2_CUDA(cudaStreamWaitEvent(st, s->arrived[0], 0));
+      if (multi) {
+        B2_CUDA(cudaStreamWaitEvent(st, s->arrived_lo[0], 0));
+        B2_CUDA(cudaStreamWaitEvent(st, s->arrived_hi[0], 0));
+      }
+      s->mark(st);  // 3: wait for X
       if (s->down >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvA, (s->recvA_bytes - HEADER) / BLOCK_REC, 0));
-      if (split && s->down >= 0)
-        ok0(b2_mpm_grid_op_layer(m, 1, s->lo));
-      else
-        ok0(b2_mpm_grid_op(m));
-      if (s->down >= 0) ok0(b2_mpm_pack_blocks(m, s->lo, s->sendB, capB));
-      if (multi) B2_CUDA(cudaEventRecord(s->ready[1], st));
-      break;
-    case 2:
-      if (split && s->up >= 0) ok0(b2_mpm_g2p_layer(m, 2, s->hi - 1, 0));  // bins that never read the ghost layer
-      if (multi) B2_CUDA(cudaStreamWaitEvent(st, s->arrived[1], 0));
-      if (s->up >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvB, (s->recvB_bytes - HEADER) / BLOCK_REC, 1));
-      if (split && s->up >= 0)
-        ok0(b2_mpm_g2p_layer(m, 1, s->hi - 1, 1));
-      else
-        ok0(b2_mpm_g2p(m));
+      if (s->up >= 0) ok0(b2_mpm_unpack_blocks(m, s->recvB, (s->recvB_bytes - HEADER) / BLOCK_REC, 2));
+      s->mark(st);  // 4: add arrivals
+      ok0(b2_mpm_grid_op(m));
+      s->mark(st);  // 5: grid-op
+      ok0(b2_mpm_g2p(m));
+      s->mark(st);  // 6: G2P
       if (multi) ok0(b2_mpm_extract_migrants2(m, s->down >= 0 ? s->sendL : nullptr, capL, s->up >= 0 ? s->sendR : nullptr, capR));
-      if (multi) B2_CUDA(cudaEventRecord(s->ready[2], st));
+      if (multi) B2_CUDA(cudaEventRecord(s->ready[1], st));
+      s->mark(st);  // 7: extract migrants
       break;
     default:
       if (multi) {
-        B2_CUDA(cudaStreamWaitEvent(st, s->arrived[2], 0));
-        if (s->comm->loopback) B2_CUDA(cudaStreamWaitEvent(st, s->arrived2, 0));
+        B2_CUDA(cudaStreamWaitEvent(st, s->arrived_lo[1], 0));
+        B2_CUDA(cudaStreamWaitEvent(st, s->arrived_hi[1], 0));
         B2_CUDA(cudaStreamWaitEvent(st, s->sent, 0));  // the send buffers are packed again by the next substep
+      }
+      s->mark(st);  // 8: wait for C
+      if (multi)
         ok0(b2_mpm_insert_records2(m, s->up >= 0 ? s->recvR : nullptr, (s->recvR_bytes - HEADER) / PART_REC, s->down >= 0 ? s->recvL : nullptr,
                                    (s->recvL_bytes - HEADER) / PART_REC));
-      }
+      s->mark(st);  // 9: insert arrivals
       ok0(b2_mpm_end_substep(m));
   }
 }
-// exchange ex of this rank, enqueued on its comm stream behind ready[ex]
+// exchange ex (0: ghost / owned layers, 1: migrants) of this rank, enqueued on its comm stream behind ready[ex]
 static void slab_exchange(B2Slab_t *s, int ex) {
   if (s->world == 1) return;
   cudaStream_t sc = s->overlap ? s->comm_stream : s->rt->stream();
   B2_CUDA(cudaStreamWaitEvent(sc, s->ready[ex], 0));
+  const uint8_t *to_up = ex == 0 ? s->sendA : s->sendR, *to_down = ex == 0 ? s->sendB : s->sendL;
+  const int64_t up_bytes = ex == 0 ? s->sendA_bytes : s->sendR_bytes, down_bytes = ex == 0 ? s->sendB_bytes : s->sendL_bytes;
+  uint8_t *from_down = ex == 0 ? s->recvA : s->recvL, *from_up = ex == 0 ? s->recvB : s->recvR;
+  const int64_t from_down_bytes = ex == 0 ? s->recvA_bytes : s->recvL_bytes, from_up_bytes = ex == 0 ? s->recvB_bytes : s->recvR_bytes;
   if (s->comm->loopback) {
     // a "send" is a device-to-device copy into the peer's receive buffer; the peer's arrived event follows the copy
-    auto put = [&](const uint8_t *src, int64_t bytes, int dst, int which, bool second) {
-      B2Slab_t *p = s->comm->peers[dst];
-      B2_CUDA(cudaMemcpyAsync(recv_buffer(p, which), src, (size_t)bytes, cudaMemcpyDeviceToDevice, sc));
-      B2_CUDA(cudaEventRecord(second ? p->arrived2 : p->arrived[ex], sc));
-    };
-    if (ex == 0 && s->up >= 0) put(s->sendA, s->sendA_bytes, s->up, 0, false);
-    if (ex == 1 && s->down >= 0) put(s->sendB, s->sendB_bytes, s->down, 1, false);
-    if (ex == 2) {
-      if (s->down >= 0) put(s->sendL, s->sendL_bytes, s->down, 3, true);   // my left migrants arrive at the lower rank from above
-      if (s->up >= 0) put(s->sendR, s->sendR_bytes, s->up, 2, false);      // my right migrants arrive at the upper rank from below
+    if (s->up >= 0) {
+      B2Slab_t *p = s->comm->peers[s->up];
+      B2_CUDA(cudaMemcpyAsync(ex == 0 ? p->recvA : p->recvL, to_up, (size_t)up_bytes, cudaMemcpyDeviceToDevice, sc));
+      B2_CUDA(cudaEventRecord(p->arrived_lo[ex], sc));
+    } else {
+      B2_CUDA(cudaEventRecord(s->arrived_hi[ex], sc));  // nothing will arrive from above: the wait must not dangle
     }
-    // ranks at the ends of the chain receive nothing in some exchanges: their wait must not dangle
-    if (ex == 0 && s->down < 0) B2_CUDA(cudaEventRecord(s->arrived[0], sc));
-    if (ex == 1 && s->up < 0) B2_CUDA(cudaEventRecord(s->arrived[1], sc));
-    if (ex == 2 && s->down < 0) B2_CUDA(cudaEventRecord(s->arrived[2], sc));
-    if (ex == 2 && s->up < 0) B2_CUDA(cudaEventRecord(s->arrived2, sc));
-    if (ex == 2) B2_CUDA(cudaEventRecord(s->sent, sc));
+    if (s->down >= 0) {
+      B2Slab_t *p = s->comm->peers[s->down];
+      B2_CUDA(cudaMemcpyAsync(ex == 0 ? p->recvB : p->recvR, to_down, (size_t)down_bytes, cudaMemcpyDeviceToDevice, sc));
+      B2_CUDA(cudaEventRecord(p->arrived_hi[ex], sc));
+    } else {
+      B2_CUDA(cudaEventRecord(s->arrived_lo[ex], sc));
+    }
+    if (ex == 1) B2_CUDA(cudaEventRecord(s->sent, sc));
     return;
   }
   NcclApi &n = nccl();
   B2_NCCL(n.GroupStart());
-  if (ex == 0) {
-    if (s->up >= 0) B2_NCCL(n.Send(s->sendA, (size_t)s->sendA_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
-    if (s->down >= 0) B2_NCCL(n.Recv(s->recvA, (size_t)s->recvA_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
-  } else if (ex == 1) {
-    if (s->down >= 0) B2_NCCL(n.Send(s->sendB, (size_t)s->sendB_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
-    if (s->up >= 0) B2_NCCL(n.Recv(s->recvB, (size_t)s->recvB_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
-  } else {
-    if (s->down >= 0) {
-      B2_NCCL(n.Send(s->sendL, (size_t)s->sendL_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
-      B2_NCCL(n.Recv(s->recvL, (size_t)s->recvL_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
-    }
-    if (s->up >= 0) {
-      B2_NCCL(n.Send(s->sendR, (size_t)s->sendR_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
-      B2_NCCL(n.Recv(s->recvR, (size_t)s->recvR_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
-    }
+  if (s->down >= 0) {
+    B2_NCCL(n.Send(to_down, (size_t)down_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
+    B2_NCCL(n.Recv(from_down, (size_t)from_down_bytes, NCCL_UINT8, s->down, s->comm->comm, sc));
+  }
+  if (s->up >= 0) {
+    B2_NCCL(n.Send(to_up, (size_t)up_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
+    B2_NCCL(n.Recv(from_up, (size_t)from_up_bytes, NCCL_UINT8, s->up, s->comm->comm, sc));
   }
   B2_NCCL(n.GroupEnd());
-  B2_CUDA(cudaEventRecord(s->arrived[ex], sc));
-  if (ex == 2) B2_CUDA(cudaEventRecord(s->sent, sc));
+  B2_CUDA(cudaEventRecord(s->arrived_lo[ex], sc));
+  B2_CUDA(cudaEventRecord(s->arrived_hi[ex], sc));
+  if (ex == 1) B2_CUDA(cudaEventRecord(s->sent, sc));
 }
 
+static void slab_prof_print(B2Slab_t *s) {
+  static const char *names[9] = {"clear+p2g", "pack", "wait_X", "unpack", "grid_op", "g2p", "extract", "wait_C", "insert"};
+  if (!s->pcount) return;
+  fprintf(stderr, "[b2_slab rank %d/%d] per substep over %lld substeps (ms):", s->rank, s->world, s->pcount);
+  double tot = 0;
+  for (int k = 0; k < 9; k++) fprintf(stderr, " %s %.4f", names[k], s->psum[k] / s->pcount), tot += s->psum[k] / s->pcount;
+  fprintf(stderr, " | total %.4f\n", tot);
+  for (int k = 0; k < 12; k++) s->psum[k] = 0;
+  s->pcount = 0;
+}
+static void slab_prof_collect(B2Slab_t *s) {
+  if (!s->prof || s->pev_n == 0) return;
+  cudaEventSynchronize(s->pev[s->pev_n - 1]);
+  for (size_t b = 0; b + 10 <= s->pev_n; b += 10) {
+    for (int k = 0; k < 9; k++) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, s->pev[b + k], s->pev[b + k + 1]);
+      s->psum[k] += ms;
+    }
+    s->pcount++;
+  }
+  s->pev_n = 0;
+  if (s->prof_every > 0 && s->pcount >= s->prof_every) slab_prof_print(s);
+}
 int32_t b2_slab_substep(B2Slab s, int32_t nsteps) {
   B2_API_BEGIN
   require(s != nullptr, TI_ERROR_ARGUMENT_NULL, "slab");
   require(s->world == 1 || !s->comm->loopback, TI_ERROR_INVALID_STATE, "loopback slabs advance together: b2_slab_substep_lockstep");
   for (int it = 0; it < nsteps; it++)
-    for (int ph = 0; ph < 4; ph++) {
+    for (int ph = 0; ph < 3; ph++) {
       slab_phase(s, ph);
-      if (ph < 3) slab_exchange(s, ph);
+      if (ph < 2) slab_exchange(s, ph);
     }
+  slab_prof_collect(s);
   return 0;
   B2_API_END(-1)
 }
@@ -330,9 +370,9 @@ int32_t b2_slab_substep_lockstep(B2Slab *slabs, int32_t world, int32_t nsteps) {
     require(slabs[r] != nullptr && slabs[r]->world == world && slabs[r]->rank == r && (world == 1 || slabs[r]->comm->loopback), TI_ERROR_INVALID_ARGUMENT,
             "slabs[r] must be rank r of one loopback communicator");
   for (int it = 0; it < nsteps; it++)
-    for (int ph = 0; ph < 4; ph++) {
+    for (int ph = 0; ph < 3; ph++) {
       for (int r = 0; r < world; r++) slab_phase(slabs[r], ph);
-      if (ph < 3)
+      if (ph < 2)
         for (int r = 0; r < world; r++) slab_exchange(slabs[r], ph);
     }
   return 0;
