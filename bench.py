@@ -95,24 +95,40 @@ def make_slab_cloud(world, rank, per_rank, n_grid):
     return x, v, np.zeros((n, 3, 3), np.float32), np.ones(n, np.float32), ids
 
 
-def make_c5_cloud(world, rank, total, n_grid):
+def c5_ball(b, total, n_grid):
+    per_ball = total // 6
+    radius = (3.0 * per_ball / 9.7 / (4.0 * np.pi)) ** (1.0 / 3.0) / n_grid
+    rng = np.random.default_rng(5 + b)
+    n = per_ball if b < 5 else total - 5 * per_ball
+    d = rng.standard_normal((n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    r = np.float32(radius) * rng.random(n, dtype=np.float32) ** np.float32(1.0 / 3.0)
+    return (np.array([0.1 + 0.8 * (b + 0.5) / 6.0, 0.6 if b % 2 == 0 else 0.35, 0.5], np.float32) + d * r[:, None]).astype(np.float32)
+
+
+def c5_bounds(world, total, n_grid):
+    """Static slabs cut by the initial particle count per block layer (--slabs weighted)."""
+    from taichi_b200 import multigpu as mg
+    w = np.zeros(n_grid // 4, np.float64)
+    for b in range(6):
+        x = c5_ball(b, total, n_grid)
+        bx = ((x[:, 0] * np.float32(n_grid) - np.float32(0.5)).astype(np.int32)) >> 2
+        w += np.bincount(bx, minlength=n_grid // 4)[:n_grid // 4]
+    return mg.weighted_slab_bounds(w, world)
+
+
+def make_c5_cloud(world, rank, total, n_grid, bounds=None):
     """the C3 cloud scaled x8 -- SIX balls spread along x (seed 5), same particle density as C3 (ball radius
     64 cells at 1024^3 for 64M particles), v = (0.5,-1,0).  Slabs are static, so the ranks' loads differ (SURVEY hard part 7)."""
     from taichi_b200 import multigpu as mg
     per_ball = total // 6
-    radius = (3.0 * per_ball / 9.7 / (4.0 * np.pi)) ** (1.0 / 3.0) / n_grid
     xs, ids = [], []
     for b in range(6):
-        rng = np.random.default_rng(5 + b)
-        n = per_ball if b < 5 else total - 5 * per_ball
-        d = rng.standard_normal((n, 3)).astype(np.float32)
-        d /= np.linalg.norm(d, axis=1, keepdims=True)
-        r = np.float32(radius) * rng.random(n, dtype=np.float32) ** np.float32(1.0 / 3.0)
-        x = (np.array([0.1 + 0.8 * (b + 0.5) / 6.0, 0.6 if b % 2 == 0 else 0.35, 0.5], np.float32) + d * r[:, None]).astype(np.float32)
-        keep = mg.partition_particles(x, n_grid, world) == rank
+        x = c5_ball(b, total, n_grid)
+        keep = mg.partition_particles(x, n_grid, world, bounds) == rank
         xs.append(np.ascontiguousarray(x[keep]))
         ids.append(np.flatnonzero(keep).astype(np.int32) + np.int32(b * per_ball))
-        del d, r, x, keep
+        del x, keep
     x, ids = np.concatenate(xs), np.concatenate(ids)
     n = len(x)
     v = np.tile(np.array([0.5, -1.0, 0.0], np.float32), (n, 1))
@@ -401,12 +417,15 @@ def run_slabs(args, world, rank, local):
     total_c5 = 64 * 1024 * 1024 if args.strong else per_rank * world
     desc = ("sparse 3D MLS-MPM 1024^3 pointer->bitmasked->dense(4^3), " +
             ("64M particles in total (strong scaling), " if args.strong else "8M particles/GPU (weak scaling), ") +
-            ("SURVEY C5 cloud: six balls along x, static slabs (unbalanced), " if args.cloud == "c5" else
+            ("SURVEY C5 cloud: six balls along x, static slabs " + ("cut by initial particle count, " if args.slabs == "weighted" else "(equal width: unbalanced), ") if args.cloud == "c5" else
              "one ball per slab + half a ball on every slab boundary (balanced), ") + "slabs along i, halo exchange + migration")
     rt = tb.Runtime(local, device_memory_GB=6)
     lo, hi = mg.slab_bounds(n_grid // 4, world, rank)
     if args.cloud == "c5":
-        x, v, Cm, J, ids = make_c5_cloud(world, rank, total_c5, n_grid)
+        bounds = c5_bounds(world, total_c5, n_grid) if args.slabs == "weighted" else None
+        if bounds is not None:
+            lo, hi = bounds[rank]
+        x, v, Cm, J, ids = make_c5_cloud(world, rank, total_c5, n_grid, bounds)
     else:
         assert not args.strong, "--strong uses --cloud c5"
         x, v, Cm, J, ids = make_slab_cloud(world, rank, per_rank, n_grid)
@@ -488,7 +507,7 @@ def run_slabs(args, world, rank, local):
         "metric": "MPM particle-updates/s", "value": value, "unit": "particle-updates/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if args.strong else "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "n_grid": n_grid, "particles_total": n_total, "particles_per_rank": per_rank_counts, "cloud": args.cloud,
+        "config": {"workload": desc, "n_grid": n_grid, "particles_total": n_total, "particles_per_rank": per_rank_counts, "cloud": args.cloud, "slabs": args.slabs,
                    "substeps_per_step": SUBSTEPS, "dt": dt,
                    "l2": "particle state per GPU (>=512 MiB/substep) exceeds the 126 MB L2: no flush needed",
                    "parallelism": f"slab{world}: 1 process/GPU, ncclSend/ncclRecv ghost-layer + migrant exchange enqueued from C++, no data-path collective"},
@@ -533,6 +552,8 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="skip the lifecycle / listgen / reduction blocks")
     ap.add_argument("--cloud", default="balanced", choices=["balanced", "c5"],
                     help="N > 1: balanced = one ball per slab (+ boundary balls), c5 = SURVEY C5: six balls along x under static slabs")
+    ap.add_argument("--slabs", default="equal", choices=["equal", "weighted"],
+                    help="--cloud c5: equal-width slabs, or static slabs cut so every rank starts with the same particle count")
     ap.add_argument("--force-slabs", action="store_true", help="N = 1 through the slab driver on the N > 1 workload (what one rank of a weak-scaling run does, minus the exchange)")
     ap.add_argument("--strong", action="store_true", help="N > 1 with --cloud c5: 64M particles in total at every N (also N = 1 via torchrun)")
     args = ap.parse_args()

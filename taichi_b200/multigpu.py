@@ -36,6 +36,25 @@ def slab_bounds(nb, world, rank):
     return lo, hi
 
 
+def weighted_slab_bounds(layer_weight, world, unit=8):
+    """Static slabs cut by load: [(lo, hi)] over block layers along i such that every rank's share of sum(layer_weight)
+    is as even as pointer-cell alignment (unit layers) allows; every rank keeps at least one unit."""
+    w = np.asarray(layer_weight, np.float64)
+    nb = len(w)
+    if nb % unit != 0 or nb // unit < world:
+        unit = 1
+    cells = nb // unit
+    cw = np.concatenate([[0.0], np.cumsum(w.reshape(cells, unit).sum(1))])
+    cuts = [0]
+    for r in range(1, world):
+        c = int(np.searchsorted(cw, cw[-1] * r / world, side="left"))
+        if c > 0 and abs(cw[c - 1] - cw[-1] * r / world) <= abs(cw[min(c, cells)] - cw[-1] * r / world):
+            c -= 1
+        cuts.append(min(max(c, cuts[-1] + 1), cells - (world - r)))
+    cuts.append(cells)
+    return [(cuts[r] * unit, cuts[r + 1] * unit) for r in range(world)]
+
+
 class CudaSlab:
     """Backend over libb200mpm.so: one Mpm3D restricted to [lo, hi) block layers."""
 
@@ -320,13 +339,13 @@ def _recv_for(self, ph, k, src):
 SlabDriver._recv_for = _recv_for
 
 
-def partition_particles(x, n_grid, world):
-    """Rank that owns each particle: the slab of the block of its base cell."""
+def partition_particles(x, n_grid, world, bounds=None):
+    """Rank that owns each particle: the slab of the block of its base cell (bounds: [(lo, hi)] per rank, default equal slabs)."""
     nb = n_grid // 4
     base = (x[:, 0].astype(np.float32) * np.float32(n_grid) - np.float32(0.5)).astype(np.int32)
     bx = base >> 2
     owner = np.zeros(len(x), np.int32)
     for r in range(world):
-        lo, hi = slab_bounds(nb, world, r)
+        lo, hi = bounds[r] if bounds is not None else slab_bounds(nb, world, r)
         owner[(bx >= lo) & (bx < hi)] = r
     return owner

@@ -67,6 +67,31 @@ def test_slab_bounds_cover_domain():
             assert all(lo % 8 == 0 for lo, _ in b)             # pointer-cell aligned
 
 
+def test_weighted_slab_bounds():
+    """Slabs cut by particle count: contiguous cover, aligned to pointer cells, loads within one unit's weight of even."""
+    rng = np.random.default_rng(3)
+    w = np.zeros(256)
+    for c in (40, 90, 130, 170, 215):
+        w += 1e6 * np.exp(-0.5 * ((np.arange(256) - c) / 9.0) ** 2)
+    for world in (2, 3, 4, 8):
+        b = mg.weighted_slab_bounds(w, world)
+        assert b[0][0] == 0 and b[-1][1] == 256
+        assert all(b[r][1] == b[r + 1][0] for r in range(world - 1))
+        assert all(lo % 8 == 0 and hi > lo for lo, hi in b)
+        load = np.array([w[lo:hi].sum() for lo, hi in b])
+        assert load.max() - w.sum() / world <= w.reshape(32, 8).sum(1).max() + 1e-6
+        eq = np.array([w[slice(*mg.slab_bounds(256, world, r))].sum() for r in range(world)])
+        assert load.max() <= eq.max() + 1e-6
+    # degenerate: all the load in one unit still leaves every rank a slab
+    w = np.zeros(64); w[3] = 5.0
+    b = mg.weighted_slab_bounds(w, 4)
+    assert all(hi > lo for lo, hi in b) and b[-1][1] == 64
+    x = rng.random((1000, 3)).astype(np.float32)
+    own = mg.partition_particles(x, 256, 4, bounds=[(0, 8), (8, 16), (16, 40), (40, 64)])
+    bx = ((x[:, 0] * np.float32(256) - np.float32(0.5)).astype(np.int32)) >> 2
+    assert np.array_equal(own, np.digitize(bx, [8, 16, 40]))
+
+
 @pytest.mark.parametrize("world", [2, 4])
 def test_lockstep_slabs_match_single_domain(world):
     ranks = [make_rank(r, world) for r in range(world)]
