@@ -355,6 +355,15 @@ TI_DLL_EXPORT int32_t b2_field_reduce(B2Tree tree, int32_t place, int32_t op, in
 TI_DLL_EXPORT int32_t b2_reduce(TiRuntime runtime, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_host);
 /* same, enqueue only: the 4-byte result lands in device memory (no host round trip) */
 TI_DLL_EXPORT int32_t b2_reduce_device(TiRuntime runtime, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_dev);
+/* b2_reduce_device for callers that must not allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+   No counterpart in the reference.  Same arguments and result (4 bytes in device
+   memory, enqueued on the runtime's stream); the per-CTA partials and the arrival ticket live in a static __device__ array of
+   8448 bytes that every GPU loading the library holds until exit, so the call allocates nothing (no cudaMalloc / cudaFree /
+   stream-ordered allocation).  n <= B2_REDUCE_NOALLOC_MAX_N, else TI_ERROR_ARGUMENT_OUT_OF_RANGE.  The partials are folded in
+   index order: the result is deterministic for a given n, and differs from b2_reduce_device's only by fp32 summation order.
+   All calls share the array: calls that overlap on the GPU (two streams, two host threads on one device) race. */
+#define B2_REDUCE_NOALLOC_MAX_N (1ll << 28)
+TI_DLL_EXPORT int32_t b2_reduce_noalloc(TiRuntime runtime, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_dev);
 
 /* runtime-level */
 TI_DLL_EXPORT void b2_sync(TiRuntime runtime);

@@ -159,6 +159,7 @@ SIGNATURES = {
     "b2_field_reduce": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "b2_reduce": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
     "b2_reduce_device": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
+    "b2_reduce_noalloc": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
     "b2_sync": (None, [C.c_void_p]),
     "b2_device_index": (C.c_int32, [C.c_void_p]),
     "b2_pool_bytes_used": (C.c_int64, [C.c_void_p]),

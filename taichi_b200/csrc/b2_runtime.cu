@@ -60,6 +60,7 @@ void b2_set_pool_size(uint64_t bytes) { g_pool_size = bytes; }
 // ------------------------------------------------------------------------------------------
 // runtime
 // ------------------------------------------------------------------------------------------
+static void b2_noalloc_setup(int device);  // address of the static scratch of b2_reduce_noalloc (below)
 TiRuntime_t::TiRuntime_t(int device_index) : device(device_index) {
   int count = 0;
   cudaError_t e = cudaGetDeviceCount(&count);
@@ -91,6 +92,7 @@ TiRuntime_t::TiRuntime_t(int device_index) : device(device_index) {
   h.size = pool_size;
   B2_CUDA(cudaMemcpyAsync(pool_dev, &h, sizeof(h), cudaMemcpyHostToDevice, stream()));
   B2_CUDA(cudaStreamSynchronize(stream()));
+  b2_noalloc_setup(device_index);
 }
 TiRuntime_t::~TiRuntime_t() {
   cudaSetDevice(device);
@@ -840,6 +842,79 @@ __global__ void __launch_bounds__(256) k_reduce(const V *data, long long n, int 
 }
 __global__ void k_set_u32(u32 *dst, u32 v) { *dst = v; }
 
+// ---- allocation-free reduction (b2_reduce_noalloc) -------------------------------------------------------------
+// The per-CTA partials and the arrival ticket live in a file-scope device array instead of a buffer from cudaMalloc: every
+// GPU that loads the library holds B2_NOALLOC_SCRATCH_BYTES of it until the process exits.  Word 0 is the ticket, the
+// partials start at word 64 (their own 256-byte line).  All calls share the array: two calls that overlap on the GPU race.
+#define B2_NOALLOC_MAX_CTAS 2048
+#define B2_NOALLOC_MAX_N ((long long)B2_NOALLOC_MAX_CTAS * 256 * 512) /* 2^28 elements = 1 GiB of f32 / i32 */
+#define B2_NOALLOC_SCRATCH_WORDS (64 + B2_NOALLOC_MAX_CTAS)
+static __device__ __align__(256) u32 b2_noalloc_scratch[B2_NOALLOC_SCRATCH_WORDS];
+static u32 *g_noalloc_scratch[64];  // the array's DEVICE address per device (the name above is only a host-side stand-in)
+
+// set-up, once per device, with that device current (runtime construction)
+static void b2_noalloc_setup(int device) {
+  if (device < 0 || device >= 64 || g_noalloc_scratch[device]) return;
+  u32 *ptr = nullptr;
+  B2_CUDA(cudaGetSymbolAddress((void **)&ptr, b2_noalloc_scratch));
+  if (!ptr) throw B2Error(TI_ERROR_INVALID_STATE, "cudaGetSymbolAddress(b2_noalloc_scratch) returned null");
+  g_noalloc_scratch[device] = ptr;
+}
+template <typename V>
+__device__ __forceinline__ V b2_block_reduce_value(V acc, V ident, int op) {  // valid in thread 0
+  __shared__ V part[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) acc = b2_red_op(acc, __shfl_down_sync(0xffffffffu, acc, d), op);
+  __syncthreads();
+  if (lane == 0) part[warp] = acc;
+  __syncthreads();
+  V v = (warp == 0 && lane < nw) ? part[lane] : ident;
+  if (warp == 0) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v = b2_red_op(v, __shfl_down_sync(0xffffffffu, v, d), op);
+  }
+  return v;
+}
+// two stages in one launch: every CTA leaves its partial in the scratch array, the CTA that draws the last ticket folds
+// the partials in index order (the result does not depend on which CTA that is) and hands the ticket back as zero
+template <typename V>
+__global__ void __launch_bounds__(256) k_reduce_noalloc(const V *data, long long n, int op, V ident, u32 *scratch, V *dst) {
+  __shared__ int is_last;
+  V *partial = (V *)(scratch + 64);
+  V acc = ident;
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  if ((((unsigned long long)data) & 15ull) == 0) {
+    const long long n4 = n >> 2;
+    const uint4 *d4 = (const uint4 *)data;
+    for (long long i = tid; i < n4; i += nth) {
+      V v[4];
+      const uint4 a = d4[i];
+      memcpy(v, &a, 16);
+      acc = b2_red_op(b2_red_op(acc, v[0], op), b2_red_op(v[1], b2_red_op(v[2], v[3], op), op), op);
+    }
+    for (long long j = (n4 << 2) + tid; j < n; j += nth) acc = b2_red_op(acc, data[j], op);
+  } else {
+    for (long long i = tid; i < n; i += nth) acc = b2_red_op(acc, data[i], op);
+  }
+  const V mine = b2_block_reduce_value<V>(acc, ident, op);
+  if (threadIdx.x == 0) {
+    __stcg(partial + blockIdx.x, mine);
+    __threadfence();
+    is_last = atomicAdd(scratch, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  V fold = ident;
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) fold = b2_red_op(fold, __ldcg(partial + i), op);
+  fold = b2_block_reduce_value<V>(fold, ident, op);
+  if (threadIdx.x == 0) {
+    *dst = fold;
+    *scratch = 0u;
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // coordinate-list kernels (activate / deactivate / is_active / read / write / dynamic)
 // ------------------------------------------------------------------------------------------
@@ -1425,6 +1500,36 @@ int32_t b2_reduce_device(TiRuntime rt, const void *data_dev, int64_t n, int32_t 
     }
     rt->count_launch();
   }
+  B2_CUDA(cudaGetLastError());
+  return 0;
+  B2_API_END(-1)
+}
+// Allocation-free variant of b2_reduce_device: no cudaMalloc / cudaFree / stream-ordered allocation on this path; the
+// scratch is the static device array above.  n <= B2_NOALLOC_MAX_N.
+int32_t b2_reduce_noalloc(TiRuntime rt, const void *data_dev, int64_t n, int32_t op, int32_t dtype, void *out_dev) {
+  B2_API_BEGIN
+  require(rt && out_dev, TI_ERROR_ARGUMENT_NULL, "runtime/out");
+  require(op >= 0 && op <= 2 && (dtype == 0 || dtype == 1), TI_ERROR_INVALID_ARGUMENT, "op/dtype");
+  require(n >= 0, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "b2_reduce_noalloc: n < 0");
+  if (n > B2_NOALLOC_MAX_N)
+    throw B2Error(TI_ERROR_ARGUMENT_OUT_OF_RANGE, "b2_reduce_noalloc: n = " + std::to_string((long long)n) + " exceeds the static scratch's maximum of " +
+                                                      std::to_string(B2_NOALLOC_MAX_N) + " elements (use b2_reduce_device)");
+  require(n == 0 || data_dev, TI_ERROR_ARGUMENT_NULL, "data");
+  require(rt->device >= 0 && rt->device < 64 && g_noalloc_scratch[rt->device], TI_ERROR_INVALID_STATE,
+          "b2_reduce_noalloc: the scratch array was not set up for this device");
+  u32 *scratch = g_noalloc_scratch[rt->device];
+  cudaStream_t st = rt->stream();
+  const u32 id = ident_bits(op, dtype);
+  B2_CUDA(cudaMemsetAsync(scratch, 0, 4, st));  // the ticket starts at zero whatever an earlier (aborted) call left
+  int grid = (int)std::min<long long>(B2_NOALLOC_MAX_CTAS, std::max<long long>(1, rt->grid_for(std::max<int64_t>(n, 1), 256 * 16, 8)));
+  if (dtype == 0) {
+    float idf;
+    memcpy(&idf, &id, 4);
+    k_reduce_noalloc<float><<<grid, 256, 0, st>>>((const float *)data_dev, n, op, idf, scratch, (float *)out_dev);
+  } else {
+    k_reduce_noalloc<int><<<grid, 256, 0, st>>>((const int *)data_dev, n, op, (int)id, scratch, (int *)out_dev);
+  }
+  rt->count_launch();
   B2_CUDA(cudaGetLastError());
   return 0;
   B2_API_END(-1)
