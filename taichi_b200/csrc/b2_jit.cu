@@ -18,7 +18,7 @@
 
 #include "b2_host.h"
 #include "b2_jit.cuh"
-#include "build/b2_embed.h"  // b2_src_internal / b2_src_jit / b2_src_svd: the device headers as text
+#include "b2_embed.h"        // b2_src_internal / b2_src_jit / b2_src_svd: the device headers as text
 
 namespace {
 typedef struct _nvrtcProgram *nvrtcProgram;

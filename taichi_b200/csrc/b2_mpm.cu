@@ -37,6 +37,9 @@ __device__ __forceinline__ void red_add_v4(float4 *addr, float4 v) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 __device__ __forceinline__ int ld_volatile_i32(const int *p) { return *(const volatile int *)p; }
+#ifndef MPM_SPIN_LIMIT
+#define MPM_SPIN_LIMIT (1u << 24) /* polls (a few seconds) before a wait on another CTA's publication gives up and flags an error */
+#endif
 __device__ __forceinline__ u32 ld_volatile_u32(const u32 *p) { return *(const volatile u32 *)p; }
 
 // Container of the 4^3 block (bx,by,bz); ACT activates every level above it.  nullptr if the
@@ -148,10 +151,15 @@ __device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, in
   }
   __syncwarp();
   if (valid && (slot == -1 || slot == -2)) {  // somebody else is creating the slot: wait for the outcome
-    unsigned ns = 8;
+    unsigned ns = 8, polls = 0;
     while ((slot = ld_volatile_i32(&M.slot_of[key])) == -2) {
       __nanosleep(ns);
       if (ns < 256) ns *= 2;
+      if (++polls > MPM_SPIN_LIMIT) {  // (the creator is gone: flag it, drop the particle)
+        b2_set_error(M.T->pool, B2E_ASSERT, -1002);
+        slot = -3;
+        break;
+      }
     }
     __threadfence();
   }
@@ -189,10 +197,15 @@ __device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, in
   __syncwarp();
   if (valid) {
     u32 id1;
-    unsigned ns = 8;
+    unsigned ns = 8, polls = 0;
     while ((id1 = ld_volatile_u32(cslot)) == 0) {
       __nanosleep(ns);
       if (ns < 256) ns *= 2;
+      if (++polls > MPM_SPIN_LIMIT) {  // (the chunk's holder is gone: flag it, the data goes to the sink chunk)
+        b2_set_error(M.T->pool, B2E_ASSERT, -1001);
+        id1 = M.arena_cap + 1;
+        break;
+      }
     }
     u8 *ch = mpm_chunk_ptr(M, gen, id1);
     ((float4 *)ch)[i] = p0;
@@ -466,6 +479,7 @@ __global__ void __launch_bounds__(256) k_mpm_mark_listed(MpmDev M) {
 #include "b2_f32x2.cuh"
 #include "b2_mpm_bls.cuh"
 #include "b2_mpm_p2gw.cuh"
+#include "b2_mpm_g2po.cuh"
 
 // Plain path (ti.block_local off): every particle walks the SNode tree with activation and issues
 // one vector red per node -- the reference's non-BLS access pattern (K15) on the binned particles.
@@ -800,6 +814,7 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   M.slot_of = dalloc<int>(nblocks, 0xFF);
   M.slot_key = dalloc<int>(M.max_slots);
   M.nslots = dalloc<u32>(4);
+  M.nbptr = dalloc<u64>((size_t)M.max_slots * 8);
   for (int g = 0; g < 2; g++) {
     M.count[g] = dalloc<u32>(M.max_slots);
     M.chunk_of[g] = dalloc<u32>((size_t)M.max_slots * M.maxc);
@@ -938,7 +953,7 @@ void B2Mpm_t::g2p() {
   if (prm.block_local) {
     static const bool no_order = getenv("B2_G2P_SORT") != nullptr;  // experiment switch: always sort
     if (order_valid && !no_order)
-      k_mpm_g2p_bls<64, 20, true><<<rt->num_sms * 20, 64, 0, st>>>(M, gen);
+      k_mpm_g2p_ord<G2PK_T, G2PK_MINB><<<rt->num_sms * G2PK_MINB, G2PK_T, 0, st>>>(M, gen);
     else
       k_mpm_g2p_bls<64, 12, false><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
   } else {

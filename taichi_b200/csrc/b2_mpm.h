@@ -39,6 +39,7 @@ struct MpmDev {
   // two particle generations (read g, write g^1)
   u32 *count[2];     // [max_slots]
   u32 *chunk_of[2];  // [max_slots * maxc] chunk id + 1
+  u64 *nbptr;        // [max_slots * 8] the bin's neighbour blocks {0,1}^3 as P2G resolved them (valid until the G2P of the substep)
   u32 *live[2];      // [max_slots * MPM_MAXPASS] live (non-tombstone) entries per pass, written by P2G
   u8 *arena[2];
   u32 *arena_next[2];

@@ -7,7 +7,15 @@
 // Tombstones (p0.x == MPM_TOMB, left behind by particles that moved to another block) sort into
 // bin 64 and are skipped.
 #pragma once
-
+#ifndef G2PK_T
+#define G2PK_T 64    /* threads per CTA of the ordered (PERM) G2P */
+#endif
+#ifndef G2PK_MINB
+#define G2PK_MINB 20 /* CTAs per SM */
+#endif
+#ifndef G2P_F2
+#define G2P_F2 1 /* packed fp32x2 gather of the x / y components */
+#endif
 
 template <int SB>
 struct MpmSortSmemT {
@@ -98,6 +106,91 @@ __device__ __forceinline__ void mpm_sort_pass(const MpmDev &M, MpmSortSmemT<SB> 
     if (c < 64) S.perm[S.start[c] + (int)(k & 0xffffu)] = (unsigned short)t;
   }
   __syncthreads();
+}
+
+// One particle of G2P (mpm3d.py:62-79): gather v and the affine matrix C from the 27 nodes of the block's (4+2)^3 pad, advect,
+// and find the particle's new block / cell.  id only labels the error of a particle that leaves the grid.
+__device__ __forceinline__ void mpm_g2p_particle(const MpmDev &M, const float4 *pad, const float4 p0, u32 id, float4 &o0, float4 &o1,
+                                                 float4 &o2, float4 &o3, int &nkey, int &ncell) {
+  MpmStencil s;
+  mpm_stencil(M, p0.x, p0.y, p0.z, s);
+  float v0, v1, v2, Sx0, Sx1, Sx2, Sy0, Sy1, Sy2, Sz0, Sz1, Sz2;
+  const int l0 = s.base[0] & 3, l1 = s.base[1] & 3, l2 = s.base[2] & 3;
+  const float wz0 = s.w[0][2], wz1 = s.w[1][2], wz2 = s.w[2][2];
+#if G2P_F2
+  {  // x and y components travel as one packed fp32x2 (FFMA2 / FMUL2 / FADD2: the same roundings as the scalar form,
+     // half the issue slots); the pad's float4 {vx, vy, vz, m} hands (vx, vy) over as an aligned register pair
+    u64 vxy = 0ull, Sxxy = 0ull, Syxy = 0ull, Szxy = 0ull;
+    v2 = 0.f, Sx2 = 0.f, Sy2 = 0.f, Sz2 = 0.f;
+    const u64 wz0p = f2_pack(wz0, wz0), wz1p = f2_pack(wz1, wz1), wz2p = f2_pack(wz2, wz2), twop = f2_pack(2.f, 2.f);
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+#pragma unroll
+      for (int j = 0; j < 3; j++) {
+        const float wxy = s.w[i][0] * s.w[j][1];
+        const u64 wp = f2_pack(wxy, wxy);
+        const int pidx = ((l0 + i) * 6 + (l1 + j)) * 6 + l2;
+        const float4 g0 = pad[pidx], g1v = pad[pidx + 1], g2 = pad[pidx + 2];
+        const u64 t1 = f2_mul(wz1p, f2_pack(g1v.x, g1v.y)), t2 = f2_mul(wz2p, f2_pack(g2.x, g2.y));
+        const u64 r = f2_fma(wz0p, f2_pack(g0.x, g0.y), f2_add(t1, t2)), z = f2_fma(twop, t2, t1);
+        const float t1z = wz1 * g1v.z, t2z = wz2 * g2.z;
+        const float rzv = fmaf(wz0, g0.z, t1z + t2z), zz = fmaf(2.f, t2z, t1z);
+        vxy = f2_fma(wp, r, vxy), v2 = fmaf(wxy, rzv, v2);
+        Szxy = f2_fma(wp, z, Szxy), Sz2 = fmaf(wxy, zz, Sz2);
+        if (j > 0) {
+          const float wj = (float)j * wxy;
+          Syxy = f2_fma(f2_pack(wj, wj), r, Syxy), Sy2 = fmaf(wj, rzv, Sy2);
+        }
+        if (i > 0) {
+          const float wi = (float)i * wxy;
+          Sxxy = f2_fma(f2_pack(wi, wi), r, Sxxy), Sx2 = fmaf(wi, rzv, Sx2);
+        }
+      }
+    }
+    f2_unpack(vxy, v0, v1), f2_unpack(Sxxy, Sx0, Sx1), f2_unpack(Syxy, Sy0, Sy1), f2_unpack(Szxy, Sz0, Sz1);
+  }
+#else
+  v0 = 0.f, v1 = 0.f, v2 = 0.f;
+  Sx0 = 0.f, Sx1 = 0.f, Sx2 = 0.f, Sy0 = 0.f, Sy1 = 0.f, Sy2 = 0.f, Sz0 = 0.f, Sz1 = 0.f, Sz2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const float wxy = s.w[i][0] * s.w[j][1];
+      const int pidx = ((l0 + i) * 6 + (l1 + j)) * 6 + l2;
+      const float4 g0 = pad[pidx], g1v = pad[pidx + 1], g2 = pad[pidx + 2];
+      // row = sum_k wz_k g_k ; rz = sum_k k wz_k g_k
+      const float t1x = wz1 * g1v.x, t1y = wz1 * g1v.y, t1z = wz1 * g1v.z;
+      const float t2x = wz2 * g2.x, t2y = wz2 * g2.y, t2z = wz2 * g2.z;
+      const float rx = fmaf(wz0, g0.x, t1x + t2x), ry = fmaf(wz0, g0.y, t1y + t2y), rzv = fmaf(wz0, g0.z, t1z + t2z);
+      const float zx = fmaf(2.f, t2x, t1x), zy = fmaf(2.f, t2y, t1y), zz = fmaf(2.f, t2z, t1z);
+      v0 = fmaf(wxy, rx, v0), v1 = fmaf(wxy, ry, v1), v2 = fmaf(wxy, rzv, v2);
+      Sz0 = fmaf(wxy, zx, Sz0), Sz1 = fmaf(wxy, zy, Sz1), Sz2 = fmaf(wxy, zz, Sz2);
+      if (j > 0) {
+        const float wj = (float)j * wxy;
+        Sy0 = fmaf(wj, rx, Sy0), Sy1 = fmaf(wj, ry, Sy1), Sy2 = fmaf(wj, rzv, Sy2);
+      }
+      if (i > 0) {
+        const float wi = (float)i * wxy;
+        Sx0 = fmaf(wi, rx, Sx0), Sx1 = fmaf(wi, ry, Sx1), Sx2 = fmaf(wi, rzv, Sx2);
+      }
+    }
+  }
+#endif
+  // C[a][b] = 4/dx * (sum w g_a o_b - fx_b v_a)   (mpm3d.py:75 with dpos = (o - fx) dx)
+  const float k4 = 4.0f * M.inv_dx;
+  const float C00 = k4 * (Sx0 - s.fx[0] * v0), C01 = k4 * (Sy0 - s.fx[1] * v0), C02 = k4 * (Sz0 - s.fx[2] * v0);
+  const float C10 = k4 * (Sx1 - s.fx[0] * v1), C11 = k4 * (Sy1 - s.fx[1] * v1), C12 = k4 * (Sz1 - s.fx[2] * v1);
+  const float C20 = k4 * (Sx2 - s.fx[0] * v2), C21 = k4 * (Sy2 - s.fx[1] * v2), C22 = k4 * (Sz2 - s.fx[2] * v2);
+  const float nx = p0.x + M.dt * v0, ny = p0.y + M.dt * v1, nz = p0.z + M.dt * v2;
+  const float nJ = p0.w * (1.0f + M.dt * (C00 + C11 + C22));
+  o0 = make_float4(nx, ny, nz, nJ);
+  o1 = make_float4(v0, v1, v2, C00);
+  o2 = make_float4(C01, C02, C10, C11);
+  o3 = make_float4(C12, C20, C21, C22);
+  bool ok;
+  nkey = mpm_key_of_position(M, nx, ny, nz, &ok, &ncell);
+  if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)id);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -227,52 +320,7 @@ __global__ void __launch_bounds__(G2P_THREADS, G2P_MINB) k_mpm_g2p_bls(MpmDev M,
           np0 = ((const float4 *)ch)[q % MPM_CHUNK];
           nid = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[q % MPM_CHUNK];
         }
-        if (valid) {
-          MpmStencil s;
-          mpm_stencil(M, p0.x, p0.y, p0.z, s);
-          float v0 = 0.f, v1 = 0.f, v2 = 0.f;
-          float Sx0 = 0.f, Sx1 = 0.f, Sx2 = 0.f, Sy0 = 0.f, Sy1 = 0.f, Sy2 = 0.f, Sz0 = 0.f, Sz1 = 0.f, Sz2 = 0.f;
-          const int l0 = s.base[0] & 3, l1 = s.base[1] & 3, l2 = s.base[2] & 3;
-          const float wz0 = s.w[0][2], wz1 = s.w[1][2], wz2 = s.w[2][2];
-#pragma unroll
-          for (int i = 0; i < 3; i++) {
-#pragma unroll
-            for (int j = 0; j < 3; j++) {
-              const float wxy = s.w[i][0] * s.w[j][1];
-              const int pidx = ((l0 + i) * 6 + (l1 + j)) * 6 + l2;
-              const float4 g0 = sPad[pidx], g1v = sPad[pidx + 1], g2 = sPad[pidx + 2];
-              // row = sum_k wz_k g_k ; rz = sum_k k wz_k g_k
-              const float t1x = wz1 * g1v.x, t1y = wz1 * g1v.y, t1z = wz1 * g1v.z;
-              const float t2x = wz2 * g2.x, t2y = wz2 * g2.y, t2z = wz2 * g2.z;
-              const float rx = fmaf(wz0, g0.x, t1x + t2x), ry = fmaf(wz0, g0.y, t1y + t2y), rzv = fmaf(wz0, g0.z, t1z + t2z);
-              const float zx = fmaf(2.f, t2x, t1x), zy = fmaf(2.f, t2y, t1y), zz = fmaf(2.f, t2z, t1z);
-              v0 = fmaf(wxy, rx, v0), v1 = fmaf(wxy, ry, v1), v2 = fmaf(wxy, rzv, v2);
-              Sz0 = fmaf(wxy, zx, Sz0), Sz1 = fmaf(wxy, zy, Sz1), Sz2 = fmaf(wxy, zz, Sz2);
-              if (j > 0) {
-                const float wj = (float)j * wxy;
-                Sy0 = fmaf(wj, rx, Sy0), Sy1 = fmaf(wj, ry, Sy1), Sy2 = fmaf(wj, rzv, Sy2);
-              }
-              if (i > 0) {
-                const float wi = (float)i * wxy;
-                Sx0 = fmaf(wi, rx, Sx0), Sx1 = fmaf(wi, ry, Sx1), Sx2 = fmaf(wi, rzv, Sx2);
-              }
-            }
-          }
-          // C[a][b] = 4/dx * (sum w g_a o_b - fx_b v_a)   (mpm3d.py:75 with dpos = (o - fx) dx)
-          const float k4 = 4.0f * M.inv_dx;
-          const float C00 = k4 * (Sx0 - s.fx[0] * v0), C01 = k4 * (Sy0 - s.fx[1] * v0), C02 = k4 * (Sz0 - s.fx[2] * v0);
-          const float C10 = k4 * (Sx1 - s.fx[0] * v1), C11 = k4 * (Sy1 - s.fx[1] * v1), C12 = k4 * (Sz1 - s.fx[2] * v1);
-          const float C20 = k4 * (Sx2 - s.fx[0] * v2), C21 = k4 * (Sy2 - s.fx[1] * v2), C22 = k4 * (Sz2 - s.fx[2] * v2);
-          const float nx = p0.x + M.dt * v0, ny = p0.y + M.dt * v1, nz = p0.z + M.dt * v2;
-          const float nJ = p0.w * (1.0f + M.dt * (C00 + C11 + C22));
-          o0 = make_float4(nx, ny, nz, nJ);
-          o1 = make_float4(v0, v1, v2, C00);
-          o2 = make_float4(C01, C02, C10, C11);
-          o3 = make_float4(C12, C20, C21, C22);
-          bool ok;
-          nkey = mpm_key_of_position(M, nx, ny, nz, &ok, &ncell);
-          if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)id);
-        }
+        if (valid) mpm_g2p_particle(M, sPad, p0, id, o0, o1, o2, o3, nkey, ncell);
         const bool stay = valid && nkey == key;
         const unsigned smask = __ballot_sync(0xffffffffu, stay);
         if (smask) {

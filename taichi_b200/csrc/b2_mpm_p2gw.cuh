@@ -316,6 +316,7 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, CTAS) k_mpm_p2g(MpmDev M, int 
         if (!p) p = mpm_block_ptr<true>(M, nx, ny, nz);
       }
       S.nb[lane] = p;
+      M.nbptr[(u64)slot * 8 + (u32)lane] = (u64)p;  // G2P finds the bin's neighbour blocks without walking the tree again
     }
     __syncwarp();
     for (int nidx = lane; nidx < 216; nidx += 32) {
