@@ -374,8 +374,9 @@ B2Tree_t::B2Tree_t(TiRuntime_t *rt_, const B2SNodeDesc *desc, int n) : rt(rt_) {
       B2NodeMgr &m = (*hm)[im];
       memset(&m, 0, sizeof(m));
       m.elem_size = (u64)x.alloc_size;
-      int lg = 0;
-      while (lg < 14 && ((u64)x.alloc_size << (lg + 1)) <= (64ull << 20)) lg++;
+      int lg = 0;  // elements per data chunk: chunks of <= 64 MB, and <= 1/16 of the pool so that a small pool still holds several
+      const u64 chunk_cap = std::min<u64>(64ull << 20, rt->pool_size / 16);
+      while (lg < 14 && ((u64)x.alloc_size << (lg + 1)) <= chunk_cap) lg++;
       m.log2_epc = lg;
       for (int k = 0; k < 2; k++) {
         m.free_list[k].elem_size = 4;
