@@ -401,7 +401,7 @@ def test_out_of_memory_never_writes_the_ambient_node():
     buf = C.create_string_buffer(256)
     assert lib.b2_check_runtime_error(rt, buf, 256) != 0 and b"pool exhausted" in buf.value
     act = np.zeros(4096, np.uint8)
-    cells = coords12(np.arange(4096, dtype=np.int32)[:, None] * 65536)   # (kept alive: vp() of a temporary dangles)
+    cells = coords12(np.arange(4096, dtype=np.int32))   # ti.is_active(p, [i]) takes indices at p's OWN resolution
     lib.b2_is_active(tree, p, vp(cells), 4096, vp(act))
     L.check()
     n_act = int(act.sum())
