@@ -952,7 +952,10 @@ void B2Mpm_t::g2p() {
   }
   if (prm.block_local) {
     static const bool no_order = getenv("B2_G2P_SORT") != nullptr;  // experiment switch: always sort
-    if (order_valid && !no_order)
+    static const bool r1_form = getenv("B2_G2P_R1") != nullptr;  // experiment switch: the r1 bin prologue
+    if (order_valid && !no_order && r1_form)
+      k_mpm_g2p_bls<G2PK_T, G2PK_MINB, true><<<rt->num_sms * G2PK_MINB, G2PK_T, 0, st>>>(M, gen);
+    else if (order_valid && !no_order)
       k_mpm_g2p_ord<G2PK_T, G2PK_MINB><<<rt->num_sms * G2PK_MINB, G2PK_T, 0, st>>>(M, gen);
     else
       k_mpm_g2p_bls<64, 12, false><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);

@@ -36,10 +36,7 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
 
   for (;;) {
     __syncthreads();  // everybody has left the previous bin
-    if (tid == 0) {
-      sSlot = next;
-      if (next < nslots) next = atomicAdd(&M.work_counter[1], 1u);  // (consumed one bin later)
-    }
+    if (tid == 0) sSlot = next;
     __syncthreads();
     const u32 slot = sSlot;
     if (slot >= nslots) break;
@@ -49,7 +46,10 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
     const u32 live0 = M.live[gen][(u64)slot * MPM_MAXPASS];
     if (tid < 32) sIn[tid] = mpm_chunk_ptr(M, gen, max(M.chunk_of[gen][(u64)slot * M.maxc + min((u32)tid, (u32)M.maxc - 1u)], 1u));
     if (tid >= NT - 8) sNb[tid - (NT - 8)] = (float4 *)M.nbptr[(u64)slot * 8 + (u32)(tid - (NT - 8))];
-    if (total == 0) continue;  // (uniform)
+    if (total == 0) {  // (uniform; rare: slots are compacted)
+      if (tid == 0) next = atomicAdd(&M.work_counter[1], 1u);
+      continue;
+    }
     __syncthreads();
     for (u32 q0 = 0; q0 < total; q0 += MPM_PASS) {
       const int n = (int)min((u32)MPM_PASS, total - q0);
@@ -77,6 +77,9 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
       }
       asm volatile("cp.async.wait_all;" ::: "memory");
       __syncthreads();  // order, pad, base
+      // the slot after this one, consumed one bin later.  Not requested at the very start of the kernel, where every CTA's
+      // first request queues up on the one counter: with fewer bins than CTAs (config C2) that cost 10 us of 53
+      if (q0 == 0 && tid == 0) next = atomicAdd(&M.work_counter[1], 1u);
       if (nlive == 0) continue;  // (uniform)
       const u32 base = sBase;
       const u32 c0 = base / MPM_CHUNK;
