@@ -127,5 +127,7 @@ struct B2Tree_t {
   void deactivate_all(int sid);
   // one level only (listgen of that level + deactivate body + GC if it is a pointer SNode); reset_list: child list := empty
   void deactivate_level_async(int sid);
+  // deactivate_all + GC of a pointer SNode with one container under the root, one launch (+ two lists and a bitmap emptied)
+  void deactivate_all_gc_async(int sid, unsigned char *container, int list_a, int list_b, void *zero, size_t zero_bytes);
   void reset_list_async(int sid);
 };

@@ -67,6 +67,8 @@ struct B2NodeMgr {
   u32 free_used;  // consumed since last GC   (free_list_used)
   u32 cur;        // which of free_list[2] is live
   u32 gc_ticket;  // last-CTA-done counter of the fused GC kernel
+  u32 gc_bar;     // arrival counter of the grid barrier of k_deactivate_all_gc
+  u32 pad_;
   u64 ambient;    // zero node returned for inactive reads
   u64 data_chunks[B2_MGR_MAX_CHUNKS];
   B2CList free_list[2];

@@ -692,6 +692,7 @@ struct B2Mpm_t {
   u32 *count_sp = nullptr, *chunk_sp = nullptr, *nslots_sp = nullptr;  // spare slot tables for compact_bins()
   int *key_sp = nullptr;
   int compact_every = 64;       // substeps between two bin-slot compactions
+  size_t listed_bytes = 0;  // size of M.listed (multiple of 16)
   bool in_substep = false;  // inside substep(): k_mpm_clear resets the work counters / arena cursor for the phases that follow
   std::vector<cudaEvent_t> prof_events;
   double phase_sum[6] = {0, 0, 0, 0, 0, 0};
@@ -829,7 +830,8 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   if (const char *e = getenv("B2_COMPACT_EVERY")) compact_every = atoi(e);
   M.dbg = getenv("B2_DBG") ? atoi(getenv("B2_DBG")) : 0;
   M.work_counter = dalloc<u32>(8);
-  M.listed = dalloc<u32>((size_t)(nblocks + 31) / 32);
+  listed_bytes = ((size_t)(nblocks + 31) / 32 * 4 + 15) / 16 * 16;
+  M.listed = dalloc<u32>(listed_bytes / 4);
   M.stats = dalloc<double>(8);
   B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
   B2_CUDA(cudaFuncSetAttribute(k_mpm_p2g<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(P2W_WARPS * sizeof(P2WWarp))));
@@ -1004,11 +1006,17 @@ void B2Mpm_t::substep(int n) {
       // zero-filled by the fused GC; the leaf list is regenerated (empty) and P2G activates what it touches
       if (prm.layout == 1) {
         // pointer -> bitmasked: the bitmasked container (cells + mask) IS the pointer level's NodeManager element, and the
-        // fused GC zero-fills recycled elements whole -- mask included -- so the children need no pass of their own:
-        // root listgen + deactivate body + GC = 3 launches; the leaf list and its bitmap are simply emptied
-        tree->deactivate_level_async(1);
-        tree->reset_list_async(2), tree->reset_list_async(M.leaf_sid);
-        B2_CUDA(cudaMemsetAsync(M.listed, 0, (size_t)((int64_t)M.nb * M.nb * M.nb + 31) / 32 * 4, st));
+        // fused GC zero-fills recycled elements whole -- mask included -- so the children need no pass of their own.
+        // ONE launch: deactivate every cell of the pointer container, grid barrier, GC; the lists of the two levels below
+        // and the leaf bitmap are emptied by the same kernel (r2 v3 used 3 launches + 3 memsets: 0.042 ms per substep)
+        static const bool unfused = getenv("B2_LIFECYCLE_UNFUSED") != nullptr;  // experiment switch
+        if (unfused) {
+          tree->deactivate_level_async(1);
+          tree->reset_list_async(2), tree->reset_list_async(M.leaf_sid);
+          B2_CUDA(cudaMemsetAsync(M.listed, 0, listed_bytes, st));
+        } else {
+          tree->deactivate_all_gc_async(1, M.top, 2, M.leaf_sid, M.listed, listed_bytes);
+        }
         lists_valid = true;
       } else {
         tree->deactivate_all(1);

@@ -1045,7 +1045,7 @@ __global__ void k_export_list(B2TreeDev *T, int sid, int *out, long long cap) {
 //   last CTA to finish swaps the lists and resets the counters             (gc_parallel_1)
 // ------------------------------------------------------------------------------------------
 #define B2_GC_SEG (32 * 1024)
-__global__ void __launch_bounds__(256) k_gc(B2TreeDev *T, int sid) {
+__device__ __forceinline__ void b2_gc_body(B2TreeDev *T, int sid) {
   B2NodeMgr *m = T->mgr[sid];
   const u32 cur = m->cur;
   B2CList *F0 = &m->free_list[cur], *F1 = &m->free_list[cur ^ 1];
@@ -1085,9 +1085,44 @@ __global__ void __launch_bounds__(256) k_gc(B2TreeDev *T, int sid) {
       F0->count = 0;
       m->cur = cur ^ 1;
       m->gc_ticket = 0;
+      m->gc_bar = 0;
       __threadfence();
     }
   }
+}
+__global__ void __launch_bounds__(256) k_gc(B2TreeDev *T, int sid) { b2_gc_body(T, sid); }
+
+// SNode.deactivate_all + GC of a pointer SNode whose ONE container sits directly under the root, in a single launch (the sparse
+// life cycle of the MPM solver runs it every substep): every active cell is deactivated and its node recycled, a grid barrier
+// (all CTAs are resident: the grid is sized from the occupancy), then the fused GC above.  Also empties up to two element
+// lists and a bitmap that the caller derives from the SNode's cells.  Replaces listgen + deactivate body + GC + three memsets.
+__global__ void __launch_bounds__(256) k_deactivate_all_gc(B2TreeDev *T, int sid, u8 *node, int ncells, u32 *count_a, u32 *count_b, uint4 *zero16,
+                                                           long long n_zero16) {
+  B2NodeMgr *m = T->mgr[sid];
+  const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x, gsize = (long long)gridDim.x * blockDim.x;
+  for (long long i = gtid; i < ncells; i += gsize) b2_deactivate_cell(T, sid, node, (int)i);
+  for (long long i = gtid; i < n_zero16; i += gsize) zero16[i] = make_uint4(0, 0, 0, 0);
+  if (gtid == 0) {
+    if (count_a) *count_a = 0;
+    if (count_b) *count_b = 0;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    atomicAdd(&m->gc_bar, 1u);
+    unsigned ns = 32, polls = 0;
+    while (*(volatile u32 *)&m->gc_bar < gridDim.x) {
+      __nanosleep(ns);
+      if (ns < 256) ns *= 2;
+      if (++polls > (1u << 23)) {  // (seconds: part of the grid never became resident; flag it -- nodes recycled after this
+        b2_set_error(T->pool, B2E_ASSERT, -1004);  // point are collected by the next GC)
+        break;
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+  b2_gc_body(T, sid);
 }
 
 void B2Tree_t::gc_async(int sid) {
@@ -1100,6 +1135,22 @@ void B2Tree_t::gc_async(int sid) {
 
 __global__ void k_deactivate_root_dynamic(B2TreeDev *T, int dsid) {
   b2_deactivate_cell(T, dsid, T->root + T->s[dsid].offset_in_parent_cell, 0);
+}
+void B2Tree_t::deactivate_all_gc_async(int sid, u8 *container, int list_a, int list_b, void *zero, size_t zero_bytes) {
+  check_snode(sid, "deactivate_all_gc");
+  if (s[sid].type != B2T_POINTER) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "deactivate_all_gc: pointer SNode");
+  if (zero_bytes % 16 != 0) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "deactivate_all_gc: bitmap size");
+  static int per_sm = 0;  // CTAs of the kernel that fit one SM (the grid barrier needs all of them resident)
+  if (per_sm == 0) {
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_deactivate_all_gc, 256, 0));
+    per_sm = std::max(1, std::min(per_sm, 4));
+  }
+  k_deactivate_all_gc<<<rt->num_sms * per_sm, 256, 0, rt->stream()>>>(dev, sid, container, (int)s[sid].num_cells,
+                                                                      list_a >= 0 ? &host_copy.lists[list_a]->count : nullptr,
+                                                                      list_b >= 0 ? &host_copy.lists[list_b]->count : nullptr, (uint4 *)zero,
+                                                                      (long long)(zero_bytes / 16));
+  rt->count_launch();
+  B2_CUDA(cudaGetLastError());
 }
 void B2Tree_t::reset_list_async(int sid) {
   check_snode(sid, "reset_list");
