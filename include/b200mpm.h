@@ -395,6 +395,12 @@ typedef struct B2MpmParams {
   int64_t max_particles;
   int64_t max_bins;          /* occupied 4^3 blocks the particle bins can hold at once; 0 = max(4096, max_particles / 64).
                                 Vacated bins are recycled by a compaction pass every 64 substeps. */
+  int32_t model;             /* 0: mpm3d.py (weakly compressible, J).  1: deformation gradient F + plastic Jp + material per
+                                particle with ti.svd -- the mpm128.py:36-63 constitutive model (liquid 0 / jelly 1 / snow 2)
+                                carried to 3-D as in ggui_examples/mpm3d_ggui.py:52-88; E, nu give mu_0, lambda_0 */
+  float nu;                  /* model 1: Poisson's ratio (mpm128.py:16)                                                     */
+  float p_vol;               /* > 0: particle volume (default (dx / 2)^2 as mpm3d.py:17)                                    */
+  int32_t pad_;
 } B2MpmParams;
 
 TI_DLL_EXPORT B2Mpm b2_mpm_create(TiRuntime runtime, const B2MpmParams *params);
@@ -409,6 +415,12 @@ TI_DLL_EXPORT int32_t b2_mpm_leaf_snode(B2Mpm mpm);   /* id of the dense(4^3) SN
 TI_DLL_EXPORT int32_t b2_mpm_set_particles(B2Mpm mpm, int64_t n, const float *x_any, const float *v_any, const float *C_any, const float *J_any);
 TI_DLL_EXPORT int32_t b2_mpm_add_particles(B2Mpm mpm, int64_t n, const float *x_any, const float *v_any, const float *C_any, const float *J_any, const int32_t *ids_any);
 TI_DLL_EXPORT int64_t b2_mpm_num_particles(B2Mpm mpm);
+/* model 1: the same with F[N][3][3], Jp[N], material[N] (int32: 0 liquid, 1 jelly, 2 snow); NULL = identity / 1 / 0.
+ * Host or device arrays; the get returns F and Jp as the reference holds them after the same number of substeps. */
+TI_DLL_EXPORT int32_t b2_mpm_set_particles_model(B2Mpm mpm, int64_t n, const float *x_any, const float *v_any, const float *C_any,
+                                                 const float *F_any, const float *Jp_any, const int32_t *material_any);
+TI_DLL_EXPORT int32_t b2_mpm_get_particles_model(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *F_any, float *Jp_any,
+                                                 int32_t *material_any);
 /* Any pointer may be NULL. Output is in original particle-id order. */
 TI_DLL_EXPORT int32_t b2_mpm_get_particles(B2Mpm mpm, float *x_any, float *v_any, float *C_any, float *J_any);
 /* Same, but host arrays are filled by a copy stream after return (the D2H half of kernel_launcher.cpp:175-186

@@ -36,7 +36,8 @@ class B2MpmParams(C.Structure):
     _fields_ = [("n_grid", C.c_int32), ("layout", C.c_int32), ("dt", C.c_float), ("E", C.c_float),
                 ("p_rho", C.c_float), ("gravity", C.c_float), ("bound", C.c_int32),
                 ("block_local", C.c_int32), ("bls_activate_halo", C.c_int32),
-                ("slab_lo", C.c_int32), ("slab_hi", C.c_int32), ("deactivate_every", C.c_int32), ("max_particles", C.c_int64), ("max_bins", C.c_int64)]
+                ("slab_lo", C.c_int32), ("slab_hi", C.c_int32), ("deactivate_every", C.c_int32), ("max_particles", C.c_int64), ("max_bins", C.c_int64),
+                ("model", C.c_int32), ("nu", C.c_float), ("p_vol", C.c_float), ("pad_", C.c_int32)]
 
 
 class TiMemoryAllocateInfo(C.Structure):
@@ -173,6 +174,8 @@ SIGNATURES = {
     "b2_mpm_set_particles": (C.c_int32, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2_mpm_add_particles": (C.c_int32, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2_mpm_num_particles": (C.c_int64, [C.c_void_p]),
+    "b2_mpm_set_particles_model": (C.c_int32, [C.c_void_p, C.c_int64] + [C.c_void_p] * 6),
+    "b2_mpm_get_particles_model": (C.c_int32, [C.c_void_p] + [C.c_void_p] * 6),
     "b2_mpm_get_particles": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2_mpm_get_particles_async": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2_mpm_wait_io": (C.c_int32, [C.c_void_p]),

@@ -29,6 +29,7 @@
 
 #include "b2_host.h"
 #include "b2_mpm.h"
+#include "b2_svd.cuh"
 
 // ------------------------------------------------------------------------------------------
 // device helpers
@@ -120,11 +121,25 @@ __device__ __forceinline__ void mpm_unkey(const MpmDev &M, int key, int &bx, int
 }
 
 __device__ __forceinline__ u8 *mpm_chunk_ptr(const MpmDev &M, int gen, u32 id1) { return M.arena[gen] + (u64)(id1 - 1) * MPM_CHUNK_BYTES; }
+__device__ __forceinline__ u8 *mpm_xchunk_ptr(const MpmDev &M, int gen, u32 id1) { return M.xarena[gen] + (u64)(id1 - 1) * MPM_XCHUNK_BYTES; }
+// model 1: the particle's F (row-major), Jp and material as three float4
+struct MpmX {
+  float4 a, b, c;  // {F00,F01,F02,F10} {F11,F12,F20,F21} {F22,Jp,material bits,0}
+};
+__device__ __forceinline__ MpmX mpm_x_load(const u8 *xch, u32 i) {
+  MpmX r;
+  r.a = ((const float4 *)xch)[i], r.b = ((const float4 *)(xch + MPM_PLANE_BYTES))[i], r.c = ((const float4 *)(xch + 2 * MPM_PLANE_BYTES))[i];
+  return r;
+}
+__device__ __forceinline__ void mpm_x_store(u8 *xch, u32 i, const MpmX &r) {
+  ((float4 *)xch)[i] = r.a, ((float4 *)(xch + MPM_PLANE_BYTES))[i] = r.b, ((float4 *)(xch + 2 * MPM_PLANE_BYTES))[i] = r.c;
+}
 
 // Appends one particle to the bin of block `key` in generation `gen`.  Must be called by all 32
 // lanes of the warp (valid = false for idle lanes): lanes that go to the same bin share one
 // atomicAdd (match_any), the lane that opens a new chunk allocates it, the others wait for it.
-__device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, int cell, bool valid, float4 p0, float4 p1, float4 p2, float4 p3, u32 id) {
+__device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, int cell, bool valid, float4 p0, float4 p1, float4 p2, float4 p3, u32 id,
+                                           const MpmX *px = nullptr) {
   const int lane = threadIdx.x & 31;
   int slot = -1;
   if (valid) {
@@ -214,6 +229,7 @@ __device__ __forceinline__ void mpm_insert(const MpmDev &M, int gen, int key, in
     ((float4 *)(ch + 3 * MPM_PLANE_BYTES))[i] = p3;
     ((u32 *)(ch + 4 * MPM_PLANE_BYTES))[i] = id;
     (ch + MPM_CELL_OFF)[i] = (u8)cell;
+    if (px) mpm_x_store(mpm_xchunk_ptr(M, gen, id1), i, *px);
   }
 }
 
@@ -247,7 +263,8 @@ __device__ __forceinline__ int mpm_key_of_position(const MpmDev &M, float x, flo
 // x[N][3] v[N][3] C[N][3][3] J[N] (reference field layouts) -> bins of generation gen
 __global__ void __launch_bounds__(256) k_mpm_insert(MpmDev M, int gen, const float *__restrict__ x, const float *__restrict__ v,
                                                      const float *__restrict__ C, const float *__restrict__ J, const int *__restrict__ ids,
-                                                     long long n, long long id0) {
+                                                     long long n, long long id0, const float *__restrict__ Fm = nullptr,
+                                                     const float *__restrict__ Jp = nullptr, const int *__restrict__ mat = nullptr) {
   const long long nround = (n + 31) / 32 * 32;
   for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < nround; p += (long long)gridDim.x * blockDim.x) {
     const bool valid = p < n;
@@ -268,11 +285,26 @@ __global__ void __launch_bounds__(256) k_mpm_insert(MpmDev M, int gen, const flo
       key = mpm_key_of_position(M, p0.x, p0.y, p0.z, &ok, &cell);
       if (!ok) b2_set_error(M.T->pool, B2E_ASSERT, (int)p);
     }
-    mpm_insert(M, gen, key, cell, valid, p0, p1, p2, p3, id);
+    if (M.model) {  // F = identity, Jp = 1, material 0 unless given
+      MpmX X;
+      X.a = make_float4(1.f, 0.f, 0.f, 0.f), X.b = make_float4(1.f, 0.f, 0.f, 0.f), X.c = make_float4(1.f, 1.f, 0.f, 0.f);
+      if (valid) {
+        if (Fm) {
+          const float *f = Fm + p * 9;
+          X.a = make_float4(f[0], f[1], f[2], f[3]), X.b = make_float4(f[4], f[5], f[6], f[7]), X.c.x = f[8];
+        }
+        if (Jp) X.c.y = Jp[p];
+        if (mat) X.c.z = __int_as_float(mat[p]);
+      }
+      mpm_insert(M, gen, key, cell, valid, p0, p1, p2, p3, id, &X);
+    } else {
+      mpm_insert(M, gen, key, cell, valid, p0, p1, p2, p3, id);
+    }
   }
 }
 
-__global__ void __launch_bounds__(256) k_mpm_extract(MpmDev M, int gen, float *x, float *v, float *C, float *J, long long nmax) {
+__global__ void __launch_bounds__(256) k_mpm_extract(MpmDev M, int gen, float *x, float *v, float *C, float *J, long long nmax, float *Fm = nullptr,
+                                                      float *Jp = nullptr, int *mat = nullptr) {
   const u32 ns = *M.nslots;
   for (u32 slot = blockIdx.x; slot < ns; slot += gridDim.x) {
     const u32 cnt = M.count[gen][slot];
@@ -294,6 +326,84 @@ __global__ void __launch_bounds__(256) k_mpm_extract(MpmDev M, int gen, float *x
         float *c = C + (u64)id * 9;
         c[0] = p1.w, c[1] = p2.x, c[2] = p2.y, c[3] = p2.z, c[4] = p2.w, c[5] = p3.x, c[6] = p3.y, c[7] = p3.z, c[8] = p3.w;
       }
+      if (M.model && (Fm || Jp || mat)) {
+        const MpmX X = mpm_x_load(mpm_xchunk_ptr(M, gen, id1), i);
+        if (Fm) {
+          float *f = Fm + (u64)id * 9;
+          f[0] = X.a.x, f[1] = X.a.y, f[2] = X.a.z, f[3] = X.a.w, f[4] = X.b.x, f[5] = X.b.y, f[6] = X.b.z, f[7] = X.b.w, f[8] = X.c.x;
+        }
+        if (Jp) Jp[id] = X.c.y;
+        if (mat) mat[id] = __float_as_int(X.c.z);
+      }
+    }
+  }
+}
+
+// model 1, before P2G (mpm128.py:36-63 carried to 3-D, ggui_examples/mpm3d_ggui.py:52-88): F <- (I + dt C) F, hardening from Jp,
+// ti.svd, snow plasticity (singular values clamped, Jp updated), liquid reset, fixed-corotated stress.  The kernel leaves
+// affine / p_mass = C + stress / p_mass in the particle's C planes and J = 1, so that the P2G kernel, which scatters
+// p_mass v + (stress_k (J - 1) I + p_mass C) dpos, needs no variant; G2P rewrites C from the grid afterwards.
+__global__ void __launch_bounds__(128) k_mpm_material(MpmDev M, int gen) {
+  const u32 ns = *M.nslots;
+  for (u32 slot = blockIdx.x; slot < ns; slot += gridDim.x) {
+    const u32 cnt = M.count[gen][slot];
+    for (u32 q = threadIdx.x; q < cnt; q += blockDim.x) {
+      const u32 id1 = M.chunk_of[gen][(u64)slot * M.maxc + q / MPM_CHUNK];
+      u8 *ch = mpm_chunk_ptr(M, gen, id1);
+      const u32 i = q % MPM_CHUNK;
+      if ((ch + MPM_CELL_OFF)[i] == 0xffu) continue;  // tombstone
+      u8 *xch = mpm_xchunk_ptr(M, gen, id1);
+      float4 p1 = ((const float4 *)(ch + MPM_PLANE_BYTES))[i];
+      const float4 p2 = ((const float4 *)(ch + 2 * MPM_PLANE_BYTES))[i], p3 = ((const float4 *)(ch + 3 * MPM_PLANE_BYTES))[i];
+      MpmX X = mpm_x_load(xch, i);
+      const float C[9] = {p1.w, p2.x, p2.y, p2.z, p2.w, p3.x, p3.y, p3.z, p3.w};
+      const float Fo[9] = {X.a.x, X.a.y, X.a.z, X.a.w, X.b.x, X.b.y, X.b.z, X.b.w, X.c.x};
+      const int material = __float_as_int(X.c.z);
+      float F[9];
+      for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) {
+          float a = 0.f;
+          for (int m = 0; m < 3; m++) a += ((r == m ? 1.f : 0.f) + M.dt * C[r * 3 + m]) * Fo[m * 3 + c];
+          F[r * 3 + c] = a;
+        }
+      float jp = X.c.y;
+      float h = fmaxf(0.1f, fminf(5.f, expf(10.f * (1.f - jp))));
+      if (material == 1) h = 0.3f;
+      float mu = M.mu_0 * h;
+      const float la = M.lambda_0 * h;
+      if (material == 0) mu = 0.f;
+      float U[9], sig[3], V[9];
+      b2_svd3(F, U, sig, V);
+      float J = 1.f;
+      for (int d = 0; d < 3; d++) {
+        float nsig = sig[d];
+        if (material == 2) nsig = fminf(fmaxf(sig[d], 1.f - 2.5e-2f), 1.f + 4.5e-3f);
+        jp *= sig[d] / nsig, sig[d] = nsig, J *= nsig;
+      }
+      float R[9];
+      for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) {
+          R[r * 3 + c] = U[r * 3] * V[c * 3] + U[r * 3 + 1] * V[c * 3 + 1] + U[r * 3 + 2] * V[c * 3 + 2];
+          if (material == 0)
+            F[r * 3 + c] = r == c ? cbrtf(J) : 0.f;
+          else if (material == 2)
+            F[r * 3 + c] = U[r * 3] * sig[0] * V[c * 3] + U[r * 3 + 1] * sig[1] * V[c * 3 + 1] + U[r * 3 + 2] * sig[2] * V[c * 3 + 2];
+        }
+      const float k = -M.dt * M.p_vol * 4.f * M.inv_dx * M.inv_dx / M.p_mass;
+      float A[9];
+      for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) {
+          float a = 0.f;
+          for (int m = 0; m < 3; m++) a += (F[r * 3 + m] - R[r * 3 + m]) * F[c * 3 + m];
+          A[r * 3 + c] = k * (2.f * mu * a + (r == c ? la * J * (J - 1.f) : 0.f)) + C[r * 3 + c];
+        }
+      X.a = make_float4(F[0], F[1], F[2], F[3]), X.b = make_float4(F[4], F[5], F[6], F[7]), X.c.x = F[8], X.c.y = jp;
+      mpm_x_store(xch, i, X);
+      p1.w = A[0];
+      ((float4 *)(ch + MPM_PLANE_BYTES))[i] = p1;
+      ((float4 *)(ch + 2 * MPM_PLANE_BYTES))[i] = make_float4(A[1], A[2], A[3], A[4]);
+      ((float4 *)(ch + 3 * MPM_PLANE_BYTES))[i] = make_float4(A[5], A[6], A[7], A[8]);
+      ((float *)ch)[i * 4 + 3] = 1.0f;  // J: the scalar stress of the mpm3d.py model is switched off
     }
   }
 }
@@ -746,6 +856,11 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   if (p.layout < 0 || p.layout > 2) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "layout");
   if (p.layout > 0 && p.n_grid % 32) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "sparse layouts need n_grid % 32 == 0");
   if (p.max_particles <= 0) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "max_particles");
+  if (p.model < 0 || p.model > 1) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "model");
+  if (p.model == 1 && !(p.nu > -1.f && p.nu < 0.5f)) throw B2Error(TI_ERROR_INVALID_ARGUMENT, "model 1 needs Poisson's ratio nu in (-1, 0.5)");
+  if (p.model == 1 && !p.block_local) throw B2Error(TI_ERROR_NOT_SUPPORTED, "model 1 runs on the block-local kernels only");
+  if (p.model == 1 && (p.slab_lo != 0 || (p.slab_hi != 0 && p.slab_hi != p.n_grid / 4)))
+    throw B2Error(TI_ERROR_NOT_SUPPORTED, "model 1 is not slab-decomposed (migrant records carry no F / Jp / material)");
   const int nb = p.n_grid / 4;
   // grid SNode tree; leaf cell = {vx, vy, vz, m}
   std::vector<B2SNodeDesc> d;
@@ -789,7 +904,9 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   M.dx = 1.0f / (float)p.n_grid;
   M.inv_dx = (float)p.n_grid;
   M.dt = p.dt;
-  M.p_vol = (M.dx * 0.5f) * (M.dx * 0.5f);
+  M.p_vol = p.p_vol > 0.f ? p.p_vol : (M.dx * 0.5f) * (M.dx * 0.5f);
+  M.model = p.model;
+  M.mu_0 = p.E / (2.f * (1.f + p.nu)), M.lambda_0 = p.E * p.nu / ((1.f + p.nu) * (1.f - 2.f * p.nu));
   M.p_mass = M.p_vol * p.p_rho;
   M.E = p.E;
   M.gravity = p.gravity;
@@ -824,6 +941,13 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
     B2_CUDA(cudaMalloc(&a, ((size_t)M.arena_cap + 1) * MPM_CHUNK_BYTES));  // (+ the sink chunk of an exhausted arena)
     allocs.push_back(a);
     M.arena[g] = (u8 *)a;
+    M.xarena[g] = nullptr;
+    if (p.model == 1) {  // F, Jp, material: a side arena with the same chunk ids (the default model's chunks stay as they are)
+      void *xa = nullptr;
+      B2_CUDA(cudaMalloc(&xa, ((size_t)M.arena_cap + 1) * MPM_XCHUNK_BYTES));
+      allocs.push_back(xa);
+      M.xarena[g] = (u8 *)xa;
+    }
     M.arena_next[g] = dalloc<u32>(4);
   }
   count_sp = dalloc<u32>(M.max_slots), chunk_sp = dalloc<u32>((size_t)M.max_slots * M.maxc), key_sp = dalloc<int>(M.max_slots), nslots_sp = dalloc<u32>(4);
@@ -922,6 +1046,10 @@ void B2Mpm_t::clear_grid() {
 }
 void B2Mpm_t::p2g() {
   cudaStream_t st = rt->stream();
+  if (M.model == 1) {  // the reference does this at the top of its P2G loop (mpm128.py:36-63)
+    k_mpm_material<<<rt->num_sms * 16, 128, 0, st>>>(M, gen);
+    rt->count_launch();
+  }
   if (!in_substep) B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));  // (P2G takes slots from counter 0, G2P from counter 1)
   if (prm.block_local)
   {
@@ -957,8 +1085,11 @@ void B2Mpm_t::g2p() {
     static const bool r1_form = getenv("B2_G2P_R1") != nullptr;  // experiment switch: the r1 bin prologue
     if (order_valid && !no_order && r1_form)
       k_mpm_g2p_bls<G2PK_T, G2PK_MINB, true><<<rt->num_sms * G2PK_MINB, G2PK_T, 0, st>>>(M, gen);
-    else if (order_valid && !no_order)
-      k_mpm_g2p_ord<G2PK_T, G2PK_MINB><<<rt->num_sms * G2PK_MINB, G2PK_T, 0, st>>>(M, gen);
+    else if (M.model == 1) {
+      if (!order_valid) throw B2Error(TI_ERROR_INVALID_STATE, "model 1: g2p needs the p2g of the same substep before it");
+      k_mpm_g2p_ord<64, 12, true><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
+    } else if (order_valid && !no_order)
+      k_mpm_g2p_ord<G2PK_T, G2PK_MINB, false><<<rt->num_sms * G2PK_MINB, G2PK_T, 0, st>>>(M, gen);
     else
       k_mpm_g2p_bls<64, 12, false><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
   } else {
@@ -1122,6 +1253,55 @@ int32_t b2_mpm_set_particles(B2Mpm m, int64_t n, const float *x, const float *v,
   return b2_mpm_add_particles(m, n, x, v, C, J, nullptr);
 }
 int64_t b2_mpm_num_particles(B2Mpm m) { return m ? m->n_particles : -1; }
+int32_t b2_mpm_set_particles_model(B2Mpm m, int64_t n, const float *x, const float *v, const float *C, const float *Fm, const float *Jp, const int32_t *mat) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  require(m->M.model == 1, TI_ERROR_INVALID_STATE, "the solver was created with model 0 (B2MpmParams.model)");
+  m->reset_bins();
+  if (n <= 0) return 0;
+  require(x != nullptr, TI_ERROR_ARGUMENT_NULL, "x");
+  require(n <= m->prm.max_particles, TI_ERROR_ARGUMENT_OUT_OF_RANGE, "more particles than max_particles");
+  cudaStream_t st = m->rt->stream();
+  B2Staged sx, sv, sc, sf, sj, sm;
+  sx.init(x, (size_t)n * 12, true, false, st);
+  if (v) sv.init(v, (size_t)n * 12, true, false, st);
+  if (C) sc.init(C, (size_t)n * 36, true, false, st);
+  if (Fm) sf.init(Fm, (size_t)n * 36, true, false, st);
+  if (Jp) sj.init(Jp, (size_t)n * 4, true, false, st);
+  if (mat) sm.init(mat, (size_t)n * 4, true, false, st);
+  k_mpm_insert<<<m->rt->grid_for(n, 256, 8), 256, 0, st>>>(m->M, m->gen, sx.as<float>(), sv.as<float>(), sc.as<float>(), nullptr, nullptr, n, 0,
+                                                            sf.as<float>(), sj.as<float>(), sm.as<int>());
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  m->n_particles = n;
+  m->order_valid = false;
+  sx.finish(), sv.finish(), sc.finish(), sf.finish(), sj.finish(), sm.finish();
+  return 0;
+  B2_API_END(-1)
+}
+int32_t b2_mpm_get_particles_model(B2Mpm m, float *x, float *v, float *C, float *Fm, float *Jp, int32_t *mat) {
+  B2_API_BEGIN
+  require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");
+  require(m->M.model == 1, TI_ERROR_INVALID_STATE, "the solver was created with model 0 (B2MpmParams.model)");
+  const int64_t n = m->n_particles;
+  if (n == 0) return 0;
+  cudaStream_t st = m->rt->stream();
+  B2Staged sx, sv, sc, sf, sj, sm;
+  if (x) sx.init(x, (size_t)n * 12, false, true, st);
+  if (v) sv.init(v, (size_t)n * 12, false, true, st);
+  if (C) sc.init(C, (size_t)n * 36, false, true, st);
+  if (Fm) sf.init(Fm, (size_t)n * 36, false, true, st);
+  if (Jp) sj.init(Jp, (size_t)n * 4, false, true, st);
+  if (mat) sm.init(mat, (size_t)n * 4, false, true, st);
+  k_mpm_extract<<<m->rt->num_sms * 8, 256, 0, st>>>(m->M, m->gen, sx.as<float>(), sv.as<float>(), sc.as<float>(), nullptr, n, sf.as<float>(),
+                                                    sj.as<float>(), sm.as<int>());
+  m->rt->count_launch();
+  B2_CUDA(cudaGetLastError());
+  sx.finish(), sv.finish(), sc.finish(), sf.finish(), sj.finish(), sm.finish();
+  m->rt->sync();
+  return 0;
+  B2_API_END(-1)
+}
 static int32_t mpm_get_particles(B2Mpm m, float *x, float *v, float *C, float *J, bool wait) {
   B2_API_BEGIN
   require(m != nullptr, TI_ERROR_ARGUMENT_NULL, "mpm");

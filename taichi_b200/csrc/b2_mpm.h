@@ -5,6 +5,7 @@
 #define MPM_CHUNK 256            /* particles per bin chunk                      */
 #define MPM_PLANE_BYTES 4096     /* 256 x float4                                 */
 #define MPM_CHUNK_BYTES 18176    /* 4 float4 planes + 256 x u32 particle ids + 256 x u16 cell-sorted order + 256 x u8 cell */
+#define MPM_XCHUNK_BYTES 12288    /* model 1: bytes per chunk of the side arena (3 float4 planes) */
 #define MPM_PERM_OFF 17408       /* byte offset of the u16 order plane (written by P2G, read by G2P) */
 #define MPM_CELL_OFF 17920       /* byte offset of the u8 cell plane: cell of the entry inside its 4^3 block, 0xff = tombstone (written with the
                                     position by insert / G2P, read by P2G's count phase instead of the 16-byte position) */
@@ -21,6 +22,8 @@ struct MpmDev {
   int nb_shift;    // log2(nb) when pot
   float dx, inv_dx, dt, p_vol, p_mass, E, gravity, stress_k;  // stress_k = -dt*4*E*p_vol/dx^2
   int bound;
+  int model;         // 0: mpm3d.py (J);  1: F / Jp / material with SVD (mpm128.py:36-63 in 3-D)
+  float mu_0, lambda_0;
   int activate_halo;  // reproduce the CUDA-BLS epilogue's wider active set
   int slab_lo, slab_hi;
   // grid
@@ -42,6 +45,7 @@ struct MpmDev {
   u64 *nbptr;        // [max_slots * 8] the bin's neighbour blocks {0,1}^3 as P2G resolved them (valid until the G2P of the substep)
   u32 *live[2];      // [max_slots * MPM_MAXPASS] live (non-tombstone) entries per pass, written by P2G
   u8 *arena[2];
+  u8 *xarena[2];     // model 1: three more float4 planes per chunk {F00..F03 | F10.. | F22, Jp, material, -}, same chunk ids
   u32 *arena_next[2];
   u32 arena_cap;
   u32 *work_counter;  // dynamic slot fetch for the persistent kernels [8]

@@ -19,12 +19,15 @@ __device__ __forceinline__ void g2o_cp16(void *smem, const void *gmem) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((u32)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
 }
 
-template <int NT, int MINB>
+// MODEL: the particle's F / Jp / material (side arena, model 1) travel with it.
+template <int NT, int MINB, bool MODEL>
 __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
   __shared__ float4 sPad[216];
   __shared__ __align__(16) unsigned short sOrder[MPM_PASS];
   __shared__ const u8 *sIn[32];  // the bin's chunks (maxc <= 32)
   __shared__ u8 *sOut[8];
+  __shared__ u8 *sOutX[MODEL ? 8 : 1];
+  __shared__ const u8 *sInX[MODEL ? 32 : 1];
   __shared__ float4 *sNb[8];
   __shared__ u32 sBase, sStay, sSlot;
   const int tid = threadIdx.x, lane = tid & 31;
@@ -44,7 +47,11 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
     const u32 total = M.count[gen][slot];
     const int key = M.slot_key[slot];
     const u32 live0 = M.live[gen][(u64)slot * MPM_MAXPASS];
-    if (tid < 32) sIn[tid] = mpm_chunk_ptr(M, gen, max(M.chunk_of[gen][(u64)slot * M.maxc + min((u32)tid, (u32)M.maxc - 1u)], 1u));
+    if (tid < 32) {
+      const u32 cid = max(M.chunk_of[gen][(u64)slot * M.maxc + min((u32)tid, (u32)M.maxc - 1u)], 1u);
+      sIn[tid] = mpm_chunk_ptr(M, gen, cid);
+      if (MODEL) sInX[tid] = mpm_xchunk_ptr(M, gen, cid);
+    }
     if (tid >= NT - 8) sNb[tid - (NT - 8)] = (float4 *)M.nbptr[(u64)slot * 8 + (u32)(tid - (NT - 8))];
     if (total == 0) {  // (uniform; rare: slots are compacted)
       if (tid == 0) next = atomicAdd(&M.work_counter[1], 1u);
@@ -91,12 +98,14 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
       // ---- the first particles are on their way while the chunks of the reservation are allocated ------------------------
       float4 np0 = make_float4(0.f, 0.f, 0.f, 1.f);
       u32 nid = 0;
+      MpmX nX;
       auto load = [&](int t) {
         if (t < nlive) {
           const u32 q = q0 + sOrder[t];
           const u8 *ch = sIn[q / MPM_CHUNK];
           np0 = ((const float4 *)ch)[q % MPM_CHUNK];
           nid = ((const u32 *)(ch + 4 * MPM_PLANE_BYTES))[q % MPM_CHUNK];
+          if (MODEL) nX = mpm_x_load(sInX[q / MPM_CHUNK], q % MPM_CHUNK);
         }
       };
       load(tid);
@@ -125,6 +134,7 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
           }
         }
         sOut[c - c0] = mpm_chunk_ptr(M, g1, id1);
+        if (MODEL) sOutX[c - c0] = mpm_xchunk_ptr(M, g1, id1);
       }
       for (int t0 = 0; t0 < nlive; t0 += NT) {
         const int t = t0 + tid;
@@ -133,6 +143,8 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
         int nkey = -1, ncell = 0;
         const float4 p0 = np0;
         const u32 id = nid;
+        MpmX X;
+        if (MODEL) X = nX;
         load(t + NT);  // software pipeline: the next particle is loaded while this one is computed
         if (valid) mpm_g2p_particle(M, sPad, p0, id, o0, o1, o2, o3, nkey, ncell);
         if (t0 == 0) __syncthreads();  // sOut (the arithmetic above did not need it)
@@ -154,10 +166,11 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
               ((float4 *)(ch + 3 * MPM_PLANE_BYTES))[i] = o3;
               ((u32 *)(ch + 4 * MPM_PLANE_BYTES))[i] = id;
               (ch + MPM_CELL_OFF)[i] = (u8)ncell;
+              if (MODEL) mpm_x_store(sOutX[c - c0], i, X);
             }
           }
         }
-        if (__any_sync(FULL, valid && !stay)) mpm_insert(M, g1, nkey, ncell, valid && !stay, o0, o1, o2, o3, id);
+        if (__any_sync(FULL, valid && !stay)) mpm_insert(M, g1, nkey, ncell, valid && !stay, o0, o1, o2, o3, id, MODEL ? &X : nullptr);
       }
       __syncthreads();
       // unused tail of the reservation (one entry per particle that left the block)

@@ -158,12 +158,17 @@ class Mpm3D:
     """
 
     def __init__(self, rt, n_grid, max_particles, dt, layout="pointer_bitmasked", E=400.0, p_rho=1.0, gravity=9.8,
-                 bound=3, block_local=True, bls_activate_halo=False, deactivate_every=0, max_bins=0):
+                 bound=3, block_local=True, bls_activate_halo=False, deactivate_every=0, max_bins=0, model="fluid", nu=0.2,
+                 p_vol=0.0):
+        """model: 'fluid' = mpm3d.py (weakly compressible, J);  'materials' = deformation gradient F, plastic Jp and a
+        material id per particle with ti.svd (mpm128.py:36-63 in 3-D: 0 liquid, 1 jelly, 2 snow; E, nu -> mu_0, lambda_0)."""
         self.rt = rt
         self.n_grid = n_grid
+        self.model = {"fluid": 0, "materials": 1}[model]
         p = L.B2MpmParams(n_grid=n_grid, layout=LAYOUTS[layout], dt=dt, E=E, p_rho=p_rho, gravity=gravity, bound=bound,
                           block_local=int(block_local), bls_activate_halo=int(bls_activate_halo), slab_lo=0, slab_hi=0,
-                          deactivate_every=int(deactivate_every), max_particles=max_particles, max_bins=int(max_bins))
+                          deactivate_every=int(deactivate_every), max_particles=max_particles, max_bins=int(max_bins),
+                          model=self.model, nu=nu, p_vol=p_vol)
         self.handle = lib.b2_mpm_create(rt.handle, C.byref(p))
         L.check()
         self.tree = lib.b2_mpm_tree(self.handle)
@@ -180,6 +185,17 @@ class Mpm3D:
     def add_particles(self, x, v=None, Cm=None, J=None, ids=None):
         n = x.shape[0]
         self._ok(lib.b2_mpm_add_particles(self.handle, n, _ptr(x), _ptr(v), _ptr(Cm), _ptr(J), _ptr(ids)))
+
+    def set_particles_model(self, x, v=None, Cm=None, F=None, Jp=None, material=None):
+        """model='materials': F (n, 3, 3) float32, Jp (n,) float32, material (n,) int32; None = identity / 1 / 0."""
+        self._ok(lib.b2_mpm_set_particles_model(self.handle, x.shape[0], _ptr(x), _ptr(v), _ptr(Cm), _ptr(F), _ptr(Jp), _ptr(material)))
+
+    def get_particles_model(self):
+        n = self.num_particles
+        x, v, Cm = np.empty((n, 3), np.float32), np.empty((n, 3), np.float32), np.empty((n, 3, 3), np.float32)
+        F, Jp, mat = np.empty((n, 3, 3), np.float32), np.empty(n, np.float32), np.empty(n, np.int32)
+        self._ok(lib.b2_mpm_get_particles_model(self.handle, _ptr(x), _ptr(v), _ptr(Cm), _ptr(F), _ptr(Jp), _ptr(mat)))
+        return x, v, Cm, F, Jp, mat
 
     @property
     def num_particles(self):
