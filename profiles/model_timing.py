@@ -24,7 +24,8 @@ for model in ("fluid", "materials"):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); s.substep(100); e1.record(); e1.synchronize()
     ms = e0.elapsed_time(e1) / 100
+    s.set_profiling(True); s.substep(25); torch.cuda.synchronize(); ph = s.phase_ms(); s.set_profiling(False)
     st = s.stats()
-    out[model] = {"ms_per_substep": ms, "updates_per_s": N / (ms * 1e-3), "particles": st["particles"], "active_blocks": st["active_blocks"]}
+    out[model] = {"ms_per_substep": ms, "updates_per_s": N / (ms * 1e-3), "particles": st["particles"], "active_blocks": st["active_blocks"], "phase_ms": ph}
     s.destroy()
 print(json.dumps(out))
