@@ -35,12 +35,11 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
   const u32 nslots = *M.nslots;
   const int g1 = gen ^ 1;
   u32 next = 0;  // (thread 0) the slot after the current one
-  if (tid == 0) next = atomicAdd(&M.work_counter[1], 1u);
+  if (tid == 0) sSlot = atomicAdd(&M.work_counter[1], 1u);
 
   for (;;) {
-    __syncthreads();  // everybody has left the previous bin
-    if (tid == 0) sSlot = next;
-    __syncthreads();
+    __syncthreads();  // everybody has left the previous bin, and thread 0 has left the next slot in sSlot (every thread reads
+                      // it before the bin's second barrier, thread 0 writes it again after the bin's last one)
     const u32 slot = sSlot;
     if (slot >= nslots) break;
     // ---- header: independent loads ------------------------------------------------------------------------------------
@@ -54,7 +53,8 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
     }
     if (tid >= NT - 8) sNb[tid - (NT - 8)] = (float4 *)M.nbptr[(u64)slot * 8 + (u32)(tid - (NT - 8))];
     if (total == 0) {  // (uniform; rare: slots are compacted)
-      if (tid == 0) next = atomicAdd(&M.work_counter[1], 1u);
+      __syncthreads();  // (everybody has read sSlot)
+      if (tid == 0) sSlot = atomicAdd(&M.work_counter[1], 1u);
       continue;
     }
     __syncthreads();
@@ -185,6 +185,9 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
     // this generation's bin is consumed: leave it empty for the generation after next
     const u32 nchunks = (total + MPM_CHUNK - 1) / MPM_CHUNK;
     for (int t = tid; t < (int)nchunks; t += NT) M.chunk_of[gen][(u64)slot * M.maxc + t] = 0;
-    if (tid == 0) M.count[gen][slot] = 0;
+    if (tid == 0) {
+      M.count[gen][slot] = 0;
+      sSlot = next;
+    }
   }
 }
