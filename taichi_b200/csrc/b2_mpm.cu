@@ -516,8 +516,8 @@ __global__ void __launch_bounds__(256) k_mpm_diag(MpmDev M, int gen, double *out
 // zero_a / zero_b (optional): the substep's work counters and the chunk-arena cursor of the generation G2P will
 // write -- reset here, by the first kernel of the substep, instead of by three memset nodes between the kernels
 __global__ void __launch_bounds__(256) k_mpm_clear(B2TreeDev *T, int leaf, u32 *zero_a, u32 *zero_b) {
-  if (blockIdx.x == 0 && threadIdx.x < 8) {
-    if (zero_a) zero_a[threadIdx.x] = 0;
+  if (blockIdx.x == 0 && threadIdx.x < 24) {
+    if (zero_a) zero_a[threadIdx.x] = 0;  // (work counters and the size-class lengths of the G2P order)
     if (zero_b && threadIdx.x < 4) zero_b[threadIdx.x] = 0;
   }
   B2CList *L = T->lists[leaf];
@@ -959,7 +959,8 @@ B2Mpm_t::B2Mpm_t(TiRuntime_t *rt_, const B2MpmParams &p) : rt(rt_), prm(p) {
   count_sp = dalloc<u32>(M.max_slots), chunk_sp = dalloc<u32>((size_t)M.max_slots * M.maxc), key_sp = dalloc<int>(M.max_slots), nslots_sp = dalloc<u32>(4);
   if (const char *e = getenv("B2_COMPACT_EVERY")) compact_every = atoi(e);
   M.dbg = getenv("B2_DBG") ? atoi(getenv("B2_DBG")) : 0;
-  M.work_counter = dalloc<u32>(8);
+  M.work_counter = dalloc<u32>(24);
+  M.glist = dalloc<u32>((size_t)16 * M.max_slots);
   listed_bytes = ((size_t)(nblocks + 31) / 32 * 4 + 15) / 16 * 16;
   M.listed = dalloc<u32>(listed_bytes / 4);
   M.stats = dalloc<double>(8);
@@ -1056,7 +1057,7 @@ void B2Mpm_t::p2g() {
     k_mpm_material<<<rt->num_sms * MAT_MINB * 2, MAT_T, 0, st>>>(M, gen);
     rt->count_launch();
   }
-  if (!in_substep) B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 32, st));  // (P2G takes slots from counter 0, G2P from counter 1)
+  if (!in_substep) B2_CUDA(cudaMemsetAsync(M.work_counter, 0, 96, st));  // (P2G takes slots from counter 0, G2P from counter 1; [8..23]: G2P order)
   if (prm.block_local)
   {
     static const int ctas = getenv("B2_P2G_CTAS") ? atoi(getenv("B2_P2G_CTAS")) : P2W_CTAS;  // experiment switch

@@ -48,7 +48,8 @@ struct MpmDev {
   u8 *xarena[2];     // model 1: three more float4 planes per chunk {F00..F03 | F10.. | F22, Jp, material, -}, same chunk ids
   u32 *arena_next[2];
   u32 arena_cap;
-  u32 *work_counter;  // dynamic slot fetch for the persistent kernels [8]
+  u32 *work_counter;  // [0..7] dynamic slot fetch for the persistent kernels; [8..23] lengths of the 16 size classes of glist
+  u32 *glist;         // [16 * max_slots] the bins P2G has processed, by size class (0 = largest): the order G2P takes them in
   u32 *listed;        // [nb^3 / 32] bit per block: the block is in the leaf element list (kept current incrementally)
   int dbg;              // B2_DBG experiment switches (0 in production)
   double *stats;      // [8]

@@ -6,7 +6,7 @@
 // -> chunk ids -> two tree levels per neighbour block -> pad -> live count -> order plane -> reservation -> chunk allocation
 // -> first particle); the ncu source view charges a fifth of the kernel's warp samples to the instructions that wait for them
 // (profiles/r2_ncu_g2p_f2.txt).  Here:
-//   * the slot of the NEXT bin is requested while the current one is processed;
+//   * the slot of the NEXT bin is looked up while the current one is processed;
 //   * entries, key, first live count, chunk ids and the eight neighbour-block pointers (left in M.nbptr by P2G: no tree walk)
 //     are independent loads of one round trip;
 //   * pad and order plane travel global -> shared with cp.async while thread 0 reserves the range in the next generation;
@@ -35,7 +35,23 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
   const u32 nslots = *M.nslots;
   const int g1 = gen ^ 1;
   u32 next = 0;  // (thread 0) the slot after the current one
-  if (tid == 0) sSlot = atomicAdd(&M.work_counter[1], 1u);
+  // Work order: the bins P2G processed, largest size class first, dealt round-robin to the CTAs (item w = blockIdx.x + k *
+  // gridDim.x of the concatenated classes): every CTA gets the same mix and they finish together.
+  __shared__ u32 sCls[17];  // prefix of the class lengths
+  if (tid == 0) {
+    u32 acc = 0;
+    for (int c = 0; c < 16; c++) sCls[c] = acc, acc += M.work_counter[8 + c];
+    sCls[16] = acc;
+  }
+  __syncthreads();
+  auto item = [&](u32 w) -> u32 {  // (thread 0) slot of item w, nslots past the end
+    if (w >= sCls[16]) return nslots;
+    int c = 0;
+    while (w >= sCls[c + 1]) c++;
+    return M.glist[(u64)c * M.max_slots + (w - sCls[c])];
+  };
+  u32 kitem = blockIdx.x;
+  if (tid == 0) sSlot = item(kitem);
 
   for (;;) {
     __syncthreads();  // everybody has left the previous bin, and thread 0 has left the next slot in sSlot (every thread reads
@@ -54,7 +70,8 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
     if (tid >= NT - 8) sNb[tid - (NT - 8)] = (float4 *)M.nbptr[(u64)slot * 8 + (u32)(tid - (NT - 8))];
     if (total == 0) {  // (uniform; rare: slots are compacted)
       __syncthreads();  // (everybody has read sSlot)
-      if (tid == 0) sSlot = atomicAdd(&M.work_counter[1], 1u);
+      kitem += gridDim.x;
+      if (tid == 0) sSlot = item(kitem);
       continue;
     }
     __syncthreads();
@@ -84,9 +101,11 @@ __global__ void __launch_bounds__(NT, MINB) k_mpm_g2p_ord(MpmDev M, int gen) {
       }
       asm volatile("cp.async.wait_all;" ::: "memory");
       __syncthreads();  // order, pad, base
-      // the slot after this one, consumed one bin later.  Not requested at the very start of the kernel, where every CTA's
-      // first request queues up on the one counter: with fewer bins than CTAs (config C2) that cost 10 us of 53
-      if (q0 == 0 && tid == 0) next = atomicAdd(&M.work_counter[1], 1u);
+      // the slot after this one (a dependent load off the size-ordered list), consumed one bin later
+      if (q0 == 0) {
+        kitem += gridDim.x;
+        if (tid == 0) next = item(kitem);
+      }
       if (nlive == 0) continue;  // (uniform)
       const u32 base = sBase;
       const u32 c0 = base / MPM_CHUNK;

@@ -118,6 +118,10 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, CTAS) k_mpm_p2g(MpmDev M, int 
       continue;
     }
     const int key = (int)__shfl_sync(FULL, hdr, 1);
+    if (lane == 0) {  // G2P takes the bins largest first (its CTAs then finish together: the tail of a dynamic schedule is
+      const u32 cls = 15u - min(15u, (total - 1u) >> 6);  // half a bin's time, 8 % of the kernel with 6 bins per CTA)
+      M.glist[(u64)cls * M.max_slots + atomicAdd(&M.work_counter[8 + cls], 1u)] = slot;
+    }
     int bx, by, bz;
     mpm_unkey(M, key, bx, by, bz);
     for (int i = lane; i < 216; i += 32) S.pad[i] = make_float4(0.f, 0.f, 0.f, 0.f);
