@@ -118,10 +118,11 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, CTAS) k_mpm_p2g(MpmDev M, int 
       continue;
     }
     const int key = (int)__shfl_sync(FULL, hdr, 1);
-    if (lane == 0) {  // G2P takes the bins largest first (its CTAs then finish together: the tail of a dynamic schedule is
-      const u32 cls = 15u - min(15u, (total - 1u) >> 6);  // half a bin's time, 8 % of the kernel with 6 bins per CTA)
-      M.glist[(u64)cls * M.max_slots + atomicAdd(&M.work_counter[8 + cls], 1u)] = slot;
-    }
+    // G2P takes the bins largest first, dealt round-robin to its CTAs (they then finish together): the bin is appended to its
+    // size class; the position is requested here and used at the end of the bin (the warp never waits for the atomic)
+    const u32 gcls = 15u - min(15u, (total - 1u) >> 6);
+    u32 gpos = 0;
+    if (lane == 0) gpos = atomicAdd(&M.work_counter[8 + gcls], 1u);
     int bx, by, bz;
     mpm_unkey(M, key, bx, by, bz);
     for (int i = lane; i < 216; i += 32) S.pad[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -330,6 +331,7 @@ __global__ void __launch_bounds__(P2W_WARPS * 32, CTAS) k_mpm_p2g(MpmDev M, int 
       float4 *dst = S.nb[((px >> 2) << 2) | ((py >> 2) << 1) | (pz >> 2)];
       if (dst && (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f)) red_add_v4(dst + (((px & 3) << 4) | ((py & 3) << 2) | (pz & 3)), v);
     }
+    if (lane == 0) M.glist[(u64)gcls * M.max_slots + gpos] = slot;
     __syncwarp();
   }
 }
