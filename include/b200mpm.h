@@ -373,6 +373,8 @@ TI_DLL_EXPORT int64_t b2_pool_bytes_used(TiRuntime runtime); /* memory-profiler 
  * the allocator counters, then the pool usage. Returns the size needed (incl. NUL); synchronises. */
 TI_DLL_EXPORT int64_t b2_memory_profiler_info(B2Tree tree, char *out, int64_t cap);
 TI_DLL_EXPORT void b2_set_pool_size(uint64_t bytes);         /* ti.init(device_memory_GB=), before ti_create_runtime */
+TI_DLL_EXPORT void b2_set_random_seed(int32_t seed);      /* ti.init(random_seed=): seeds the per-thread xorshift128 states of run-time bodies
+                                                            (c.rand_u32 / rand_f32 / rand_f64, runtime.cpp:527-541,1790-1827), before the first launch */
 /* Kernel launch counter (all kernels this library launched since creation). */
 TI_DLL_EXPORT uint64_t b2_launch_count(TiRuntime runtime);
 /* device-side error channel (taichi_assert_format / check_runtime_error): returns 0 if none,

@@ -165,6 +165,7 @@ SIGNATURES = {
     "b2_device_index": (C.c_int32, [C.c_void_p]),
     "b2_pool_bytes_used": (C.c_int64, [C.c_void_p]),
     "b2_set_pool_size": (None, [C.c_uint64]),
+    "b2_set_random_seed": (None, [C.c_int32]),
     "b2_launch_count": (C.c_uint64, [C.c_void_p]),
     "b2_check_runtime_error": (C.c_int32, [C.c_void_p, C.c_char_p, C.c_uint64]),
     "b2_mpm_create": (C.c_void_p, [C.c_void_p, C.POINTER(B2MpmParams)]),

@@ -60,6 +60,9 @@ struct TiRuntime_t {
   int device = 0;
   int num_sms = 0;
   B2Pool *pool_dev = nullptr;  // device copy of the pool header
+  unsigned *rand_states = nullptr;  // xorshift128 state {x, y, z, w} per linear thread id of a run-time body (runtime.cpp:527-541)
+  int num_rand_states = 0;
+  unsigned *ensure_rand_states();   // allocated and seeded at the first use (runtime_initialize_rand_states_cuda, runtime.cpp:973-977)
   void *pool_mem = nullptr;
   uint64_t pool_size = 0;
   uint64_t launches = 0;

@@ -172,6 +172,7 @@ static void jit_upload_table(B2JitKernel k, B2Tree t, const int32_t *field_place
   static thread_local B2JitTable tab;  // 10 KB: not on the stack
   memset(&tab, 0, sizeof(tab));
   tab.n_fields = n_fields, tab.n_args = n_args;
+  tab.rand_states = (unsigned long long)t->rt->ensure_rand_states(), tab.num_rand = t->rt->num_rand_states;
   for (int i = 0; i < n_args; i++) tab.args[i] = args[i];
   for (int i = 0; i < n_fields; i++) {
     const int pid = field_places[i];

@@ -54,6 +54,8 @@ struct B2JitTable {
   B2JitField f[B2_JIT_MAX_FIELDS];
   int n_bls, pad;
   B2JitBls bls[B2_JIT_MAX_BLS];
+  unsigned long long rand_states;  // uint4 {x, y, z, w} per linear thread id
+  int num_rand, pad2;
 };
 
 #ifdef __CUDACC_RTC__  // everything below exists only in the run-time compiled translation unit
@@ -82,6 +84,25 @@ __device__ __forceinline__ void b2_atomic_minmax(double *p, double v, bool mx) {
 struct B2Access {
   B2TreeDev *T;
   const B2JitTable *tab;
+
+  // ti.random: xorshift128 with one persistent state per linear thread id of the launch, output multiplied by a prime
+  // (rand_u32 / rand_f32 / rand_f64 / rand_i32, runtime.cpp:1790-1827).  The stream a loop index sees depends on the
+  // launch geometry, as in the reference.
+  __device__ __forceinline__ unsigned rand_u32() const {
+    uint4 *st = (uint4 *)tab->rand_states + (blockIdx.x * blockDim.x + threadIdx.x) % (unsigned)tab->num_rand;
+    uint4 s = *st;
+    const unsigned t = s.x ^ (s.x << 11);
+    s.x = s.y, s.y = s.z, s.z = s.w;
+    s.w = (s.w ^ (s.w >> 19)) ^ (t ^ (t >> 8));
+    *st = s;
+    return s.w * 1000000007u;
+  }
+  __device__ __forceinline__ int rand_i32() const { return (int)rand_u32(); }
+  __device__ __forceinline__ float rand_f32() const { return (float)(rand_u32() >> 8) * (1.0f / 16777216.0f); }
+  __device__ __forceinline__ double rand_f64() const {
+    const unsigned long long hi = rand_u32(), lo = rand_u32();
+    return (double)(((hi << 32) + lo) >> 11) * (1.0 / 9007199254740992.0);
+  }
 
   template <typename V>
   __device__ __forceinline__ V arg(int k) const {

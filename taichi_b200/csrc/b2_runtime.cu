@@ -55,6 +55,8 @@ void ti_get_cuda_stream(void **stream) {
   if (stream) *stream = (void *)g_stream;
 }
 void b2_set_pool_size(uint64_t bytes) { g_pool_size = bytes; }
+static int32_t g_random_seed = 0;  // ti.init(random_seed=), compile_config.cpp
+void b2_set_random_seed(int32_t seed) { g_random_seed = seed; }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -94,9 +96,27 @@ TiRuntime_t::TiRuntime_t(int device_index) : device(device_index) {
   B2_CUDA(cudaStreamSynchronize(stream()));
   b2_noalloc_setup(device_index);
 }
+// initialize_rand_state (runtime.cpp:535-541): state i of the run = starting_rand_state + i with
+// starting_rand_state = random_seed * 1048391 (llvm_runtime_executor.cpp:639)
+__global__ void k_init_rand_states(unsigned *st, int n, unsigned start) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const unsigned k = start + (unsigned)i;
+    st[4 * i] = 123456789u * k * 1000000007u, st[4 * i + 1] = 362436069u, st[4 * i + 2] = 521288629u, st[4 * i + 3] = 88675123u;
+  }
+}
+unsigned *TiRuntime_t::ensure_rand_states() {
+  if (rand_states) return rand_states;
+  num_rand_states = num_sms * 2048;  // the widest launch of a run-time body: 8 CTAs x 256 or 16 CTAs x 128 threads per SM
+  B2_CUDA(cudaMalloc((void **)&rand_states, (size_t)num_rand_states * 16));
+  k_init_rand_states<<<num_sms * 4, 256, 0, stream()>>>(rand_states, num_rand_states, (unsigned)g_random_seed * 1048391u);
+  count_launch();
+  B2_CUDA(cudaGetLastError());
+  return rand_states;
+}
 TiRuntime_t::~TiRuntime_t() {
   cudaSetDevice(device);
   cudaDeviceSynchronize();
+  if (rand_states) cudaFree(rand_states);
   for (auto *m : memories) {
     if (m && !m->imported && m->dev) {
       if (m->host_access)

@@ -71,6 +71,7 @@ def init(arch=cuda, device_memory_GB=None, device_memory_fraction=None, device_i
     reset()
     if device_memory_GB is not None:
         lib.b2_set_pool_size(C.c_uint64(int(device_memory_GB * (1 << 30))))
+    lib.b2_set_random_seed(int(options.get("random_seed") or 0))   # c.rand_* of run-time bodies (ti.random)
     _prog.rt = lib.ti_create_runtime(L.TI_ARCH_CUDA, device_index)
     L.check()
     _prog.nodes = [dict(type=L.ROOT, parent=-1, axes=[], sizes=[], dtype_bytes=0, chunk_size=0)]

@@ -1102,3 +1102,60 @@ def test_thread_local_reductions(ti):
     assert int(n.item()) == 400
     assert abs(float(s.item()) - v.sum()) < 1e-3
     assert float(mx.item()) == float(vals[:400].max()) and float(mn.item()) == float(vals[:400].min())
+
+
+def _np_xorshift_streams(n_threads, n_draws, seed):
+    """NumPy restatement of initialize_rand_state + rand_u32 (runtime.cpp:535-541,1790-1807): draws[k, i] = k-th value of state i."""
+    i = (np.uint32(seed) * np.uint32(1048391) + np.arange(n_threads, dtype=np.uint32)).astype(np.uint32)
+    with np.errstate(over="ignore"):
+        x = (np.uint32(123456789) * i * np.uint32(1000000007)).astype(np.uint32)
+        y = np.full(n_threads, 362436069, np.uint32)
+        z = np.full(n_threads, 521288629, np.uint32)
+        w = np.full(n_threads, 88675123, np.uint32)
+        out = np.zeros((n_draws, n_threads), np.uint32)
+        for k in range(n_draws):
+            t = x ^ (x << np.uint32(11))
+            x, y, z = y, z, w
+            w = (w ^ (w >> np.uint32(19))) ^ (t ^ (t >> np.uint32(8)))
+            out[k] = w * np.uint32(1000000007)
+    return out
+
+
+@pytest.mark.gpu
+def test_rand_streams_of_a_range_for():
+    """ti.random in a run-time body = the reference's xorshift128, one persistent state per linear thread id
+    seeded from ti.init(random_seed=) (runtime.cpp:527-541,973-977,1790-1827).  A range-for of n <= grid x block indices maps
+    index i to thread i, so the first launch must return draw 0 of every stream and the second launch draw 1."""
+    if not have_gpu():
+        pytest.skip("no CUDA device")
+    import torch
+    import taichi_b200 as ti
+    seed, n = 7, 20000
+    ti.init(arch=ti.cuda, device_memory_GB=0.25, random_seed=seed)
+    try:
+        f = ti.field(ti.i32)
+        ti.root.dense(ti.i, 8).place(f)                       # (a tree must exist; the body only uses launch arguments)
+        k = ti.struct_for("""
+B2_RANGE_BODY(c) {
+  unsigned *u = c.arg<unsigned *>(0); float *r = c.arg<float *>(1); double *d = c.arg<double *>(2);
+  const int what = c.arg<int>(3);
+  if (what == 0) u[c.i] = c.rand_u32();
+  else if (what == 1) r[c.i] = c.rand_f32();
+  else d[c.i] = c.rand_f64();
+}
+""", "rand_streams")
+        u = torch.zeros(n, dtype=torch.int32, device="cuda")
+        r = torch.zeros(n, dtype=torch.float32, device="cuda")
+        d = torch.zeros(n, dtype=torch.float64, device="cuda")
+        want = _np_xorshift_streams(n, 5, seed)
+        for draw in range(2):
+            k.range(0, n, fields=[f], args=[u, r, d, np.int32(0)])
+            assert np.array_equal(u.cpu().numpy().view(np.uint32), want[draw]), draw
+        k.range(0, n, fields=[f], args=[u, r, d, np.int32(1)])
+        assert np.array_equal(r.cpu().numpy(), ((want[2] >> np.uint32(8)).astype(np.float32) * np.float32(1.0 / 16777216.0)))
+        k.range(0, n, fields=[f], args=[u, r, d, np.int32(2)])
+        u64 = (want[3].astype(np.uint64) << np.uint64(32)) + want[4].astype(np.uint64)
+        assert np.array_equal(d.cpu().numpy(), (u64 >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0))
+        assert 0.45 < float(r.mean()) < 0.55 and float(r.min()) >= 0.0 and float(r.max()) < 1.0
+    finally:
+        ti.reset()
