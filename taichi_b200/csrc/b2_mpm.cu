@@ -1094,7 +1094,7 @@ void B2Mpm_t::g2p() {
       k_mpm_g2p_bls<G2PK_T, G2PK_MINB, true><<<rt->num_sms * G2PK_MINB, G2PK_T, 0, st>>>(M, gen);
     else if (M.model == 1) {
       if (!order_valid) throw B2Error(TI_ERROR_INVALID_STATE, "model 1: g2p needs the p2g of the same substep before it");
-      k_mpm_g2p_ord<64, 12, true><<<rt->num_sms * 12, 64, 0, st>>>(M, gen);
+      k_mpm_g2p_ord<64, G2PM_MINB, true><<<rt->num_sms * G2PM_MINB, 64, 0, st>>>(M, gen);
     } else if (order_valid && !no_order)
       k_mpm_g2p_ord<G2PK_T, G2PK_MINB, false><<<rt->num_sms * G2PK_MINB, G2PK_T, 0, st>>>(M, gen);
     else

@@ -14,6 +14,9 @@
 //     those chunks to the CTA sits after the first particle's arithmetic, right before its store.
 // Three or four exposed round trips per bin instead of eleven.
 #pragma once
+#ifndef G2PM_MINB
+#define G2PM_MINB 12 /* CTAs per SM of the materials-model variant (80 registers) */
+#endif
 
 __device__ __forceinline__ void g2o_cp16(void *smem, const void *gmem) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((u32)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
