@@ -106,15 +106,16 @@ def c5_ball(b, total, n_grid):
     return (np.array([0.1 + 0.8 * (b + 0.5) / 6.0, 0.6 if b % 2 == 0 else 0.35, 0.5], np.float32) + d * r[:, None]).astype(np.float32)
 
 
-def c5_bounds(world, total, n_grid):
-    """Static slabs cut by the initial particle count per block layer (--slabs weighted)."""
+def c5_bounds(world, total, n_grid, unit=1):
+    """Static slabs cut by the initial particle count per block layer (--slabs weighted); unit = alignment of the cuts in
+    block layers (8 = pointer cells; the driver needs none: the loopback test runs unaligned slabs at world 3)."""
     from taichi_b200 import multigpu as mg
     w = np.zeros(n_grid // 4, np.float64)
     for b in range(6):
         x = c5_ball(b, total, n_grid)
         bx = ((x[:, 0] * np.float32(n_grid) - np.float32(0.5)).astype(np.int32)) >> 2
         w += np.bincount(bx, minlength=n_grid // 4)[:n_grid // 4]
-    return mg.weighted_slab_bounds(w, world)
+    return mg.weighted_slab_bounds(w, world, unit=unit)
 
 
 def make_c5_cloud(world, rank, total, n_grid, bounds=None):
@@ -422,7 +423,7 @@ def run_slabs(args, world, rank, local):
     rt = tb.Runtime(local, device_memory_GB=6)
     lo, hi = mg.slab_bounds(n_grid // 4, world, rank)
     if args.cloud == "c5":
-        bounds = c5_bounds(world, total_c5, n_grid) if args.slabs == "weighted" else None
+        bounds = c5_bounds(world, total_c5, n_grid, args.slab_unit) if args.slabs == "weighted" else None
         if bounds is not None:
             lo, hi = bounds[rank]
         x, v, Cm, J, ids = make_c5_cloud(world, rank, total_c5, n_grid, bounds)
@@ -554,6 +555,7 @@ def main():
                     help="N > 1: balanced = one ball per slab (+ boundary balls), c5 = SURVEY C5: six balls along x under static slabs")
     ap.add_argument("--slabs", default="equal", choices=["equal", "weighted"],
                     help="--cloud c5: equal-width slabs, or static slabs cut so every rank starts with the same particle count")
+    ap.add_argument("--slab-unit", type=int, default=1, help="--slabs weighted: alignment of the slab cuts in 4^3-block layers")
     ap.add_argument("--force-slabs", action="store_true", help="N = 1 through the slab driver on the N > 1 workload (what one rank of a weak-scaling run does, minus the exchange)")
     ap.add_argument("--strong", action="store_true", help="N > 1 with --cloud c5: 64M particles in total at every N (also N = 1 via torchrun)")
     args = ap.parse_args()
