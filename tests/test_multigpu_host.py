@@ -82,6 +82,14 @@ def test_weighted_slab_bounds():
         assert load.max() - w.sum() / world <= w.reshape(32, 8).sum(1).max() + 1e-6
         eq = np.array([w[slice(*mg.slab_bounds(256, world, r))].sum() for r in range(world)])
         assert load.max() <= eq.max() + 1e-6
+    # cuts at single block layers balance better than cuts at pointer cells (what bench.py --slabs weighted uses)
+    for world in (4, 8):
+        fine = mg.weighted_slab_bounds(w, world, unit=1)
+        coarse = mg.weighted_slab_bounds(w, world, unit=8)
+        assert fine[0][0] == 0 and fine[-1][1] == 256 and all(fine[r][1] == fine[r + 1][0] for r in range(world - 1))
+        lf = max(w[lo:hi].sum() for lo, hi in fine)
+        lc = max(w[lo:hi].sum() for lo, hi in coarse)
+        assert lf <= lc + 1e-6 and lf - w.sum() / world <= w.max() + 1e-6
     # degenerate: all the load in one unit still leaves every rank a slab
     w = np.zeros(64); w[3] = 5.0
     b = mg.weighted_slab_bounds(w, 4)
